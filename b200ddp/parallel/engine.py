@@ -1,0 +1,315 @@
+"""DataParallel engine — the replacement for ``DDP(model)`` + ``optim.Adam``.
+
+The reference wraps its model in ``torch.nn.parallel.DistributedDataParallel``
+(reference ``train.py:233``) and steps ``optim.Adam`` (``train.py:249,139``).  Per
+step that costs: 6 grad->bucket copies, one all-reduce, a divide, 6 bucket->grad
+copies and ~50 small optimizer launches.  This engine owns
+both jobs and lays memory out so none of those copies exist:
+
+* every parameter is a view of one flat fp32 *master* arena, every ``.grad`` a
+  view of one flat *gradient* arena, both in bucket (gradient-ready) order
+  (``buckets.py``);
+* a bucket is a contiguous slice; when its last gradient lands, ONE operation
+  reduces it across ranks, scales by ``1/world``, and applies the optimizer
+  update in place.  On the ``b200`` backend that operation is a single sm_100a
+  kernel over NVSwitch peer memory (``symm.py`` / ``csrc/comm``); on ``nccl`` /
+  ``gloo`` it is an async all-reduce followed by the flat optimizer pass;
+* buckets are launched from autograd hooks while backward is still running
+  (side stream on CUDA), so communication overlaps compute like the Reducer.
+
+DDP constructor behaviour that is preserved: parameter shapes
+are verified across ranks, then parameters and buffers are broadcast from rank
+0; buffers are re-broadcast before every training forward when they exist (K4).
+The wrapper exposes ``.module`` like DDP, so the reference's
+``save_checkpoint`` / ``load_checkpoint`` work on it unchanged.
+"""
+from __future__ import annotations
+
+import hashlib
+from typing import Callable, Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..optim import FlatOptimizer
+from ..utils.logging import get_logger
+from .buckets import ArenaLayout, Bucket, MiB, build_layout
+from .process_group import world
+
+logger = get_logger("b200ddp")
+
+
+def _native():
+    from .. import _native as nat
+    return nat
+
+
+class DataParallel(nn.Module):
+    def __init__(
+        self,
+        module: nn.Module,
+        *,
+        optimizer: str = "adam",
+        lr: float = 1e-3,
+        betas=(0.9, 0.999),
+        eps: float = 1e-8,
+        weight_decay: Optional[float] = None,
+        momentum: float = 0.9,
+        backend: str = "auto",
+        compute_dtype: torch.dtype = torch.float32,
+        wire_dtype: Optional[torch.dtype] = None,
+        bucket_cap_mb: float = 25.0,
+        first_bucket_mb: float = 1.0,
+        broadcast_buffers: bool = True,
+        init_sync: bool = True,
+        loss_fn: Optional[Callable] = None,
+        use_program: bool = True,
+        overlap: bool = True,
+        seed: int = 0,
+    ):
+        super().__init__()
+        self.module = module
+        self.rank, self.world_size = world()
+        params = [(n, p) for n, p in module.named_parameters() if p.requires_grad]
+        if not params:
+            raise ValueError("module has no trainable parameters")
+        frozen = [n for n, p in module.named_parameters() if not p.requires_grad]
+        if frozen:
+            raise ValueError(f"frozen parameters are not supported: {frozen[:3]}")
+        self.device = params[0][1].device
+        self.is_cuda = self.device.type == "cuda"
+        if backend == "auto":
+            backend = "b200" if self.is_cuda else "gloo"
+        if backend in ("b200", "nccl") and not self.is_cuda:
+            raise RuntimeError(f"backend {backend!r} requires the model on a CUDA device")
+        self.backend = backend
+        self.compute_dtype = compute_dtype
+        self.wire_dtype = wire_dtype or compute_dtype
+        self.broadcast_buffers = broadcast_buffers
+        self.loss_fn = loss_fn or F.cross_entropy
+        self.overlap = overlap
+        self.seed = seed
+        self._step_index = 0
+
+        if init_sync and self.world_size > 1:
+            self._verify_shapes(params)
+
+        # ---- flat arenas ---------------------------------------------------------
+        grad_elem = 2 if self.wire_dtype == torch.bfloat16 else 4
+        self.layout: ArenaLayout = build_layout(
+            params, elem_bytes=grad_elem,
+            caps=(int(first_bucket_mb * MiB), int(bucket_cap_mb * MiB)))
+        total = self.layout.total
+        self.symm = None
+        if backend == "b200" and self.world_size > 1:
+            from .symm import SymmetricArena
+            self.symm = SymmetricArena(self.device, self.rank, self.world_size)
+        self.master = torch.zeros(total, dtype=torch.float32, device=self.device)
+        self.shadow = None
+        if compute_dtype != torch.float32:
+            self.shadow = self._alloc(total, compute_dtype, peer=True)
+        # gradients are what peers read: they live in peer-mapped memory on b200
+        self.grad = self._alloc(total, self.wire_dtype, peer=True)
+        for (name, p), slot in zip(params, self.layout.slots):
+            sl = slice(slot.offset, slot.offset + slot.numel)
+            with torch.no_grad():
+                self.master[sl].copy_(p.detach().reshape(-1).float())
+                if self.shadow is not None:
+                    self.shadow[sl].copy_(self.master[sl])
+                    p.data = self.shadow[sl].view(slot.shape)
+                else:
+                    p.data = self.master[sl].view(slot.shape)
+            if self.wire_dtype == p.dtype:
+                p.grad = self.grad[sl].view(slot.shape)
+        self._params = [p for _, p in params]
+        if compute_dtype != torch.float32:
+            for b in module.buffers():
+                if b.is_floating_point():
+                    b.data = b.data.to(compute_dtype)
+
+        if init_sync and self.world_size > 1:
+            self._broadcast_state()
+
+        self.optimizer = FlatOptimizer(
+            self.layout, self.master, self.grad, kind=optimizer, lr=lr, betas=betas, eps=eps,
+            weight_decay=weight_decay, momentum=momentum, shadow=self.shadow)
+
+        # ---- bucket-ready tracking -----------------------------------------------
+        self._pending: List[int] = [0] * len(self.layout.buckets)
+        self._launched: List[bool] = [False] * len(self.layout.buckets)
+        self._works: Dict[int, object] = {}
+        self._in_backward = False
+        self._comm_stream = torch.cuda.Stream(self.device) if self.is_cuda else None
+        for p, slot in zip(self._params, self.layout.slots):
+            p.register_post_accumulate_grad_hook(self._make_hook(slot.bucket))
+
+        # ---- fused step program (SimpleNet-class MLPs on a B200) ---------------------
+        self.program = None
+        if use_program and self.is_cuda and hasattr(module, "mlp_spec") and _native().available():
+            from .mlp_program import MLPProgram
+            self.program = MLPProgram(self)
+
+    # ------------------------------------------------------------------ allocation
+    def _alloc(self, n: int, dtype: torch.dtype, peer: bool = False) -> torch.Tensor:
+        if peer and self.symm is not None:
+            return self.symm.alloc(n, dtype)
+        return torch.zeros(n, dtype=dtype, device=self.device)
+
+    # ------------------------------------------------------------------ ctor sync
+    def _verify_shapes(self, params) -> None:
+        desc = ";".join(f"{n}:{tuple(p.shape)}" for n, p in params)
+        digest = hashlib.sha1(desc.encode()).hexdigest()
+        got: List[Optional[str]] = [None] * self.world_size
+        dist.all_gather_object(got, digest)
+        if any(g != got[0] for g in got):
+            bad = [r for r, g in enumerate(got) if g != got[0]]
+            raise RuntimeError(f"parameter shapes differ from rank 0 on ranks {bad}")
+
+    def _broadcast_state(self) -> None:
+        dist.broadcast(self.master, src=0)
+        if self.shadow is not None:
+            self.shadow.copy_(self.master)
+        self._sync_buffers()
+
+    def _sync_buffers(self) -> None:
+        if self.world_size == 1:
+            return
+        bufs = [b for b in self.module.buffers()]
+        if not bufs:
+            return
+        by_dtype: Dict[torch.dtype, List[torch.Tensor]] = {}
+        for b in bufs:
+            by_dtype.setdefault(b.dtype, []).append(b)
+        for dtype, group in by_dtype.items():
+            flat = torch.cat([b.reshape(-1) for b in group])
+            dist.broadcast(flat, src=0)
+            off = 0
+            for b in group:
+                b.copy_(flat[off:off + b.numel()].view_as(b))
+                off += b.numel()
+
+    # ------------------------------------------------------------------ nn.Module
+    def forward(self, *args, **kwargs):
+        if self.training and self.broadcast_buffers and torch.is_grad_enabled():
+            self._sync_buffers()
+        return self.module(*args, **kwargs)
+
+    def parameters_count(self) -> int:
+        return sum(s.numel for s in self.layout.slots)
+
+    # ------------------------------------------------------------------ step API
+    def zero_grad(self) -> None:
+        self.grad.zero_()
+
+    def train_step(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        """One full optimisation step; returns the (detached, on-device) loss."""
+        if self.program is not None:
+            loss = self.program.train_step(data, target)
+            self.optimizer.step_count += 1
+            self._step_index += 1
+            return loss
+        self.module.train()
+        self.zero_grad()
+        self.begin_backward()
+        out = self(data)
+        loss = self.loss_fn(out, target)
+        loss.backward()
+        self.finish_step()
+        return loss.detach()
+
+    def eval_step(self, data: torch.Tensor, target: torch.Tensor):
+        """Validation batch: returns ``(mean loss, correct count)`` as device tensors."""
+        if self.program is not None:
+            return self.program.eval_step(data, target)
+        with torch.no_grad():
+            out = self.module(data)
+            loss = self.loss_fn(out, target)
+            correct = out.argmax(dim=1).eq(target).sum()
+        return loss, correct
+
+    # -- granular API (zero_grad -> forward -> loss.backward -> step), DDP-style -------
+    def begin_backward(self) -> None:
+        for b in self.layout.buckets:
+            self._pending[b.index] = len(b.params)
+            self._launched[b.index] = False
+        self._works.clear()
+        self._in_backward = True
+        self._first_in_step = True
+
+    def _make_hook(self, bucket_index: int):
+        def hook(param):
+            if not self._in_backward:
+                return
+            self._pending[bucket_index] -= 1
+            if self._pending[bucket_index] == 0 and self.overlap:
+                self._launch_bucket(self.layout.buckets[bucket_index])
+        return hook
+
+    def _launch_bucket(self, b: Bucket) -> None:
+        if self._launched[b.index]:
+            return
+        self._launched[b.index] = True
+        if self.world_size == 1:
+            return
+        g = self.grad[b.start:b.end]
+        if self.backend == "b200":
+            return  # fused with the optimizer in finish_step / bucket kernel
+        if self.is_cuda:
+            self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(self._comm_stream):
+                self._works[b.index] = dist.all_reduce(g, op=dist.ReduceOp.SUM, async_op=True)
+        else:
+            self._works[b.index] = dist.all_reduce(g, op=dist.ReduceOp.SUM, async_op=True)
+
+    def finish_step(self) -> None:
+        """Waits for every bucket's reduction and applies the optimizer."""
+        self._in_backward = False
+        opt = self.optimizer
+        scale = 1.0 / self.world_size
+        opt.step_count += 1
+        for b in self.layout.buckets:
+            if not self._launched[b.index]:
+                self._launch_bucket(b)
+        nat = _native() if self.is_cuda else None
+        use_native = nat is not None and nat.available()
+        if self.backend == "b200" and self.world_size > 1:
+            self.symm.allreduce_optimizer_step(self, scale)
+        else:
+            for b in self.layout.buckets:
+                w = self._works.get(b.index)
+                if w is not None:
+                    w.wait()
+                if use_native:
+                    nat.optimizer_step(opt, b.start, b.end, scale)
+                else:
+                    opt.step(b.start, b.end, grad_scale=scale, advance=False)
+        self._step_index += 1
+
+    # reference-style spelling: ``loss.backward(); optimizer.step()``
+    def step(self) -> None:
+        self.finish_step()
+
+    # ------------------------------------------------------------------ checkpoint surface
+    def model_state_dict(self) -> Dict[str, torch.Tensor]:
+        """fp32, un-prefixed, one storage per tensor."""
+        out: Dict[str, torch.Tensor] = {}
+        by_name = {s.name: s for s in self.layout.slots}
+        for k, v in self.module.state_dict().items():
+            s = by_name.get(k)
+            if s is not None:
+                out[k] = self.master[s.offset:s.offset + s.numel].view(s.shape).clone()
+            else:
+                out[k] = v.detach().clone()
+        return out
+
+    def load_model_state_dict(self, sd: Dict[str, torch.Tensor]) -> None:
+        self.module.load_state_dict(sd)
+        with torch.no_grad():
+            for s in self.layout.slots:
+                self.master[s.offset:s.offset + s.numel].copy_(sd[s.name].reshape(-1).float())
+            if self.shadow is not None:
+                self.shadow.copy_(self.master)
+        if self.program is not None:
+            self.program.on_params_changed()

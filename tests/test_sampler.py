@@ -1,0 +1,48 @@
+"""ShardSampler vs torch DistributedSampler (SURVEY §2.3 D6, §4 unit tier)."""
+import torch
+from hypothesis import given, settings, strategies as st
+from torch.utils.data.distributed import DistributedSampler
+
+from b200ddp.data import BatchLoader, ShardSampler, SyntheticDataset, create_data_loader
+
+
+def test_golden_vectors_n10_r3():
+    # survey run, N=10 R=3 epoch 0 seed 0
+    want = {0: [4, 5, 0, 2], 1: [1, 3, 8, 4], 2: [7, 9, 6, 1]}
+    for r, idx in want.items():
+        assert ShardSampler(10, 3, r).indices().tolist() == idx
+
+
+@settings(max_examples=60, deadline=None)
+@given(n=st.integers(1, 300), world=st.integers(1, 9), epoch=st.integers(0, 5),
+       seed=st.integers(0, 3), shuffle=st.booleans(), drop_last=st.booleans())
+def test_matches_distributed_sampler(n, world, epoch, seed, shuffle, drop_last):
+    ds = list(range(n))
+    for rank in range(world):
+        ref = DistributedSampler(ds, num_replicas=world, rank=rank, shuffle=shuffle, seed=seed,
+                                 drop_last=drop_last)
+        ref.set_epoch(epoch)
+        ours = ShardSampler(n, world, rank, shuffle=shuffle, seed=seed, drop_last=drop_last)
+        ours.set_epoch(epoch)
+        assert list(ours) == list(ref)
+        assert len(ours) == len(ref)
+
+
+def test_loader_batches_and_short_tail():
+    # N=10000 R=8 B=64 -> 1250 per rank -> 20 batches, last 34
+    ds = SyntheticDataset(10000, seed=0)
+    loader, sampler = create_data_loader(ds, 64, rank=3, world_size=8)
+    assert len(loader) == 20
+    sizes = [x.shape[0] for x, _ in loader]
+    assert sizes == [64] * 19 + [34]
+    idx = sampler.indices()
+    x0, y0 = next(iter(loader))
+    assert torch.equal(x0, ds.data[idx[:64]]) and torch.equal(y0, ds.labels[idx[:64]])
+
+
+def test_dataset_shapes_and_dtypes():
+    ds = SyntheticDataset(17)
+    x, y = ds[3]
+    assert x.shape == (784,) and x.dtype == torch.float32
+    assert y.dtype == torch.int64 and 0 <= int(y) < 10
+    assert len(ds) == 17
