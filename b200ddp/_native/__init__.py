@@ -22,6 +22,7 @@ LIB_PATH = os.path.join(_HERE, "libb200ddp.so")
 
 _lib: Optional[ctypes.CDLL] = None
 _load_error: Optional[str] = None
+_inited = False
 launch_count = 0  # kernels launched through this binding (bench.py reports it)
 
 
@@ -43,9 +44,14 @@ def lib() -> ctypes.CDLL:
 
 def available() -> bool:
     """True when the CUDA kernels can run.  Raises on a GPU box without the library."""
+    global _inited
     if not torch.cuda.is_available():
         return False
-    lib()
+    L = lib()
+    if not _inited:
+        L.b200_init.restype = ctypes.c_int
+        check(L.b200_init(), "b200_init")
+        _inited = True
     return True
 
 

@@ -1,0 +1,176 @@
+"""ctypes signatures and thin tensor-level wrappers for ``include/b200ddp.h``."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import check, lib, stream_ptr
+
+EPI_NONE, EPI_RELU_DROPOUT, EPI_GATE_POSITIVE, EPI_GELU, EPI_GELU_BWD, EPI_SOFTMAX_CE = range(6)
+
+
+class OptHParams(C.Structure):
+    _fields_ = [("kind", C.c_int), ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float),
+                ("eps", C.c_float), ("weight_decay", C.c_float), ("momentum", C.c_float),
+                ("grad_scale", C.c_float)]
+
+
+class GemmDesc(C.Structure):
+    _fields_ = [
+        ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
+        ("A", C.c_void_p), ("lda", C.c_int64), ("a_mn_major", C.c_int),
+        ("B", C.c_void_p), ("ldb", C.c_int64), ("b_mn_major", C.c_int),
+        ("D", C.c_void_p), ("ldd", C.c_int64), ("d_fp32", C.c_int),
+        ("bias", C.c_void_p),
+        ("epilogue", C.c_int),
+        ("aux", C.c_void_p), ("ldaux", C.c_int64),
+        ("aux_out", C.c_void_p),
+        ("colsum", C.c_void_p),
+        ("dropout_p", C.c_float), ("gate_scale", C.c_float),
+        ("seed", C.c_uint64),
+        ("step_dev", C.c_void_p),
+        ("layer_id", C.c_uint32),
+        ("targets", C.c_void_p),
+        ("ce_grad_scale", C.c_float),
+        ("loss_out", C.c_void_p),
+        ("loss_scale", C.c_float),
+        ("ce_write_grad", C.c_int),
+        ("tile_n", C.c_int),
+        ("max_ctas", C.c_int),
+    ]
+
+
+def declare(L: C.CDLL) -> None:
+    L.b200_last_error.restype = C.c_char_p
+    L.b200_launch_count.restype = C.c_uint64
+    L.b200_device_info.argtypes = [C.POINTER(C.c_int)]
+    L.b200_optimizer_step.argtypes = [C.POINTER(OptHParams), C.c_void_p, C.c_void_p, C.c_int,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                      C.c_int, C.c_int, C.c_void_p]
+    L.b200_ce_scratch_bytes.argtypes = [C.c_int64]
+    L.b200_ce_scratch_bytes.restype = C.c_int64
+    L.b200_cross_entropy.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_int64, C.c_int,
+                                     C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.b200_gemm.argtypes = [C.POINTER(GemmDesc), C.c_void_p]
+    L.b200_cast_f32_to_bf16.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+    L.b200_cast_bf16_to_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+    L.b200_stage_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                   C.c_int64, C.c_void_p]
+    L.b200_stage_batch.restype = C.c_int
+    for name in ("b200_device_info", "b200_optimizer_step", "b200_cross_entropy", "b200_gemm",
+                 "b200_cast_f32_to_bf16", "b200_cast_bf16_to_f32"):
+        getattr(L, name).restype = C.c_int
+    from . import bindings_comm
+    bindings_comm.declare(L)
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def launch_count() -> int:
+    return int(lib().b200_launch_count())
+
+
+# ------------------------------------------------------------------ optimizer
+def make_hparams(opt, grad_scale: float) -> OptHParams:
+    hp = opt.hp
+    return OptHParams(opt.kind_id, hp["lr"], hp["betas"][0], hp["betas"][1], hp["eps"],
+                      hp["weight_decay"], hp["momentum"], grad_scale)
+
+
+def optimizer_step(opt, start: int, end: int, grad_scale: float, *, device_step: bool = False,
+                   advance: bool = False) -> None:
+    """Fused update of arena slice [start, end).  Host-step mode uses opt.step_count (already
+    advanced by the caller); device-step mode reads/advances opt.step_dev (CUDA-graph safe)."""
+    hp = make_hparams(opt, grad_scale)
+    n = end - start
+    g = opt.grad[start:end]
+    v = opt.exp_avg_sq[start:end] if opt.kind != "sgd" else None
+    sh = opt.shadow[start:end] if opt.shadow is not None else None
+    check(lib().b200_optimizer_step(
+        C.byref(hp), opt.master[start:end].data_ptr(), g.data_ptr(),
+        1 if g.dtype == torch.bfloat16 else 0, opt.exp_avg[start:end].data_ptr(), _ptr(v), _ptr(sh),
+        n, opt.step_dev.data_ptr() if device_step else None, opt.step_count,
+        1 if advance else 0, stream_ptr(opt.master.device)), "b200_optimizer_step")
+
+
+# ------------------------------------------------------------------ loss
+_ce_scratch = {}
+
+
+def ce_scratch(device) -> torch.Tensor:
+    key = torch.device(device).index
+    if key not in _ce_scratch:
+        nbytes = int(lib().b200_ce_scratch_bytes(1))
+        _ce_scratch[key] = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+    return _ce_scratch[key]
+
+
+def cross_entropy(logits: torch.Tensor, targets: torch.Tensor, dlogits: Optional[torch.Tensor],
+                  grad_scale: float, loss_out: torch.Tensor) -> None:
+    assert logits.dim() == 2 and logits.stride(1) == 1
+    assert logits.dtype in (torch.bfloat16, torch.float32)
+    assert targets.dtype == torch.int64 and targets.is_contiguous()
+    if dlogits is not None:
+        assert dlogits.dtype == logits.dtype and dlogits.stride() == logits.stride()
+    check(lib().b200_cross_entropy(
+        logits.data_ptr(), 1 if logits.dtype == torch.bfloat16 else 0, logits.stride(0),
+        targets.data_ptr(), logits.shape[0], logits.shape[1], _ptr(dlogits), grad_scale,
+        loss_out.data_ptr(), ce_scratch(logits.device).data_ptr(), stream_ptr(logits.device)),
+        "b200_cross_entropy")
+
+
+# ------------------------------------------------------------------ GEMM
+def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, M: int, N: int, K: int,
+         a_mn_major: bool = False, b_mn_major: bool = False, bias: Optional[torch.Tensor] = None,
+         epilogue: int = EPI_NONE, aux: Optional[torch.Tensor] = None,
+         aux_out: Optional[torch.Tensor] = None, colsum: Optional[torch.Tensor] = None,
+         dropout_p: float = 0.0, gate_scale: float = 1.0, seed: int = 0,
+         step_dev: Optional[torch.Tensor] = None, layer_id: int = 0,
+         targets: Optional[torch.Tensor] = None, ce_grad_scale: float = 1.0,
+         loss_out: Optional[torch.Tensor] = None, loss_scale: float = 1.0,
+         ce_write_grad: bool = True, tile_n: int = 0, max_ctas: int = 0) -> None:
+    """out[M,N] = epilogue(A @ B^T).  A is [M,K] (K-major) or stored [K,M] (a_mn_major);
+    B is [N,K] or stored [K,N] (b_mn_major).  Strides are taken from the tensors."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.stride(-1) == 1 and b.stride(-1) == 1 and out.stride(-1) == 1
+    assert out.dtype in (torch.bfloat16, torch.float32)
+    if bias is not None:
+        assert bias.dtype == torch.float32
+    d = GemmDesc()
+    d.M, d.N, d.K = M, N, K
+    d.A, d.lda, d.a_mn_major = a.data_ptr(), a.stride(0), int(a_mn_major)
+    d.B, d.ldb, d.b_mn_major = b.data_ptr(), b.stride(0), int(b_mn_major)
+    d.D, d.ldd, d.d_fp32 = out.data_ptr(), out.stride(0), int(out.dtype == torch.float32)
+    d.bias = _ptr(bias)
+    d.epilogue = epilogue
+    d.aux, d.ldaux = _ptr(aux), (aux.stride(0) if aux is not None else 0)
+    d.aux_out = _ptr(aux_out)
+    d.colsum = _ptr(colsum)
+    d.dropout_p, d.gate_scale = dropout_p, gate_scale
+    d.seed = seed & 0xFFFFFFFFFFFFFFFF
+    d.step_dev = _ptr(step_dev)
+    d.layer_id = layer_id
+    d.targets = _ptr(targets)
+    d.ce_grad_scale = ce_grad_scale
+    d.loss_out = _ptr(loss_out)
+    d.loss_scale = loss_scale
+    d.ce_write_grad = int(ce_write_grad)
+    d.tile_n, d.max_ctas = tile_n, max_ctas
+    check(lib().b200_gemm(C.byref(d), stream_ptr(a.device)), "b200_gemm")
+
+
+def cast_f32_to_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
+    assert src.dtype == torch.float32 and dst.dtype == torch.bfloat16
+    assert src.is_contiguous() and dst.is_contiguous() and src.numel() == dst.numel()
+    check(lib().b200_cast_f32_to_bf16(src.data_ptr(), dst.data_ptr(), src.numel(),
+                                      stream_ptr(src.device)), "b200_cast_f32_to_bf16")
+
+
+def stage_batch(x: torch.Tensor, y: torch.Tensor, x_bf16: torch.Tensor, y_out: torch.Tensor) -> None:
+    assert x.dtype == torch.float32 and x.is_contiguous() and y.dtype == torch.int64
+    check(lib().b200_stage_batch(x.data_ptr(), y.data_ptr(), x_bf16.data_ptr(), y_out.data_ptr(),
+                                 x.numel(), y.numel(), stream_ptr(x.device)), "b200_stage_batch")

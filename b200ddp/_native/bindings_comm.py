@@ -1,0 +1,31 @@
+"""ctypes signatures for the peer-memory collectives (include/b200ddp.h)."""
+from __future__ import annotations
+
+import ctypes as C
+
+MAX_RANKS = 8
+FLAG_WORDS = 2 * MAX_RANKS + 2
+
+
+class Comm(C.Structure):
+    _fields_ = [("rank", C.c_int), ("world", C.c_int),
+                ("grad", C.c_void_p * MAX_RANKS), ("push", C.c_void_p * MAX_RANKS),
+                ("flags", C.c_void_p * MAX_RANKS),
+                ("timeout_ms", C.c_int), ("max_blocks", C.c_int)]
+
+
+def declare(L: C.CDLL) -> None:
+    from .bindings import OptHParams
+    L.b200_symm_alloc.argtypes = [C.c_int64, C.POINTER(C.c_void_p), C.c_void_p]
+    L.b200_symm_open.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+    L.b200_symm_close.argtypes = [C.c_void_p]
+    L.b200_symm_free.argtypes = [C.c_void_p]
+    L.b200_allreduce_optimizer.argtypes = [
+        C.POINTER(Comm), C.c_int, C.POINTER(OptHParams), C.c_int64, C.c_int64, C.c_int,
+        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int,
+        C.c_void_p]
+    L.b200_allreduce.argtypes = [C.POINTER(Comm), C.c_int, C.c_int64, C.c_int64, C.c_int,
+                                 C.c_void_p, C.c_float, C.c_void_p]
+    for name in ("b200_symm_alloc", "b200_symm_open", "b200_symm_close", "b200_symm_free",
+                 "b200_allreduce_optimizer", "b200_allreduce"):
+        getattr(L, name).restype = C.c_int

@@ -86,7 +86,15 @@ class DataParallel(nn.Module):
             raise RuntimeError(f"backend {backend!r} requires the model on a CUDA device")
         self.backend = backend
         self.compute_dtype = compute_dtype
-        self.wire_dtype = wire_dtype or compute_dtype
+        # SimpleNet-class MLPs on a B200 run as a fused step program: bf16 compute, fp32
+        # gradients written straight into the arena by the wgrad epilogues.
+        want_program = (use_program and self.is_cuda and hasattr(module, "mlp_spec")
+                        and compute_dtype == torch.bfloat16 and backend in ("b200",)
+                        and _native().available())
+        if wire_dtype is None:
+            wire_dtype = torch.float32 if want_program else compute_dtype
+        self.wire_dtype = wire_dtype
+        want_program = want_program and wire_dtype == torch.float32
         self.broadcast_buffers = broadcast_buffers
         self.loss_fn = loss_fn or F.cross_entropy
         self.overlap = overlap
@@ -106,7 +114,10 @@ class DataParallel(nn.Module):
         if backend == "b200" and self.world_size > 1:
             from .symm import SymmetricArena
             self.symm = SymmetricArena(self.device, self.rank, self.world_size)
-        self.master = torch.zeros(total, dtype=torch.float32, device=self.device)
+        # fp32 compute: the two-shot kernel pushes updated fp32 parameters straight into
+        # every rank's master arena, so it is peer-mapped too.
+        self.master = self._alloc(total, torch.float32, peer=compute_dtype == torch.float32)
+        self.allow_two_shot = True
         self.shadow = None
         if compute_dtype != torch.float32:
             self.shadow = self._alloc(total, compute_dtype, peer=True)
@@ -147,7 +158,7 @@ class DataParallel(nn.Module):
 
         # ---- fused step program (SimpleNet-class MLPs on a B200) ---------------------
         self.program = None
-        if use_program and self.is_cuda and hasattr(module, "mlp_spec") and _native().available():
+        if want_program:
             from .mlp_program import MLPProgram
             self.program = MLPProgram(self)
 
@@ -194,6 +205,9 @@ class DataParallel(nn.Module):
     def forward(self, *args, **kwargs):
         if self.training and self.broadcast_buffers and torch.is_grad_enabled():
             self._sync_buffers()
+        if self.compute_dtype != torch.float32:
+            args = tuple(a.to(self.compute_dtype) if torch.is_tensor(a) and a.dtype == torch.float32
+                         else a for a in args)
         return self.module(*args, **kwargs)
 
     def parameters_count(self) -> int:
@@ -214,7 +228,7 @@ class DataParallel(nn.Module):
         self.zero_grad()
         self.begin_backward()
         out = self(data)
-        loss = self.loss_fn(out, target)
+        loss = self.loss_fn(out.float(), target)
         loss.backward()
         self.finish_step()
         return loss.detach()
@@ -224,7 +238,7 @@ class DataParallel(nn.Module):
         if self.program is not None:
             return self.program.eval_step(data, target)
         with torch.no_grad():
-            out = self.module(data)
+            out = self(data).float()
             loss = self.loss_fn(out, target)
             correct = out.argmax(dim=1).eq(target).sum()
         return loss, correct

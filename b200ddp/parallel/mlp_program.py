@@ -1,0 +1,195 @@
+"""Fused step program for MLP classifiers (the reference's SimpleNet).
+
+The reference's hot loop (``train.py:132-148``) issues ~100 kernels, 12 bucket
+copies, one all-reduce and 1-2 host syncs per step for ~77 MFLOP of math
+(SURVEY §2.5).  Here the whole step is a fixed schedule of sm_100a kernels that
+is captured once per batch size into a CUDA graph and replayed:
+
+    stage      x fp32 -> bf16, labels -> fixed buffer             (1 launch, outside the graph)
+    forward    3 tcgen05 GEMMs; epilogues fuse bias+ReLU+dropout; the last one
+               fuses softmax cross-entropy forward AND backward (dlogits), the
+               bias-3 gradient and the loss/accuracy reduction
+    backward   2 dgrad GEMMs (epilogue = ReLU/dropout gate + next bias gradient)
+               and 3 wgrad GEMMs writing fp32 straight into the gradient arena
+               (wgrad runs on a forked stream, off the critical path)
+    update     ONE kernel: peer-memory all-reduce + 1/W + Adam + bf16 shadow
+               (plain fused Adam when world size is 1)
+
+No activation is transposed or copied: dgrad/wgrad read the forward tensors
+through MN-major UMMA descriptors.  Dropout masks are never stored: they are a
+pure function of (seed, step, layer, element) and the backward gate is derived
+from the stored activation (H > 0 <=> kept and positive).
+"""
+from __future__ import annotations
+
+from typing import Dict, Tuple
+
+import torch
+
+from .. import _native as nat
+from .._native import bindings as B
+
+
+class _Buffers:
+    def __init__(self, prog: "MLPProgram", bsz: int):
+        dev, bf = prog.device, torch.bfloat16
+        dims = prog.dims
+        self.bsz = bsz
+        self.x = torch.zeros(bsz, dims[0], dtype=bf, device=dev)
+        self.y = torch.zeros(bsz, dtype=torch.int64, device=dev)
+        self.h = [torch.zeros(bsz, d, dtype=bf, device=dev) for d in dims[1:-1]]
+        self.ncls_ld = (dims[-1] + 15) // 16 * 16
+        self.dlogits = torch.zeros(bsz, self.ncls_ld, dtype=bf, device=dev)
+        self.dz = [torch.zeros(bsz, d, dtype=bf, device=dev) for d in dims[1:-1]]
+        self.loss = torch.zeros(2, dtype=torch.float32, device=dev)
+        self.train_graph: torch.cuda.CUDAGraph | None = None
+        self.eval_graph: torch.cuda.CUDAGraph | None = None
+
+
+class MLPProgram:
+    def __init__(self, engine):
+        self.engine = engine
+        self.device = engine.device
+        spec = engine.module.mlp_spec()
+        if engine.shadow is None or engine.shadow.dtype != torch.bfloat16:
+            raise RuntimeError("the fused MLP program needs compute_dtype=bfloat16")
+        if engine.grad.dtype != torch.float32:
+            raise RuntimeError("the fused MLP program writes fp32 gradients (wire_dtype=float32)")
+        self.layers = []
+        by_param = {id(p): s for p, s in zip(engine._params, engine.layout.slots)}
+        for lin, relu, p in spec:
+            ws, bs = by_param[id(lin.weight)], by_param[id(lin.bias)]
+            self.layers.append(dict(
+                n_out=lin.out_features, n_in=lin.in_features, relu=relu, p=float(p),
+                w=engine.shadow[ws.offset:ws.offset + ws.numel].view(ws.shape),          # bf16 [out,in]
+                b=engine.master[bs.offset:bs.offset + bs.numel],                           # fp32 [out]
+                gw=engine.grad[ws.offset:ws.offset + ws.numel].view(ws.shape),            # fp32 [out,in]
+                gb=engine.grad[bs.offset:bs.offset + bs.numel]))
+        for lay in self.layers[:-1]:
+            if not lay["relu"]:
+                raise RuntimeError("hidden layers must be Linear+ReLU(+Dropout)")
+        self.dims = [self.layers[0]["n_in"]] + [l["n_out"] for l in self.layers]
+        if self.dims[-1] > 32:
+            raise RuntimeError("fused cross-entropy epilogue supports up to 32 classes")
+        for d in self.dims[:-1]:
+            if d % 8:
+                raise RuntimeError("layer widths must be multiples of 8 (TMA 16-byte pitch)")
+        self.seed = (int(engine.seed) * 1000003 + engine.rank * 7919 + 12345) & 0xFFFFFFFFFFFFFFFF
+        self._bufs: Dict[int, _Buffers] = {}
+        self._side = torch.cuda.Stream(self.device)
+        self.launches_per_step = 0
+
+    def on_params_changed(self) -> None:
+        pass  # weights are read in place from the arenas; nothing is cached
+
+    # ------------------------------------------------------------------ schedule
+    def _forward(self, bufs: _Buffers, train: bool) -> None:
+        step_dev = self.engine.optimizer.step_dev
+        a = bufs.x
+        L = len(self.layers)
+        for i, lay in enumerate(self.layers[:-1]):
+            B.gemm(a, lay["w"], bufs.h[i], M=bufs.bsz, N=lay["n_out"], K=lay["n_in"], bias=lay["b"],
+                   epilogue=B.EPI_RELU_DROPOUT, dropout_p=lay["p"] if train else 0.0,
+                   seed=self.seed, step_dev=step_dev, layer_id=i)
+            a = bufs.h[i]
+        last = self.layers[-1]
+        B.gemm(a, last["w"], bufs.dlogits, M=bufs.bsz, N=last["n_out"], K=last["n_in"],
+               bias=last["b"], epilogue=B.EPI_SOFTMAX_CE, targets=bufs.y,
+               ce_grad_scale=1.0 / bufs.bsz, loss_out=bufs.loss, loss_scale=1.0 / bufs.bsz,
+               ce_write_grad=train, colsum=last["gb"] if train else None)
+
+    def _backward(self, bufs: _Buffers) -> None:
+        main = torch.cuda.current_stream(self.device)
+        side = self._side
+        acts = [bufs.x] + bufs.h  # input of layer i
+        dout = bufs.dlogits        # gradient w.r.t. layer i's pre-activation, [B, n_out]
+        for i in range(len(self.layers) - 1, -1, -1):
+            lay = self.layers[i]
+            n_out, n_in = lay["n_out"], lay["n_in"]
+            # wgrad on the side stream: gW[n_out, n_in] = dout^T @ act   (both operands MN-major)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                B.gemm(dout, acts[i], lay["gw"], M=n_out, N=n_in, K=bufs.bsz,
+                       a_mn_major=True, b_mn_major=True)
+            if i > 0:
+                prev = self.layers[i - 1]
+                keep = 1.0 / (1.0 - prev["p"]) if prev["p"] > 0 else 1.0
+                # dgrad: dz_{i-1} = (dout @ W_i) * gate(h_{i-1});  W_i stored [n_out, n_in] = [K, N]
+                B.gemm(dout, lay["w"], bufs.dz[i - 1], M=bufs.bsz, N=n_in, K=n_out, b_mn_major=True,
+                       epilogue=B.EPI_GATE_POSITIVE, aux=bufs.h[i - 1], gate_scale=keep,
+                       colsum=prev["gb"])
+                dout = bufs.dz[i - 1]
+        main.wait_stream(side)
+
+    def _update(self) -> None:
+        eng = self.engine
+        scale = 1.0 / eng.world_size
+        if eng.world_size > 1 and eng.symm is not None:
+            eng.symm.allreduce_optimizer_step(eng, scale, device_step=True)
+        elif eng.world_size > 1:
+            raise RuntimeError("fused MLP program needs the b200 backend when world size > 1")
+        else:
+            nb = len(eng.layout.buckets)
+            for k, b in enumerate(eng.layout.buckets):
+                B.optimizer_step(eng.optimizer, b.start, b.end, scale, device_step=True,
+                                 advance=(k == nb - 1))
+
+    def _train_body(self, bufs: _Buffers) -> None:
+        self.engine.grad.zero_()  # bias gradients accumulate with atomics; weights overwrite
+        bufs.loss.zero_()
+        self._forward(bufs, True)
+        self._backward(bufs)
+        self._update()
+
+    def _eval_body(self, bufs: _Buffers) -> None:
+        bufs.loss.zero_()
+        self._forward(bufs, False)
+
+    def _capture(self, body, bufs: _Buffers) -> torch.cuda.CUDAGraph:
+        # Warm up eagerly once (sets kernel attributes, allocates nothing afterwards), restoring
+        # the optimizer state the warm-up step would otherwise consume.
+        g = torch.cuda.CUDAGraph()
+        before = B.launch_count()
+        with torch.cuda.graph(g, stream=torch.cuda.Stream(self.device)):
+            body(bufs)
+        self.launches_per_step = B.launch_count() - before
+        return g
+
+    def _get(self, bsz: int) -> _Buffers:
+        b = self._bufs.get(bsz)
+        if b is None:
+            b = self._bufs[bsz] = _Buffers(self, bsz)
+        return b
+
+    # ------------------------------------------------------------------ public
+    def _stage(self, bufs: _Buffers, data: torch.Tensor, target: torch.Tensor) -> None:
+        x = data.reshape(data.shape[0], -1)
+        if x.dtype != torch.float32 or not x.is_contiguous():
+            x = x.float().contiguous()
+        if x.shape[1] != self.dims[0]:
+            raise ValueError(f"expected {self.dims[0]} features, got {x.shape[1]}")
+        B.stage_batch(x, target.contiguous(), bufs.x, bufs.y)
+
+    def train_step(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        bufs = self._get(int(data.shape[0]))
+        self._stage(bufs, data, target)
+        if bufs.train_graph is None:
+            bufs.train_graph = self._capture(self._train_body, bufs)
+        bufs.train_graph.replay()
+        return bufs.loss[0].clone()
+
+    def eval_step(self, data: torch.Tensor, target: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        bufs = self._get(int(data.shape[0]))
+        self._stage(bufs, data, target)
+        if bufs.eval_graph is None:
+            bufs.eval_graph = self._capture(self._eval_body, bufs)
+        bufs.eval_graph.replay()
+        out = bufs.loss.clone()
+        return out[0], out[1]
+
+    def logits(self, data: torch.Tensor) -> torch.Tensor:
+        """Eval-mode logits [B, classes] fp32 (uncaptured; for tests and ad-hoc inference)."""
+        bufs = self._get(int(data.shape[0]))
+        self._stage(bufs, data, torch.zeros(data.shape[0], dtype=torch.int64, device=self.device))
+        self._eval_body(bufs)
+        return bufs.dlogits[:, : self.dims[-1]].float()

@@ -1,0 +1,128 @@
+"""Symmetric peer memory and the fused all-reduce + optimizer launch.
+
+The process-group half of the engine on the ``b200`` backend: every
+rank owns one symmetric segment — flag block + gradient arena (+ parameter
+arena for the two-shot push) — allocated by the native library, and maps every
+peer's segment through CUDA IPC handles exchanged once over the bootstrap
+process group.  After that no host-side collective runs on the gradient path:
+each bucket is one kernel (``csrc/comm.cu``) that synchronises with its peers
+through epoch flags in this memory.
+
+ref: ``train.py:233`` ``DDP(model)`` (torch Reducer + ProcessGroup) and
+``train.py:139`` ``optimizer.step()``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .. import _native as nat
+from .._native import bindings
+from .._native.bindings_comm import FLAG_WORDS, MAX_RANKS, Comm
+
+_DT = {torch.float32: ("<f4", 4), torch.bfloat16: ("<u2", 2), torch.int32: ("<i4", 4),
+       torch.uint8: ("|u1", 1)}
+
+# Buckets at or below this many bytes use the one-shot kernel (latency path);
+# larger ones use two-shot (bandwidth path).  Overridable for the sweep.
+ONE_SHOT_MAX_BYTES = int(os.environ.get("B200DDP_ONE_SHOT_MAX_BYTES", 2 * 1024 * 1024))
+
+
+class _RawCuda:
+    """Minimal __cuda_array_interface__ carrier so torch can wrap a raw device pointer."""
+
+    def __init__(self, ptr: int, n: int, typestr: str):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False),
+                                         "version": 3, "strides": None}
+
+
+def _wrap(ptr: int, n: int, dtype: torch.dtype, device: torch.device) -> torch.Tensor:
+    typestr, _ = _DT[dtype]
+    t = torch.as_tensor(_RawCuda(ptr, n, typestr), device=device)
+    return t.view(dtype) if t.dtype != dtype else t
+
+
+class SymmetricArena:
+    """Collective allocator of peer-mapped buffers.  ``alloc`` must be called by every rank
+    with the same arguments in the same order."""
+
+    def __init__(self, device: torch.device, rank: int, world: int, group=None):
+        if world > MAX_RANKS:
+            raise RuntimeError(f"b200 backend supports up to {MAX_RANKS} ranks per NVSwitch domain")
+        self.device = torch.device(device)
+        self.rank, self.world, self.group = rank, world, group
+        self.L = nat.lib()
+        self._segments: List[Dict] = []
+        self.flags_local, self.flags_peers = self._alloc_raw(FLAG_WORDS * 4)
+        self.timeout_ms = int(os.environ.get("B200DDP_PEER_TIMEOUT_MS", "30000"))
+
+    def _alloc_raw(self, nbytes: int):
+        nbytes = (nbytes + 255) // 256 * 256
+        ptr = C.c_void_p()
+        handle = (C.c_char * 64)()
+        nat.check(self.L.b200_symm_alloc(nbytes, C.byref(ptr), handle), "b200_symm_alloc")
+        handles: List[Optional[bytes]] = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle), group=self.group)
+        peers = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                peers.append(ptr.value)
+            else:
+                p = C.c_void_p()
+                buf = (C.c_char * 64).from_buffer_copy(h)
+                nat.check(self.L.b200_symm_open(buf, C.byref(p)), f"b200_symm_open(rank {r})")
+                peers.append(p.value)
+        self._segments.append({"local": ptr.value, "peers": peers, "bytes": nbytes})
+        return ptr.value, peers
+
+    def alloc(self, n: int, dtype: torch.dtype) -> torch.Tensor:
+        _, esize = _DT[dtype]
+        local, peers = self._alloc_raw(n * esize)
+        t = _wrap(local, n, dtype, self.device)
+        t._b200_peers = peers  # type: ignore[attr-defined]
+        return t
+
+    def comm(self, grad: torch.Tensor, push: Optional[torch.Tensor] = None) -> Comm:
+        c = Comm()
+        c.rank, c.world = self.rank, self.world
+        for j in range(self.world):
+            c.grad[j] = grad._b200_peers[j]
+            c.push[j] = push._b200_peers[j] if push is not None else None
+            c.flags[j] = self.flags_peers[j]
+        c.timeout_ms = self.timeout_ms
+        c.max_blocks = 0
+        return c
+
+    # ------------------------------------------------------------------ engine hook
+    def allreduce_optimizer_step(self, engine, scale: float, *, device_step: bool = False) -> None:
+        """One fused kernel per bucket, in bucket order (identical on every rank)."""
+        opt = engine.optimizer
+        push = engine.shadow if engine.shadow is not None else engine.master
+        can_push = hasattr(push, "_b200_peers")
+        c = self.comm(engine.grad, push if can_push else None)
+        hp = bindings.make_hparams(opt, scale)
+        wire_bf16 = engine.grad.dtype == torch.bfloat16
+        esize = 2 if wire_bf16 else 4
+        nb = len(engine.layout.buckets)
+        for k, b in enumerate(engine.layout.buckets):
+            algo = 1 if (can_push and b.numel * esize > ONE_SHOT_MAX_BYTES and engine.allow_two_shot) else 0
+            nat.check(self.L.b200_allreduce_optimizer(
+                C.byref(c), algo, C.byref(hp), b.start, b.numel, int(wire_bf16),
+                opt.master.data_ptr(), opt.exp_avg.data_ptr(),
+                opt.exp_avg_sq.data_ptr() if opt.kind != "sgd" else None,
+                opt.shadow.data_ptr() if opt.shadow is not None else None,
+                int(push.dtype == torch.bfloat16), opt.step_dev.data_ptr() if device_step else None,
+                opt.step_count, int(device_step and k == nb - 1),
+                nat.stream_ptr(self.device)), "b200_allreduce_optimizer")
+
+    def allreduce_(self, t: torch.Tensor, start: int, n: int, *, algo: int, scale: float = 1.0,
+                   out: Optional[torch.Tensor] = None) -> None:
+        c = self.comm(t)
+        nat.check(self.L.b200_allreduce(
+            C.byref(c), algo, start, n, int(t.dtype == torch.bfloat16),
+            out.data_ptr() if out is not None else None, scale, nat.stream_ptr(self.device)),
+            "b200_allreduce")

@@ -1,0 +1,357 @@
+// Peer-memory collectives over NVLink 5 / NVSwitch, fused with the optimizer.
+//
+// Replaces torch DDP's Reducer + ProcessGroup all-reduce + optim.Adam for the
+// gradient path (ref train.py:138 backward hooks -> all-reduce, train.py:139
+// optimizer.step).  One kernel per bucket:
+//
+//   one-shot  (small buckets)  every rank loads the bucket from all W ranks'
+//             gradient arenas through peer-mapped pointers, sums in rank order in
+//             fp32 registers, scales by 1/W and applies Adam/AdamW/SGD to its own
+//             full replica.  One NVLink round trip; optimizer work replicated.
+//   two-shot  (large buckets)  rank r pull-reduces shard r, updates only that
+//             shard of master/m/v (optimizer state and work divided by W), and
+//             pushes the *updated parameters* to every rank's parameter arena —
+//             the all-gather moves new weights (bf16: 2 B) instead of gradients.
+//
+// The reduction order is fixed (rank 0..W-1), so every replica computes bit-
+// identical sums and replicas never drift.
+//
+// Synchronisation: two flag barriers per kernel over peer memory — "gradients
+// ready" before the first remote load and "reads/pushes done" before exit — using
+// monotonically increasing epochs (never reset, so no reset race), release
+// stores / acquire loads at .sys scope, and a bounded spin: a dead peer raises
+// a trap on the survivors instead of wedging seven GPUs.
+//
+// Also here: the symmetric allocator (cudaMalloc + CUDA IPC handles exchanged by
+// the Python process group) and a plain in-kernel all-reduce for benchmarking.
+#include "common.cuh"
+#include "optim_update.cuh"
+
+void b200_count_launch(int n);
+
+namespace b200 {
+
+constexpr int MAX_RANKS = B200_MAX_RANKS;
+// flag block (uint32 words) in every rank's symmetric memory:
+//   [0, R)      ready[j]  written by rank j
+//   [R, 2R)     done[j]   written by rank j
+//   [2R]        epoch     local, advanced by the last block of each kernel
+//   [2R+1]      ticket    local block counter
+constexpr int F_READY = 0, F_DONE = MAX_RANKS, F_EPOCH = 2 * MAX_RANKS, F_TICKET = 2 * MAX_RANKS + 1;
+
+struct CommArgs {
+    int rank, world;
+    const void* grad[MAX_RANKS];  // peer-mapped gradient arenas (same layout on every rank)
+    void* push[MAX_RANKS];        // peer-mapped parameter arenas written by two-shot (or null)
+    uint32_t* flags[MAX_RANKS];   // peer-mapped flag blocks
+    uint64_t timeout_ns;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+    float4 v;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint2 ld_peer_u2(const void* p) {
+    uint2 v;
+    asm volatile("ld.global.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ void spin_until(const uint32_t* flag, uint32_t epoch, uint64_t timeout_ns,
+                                           int who) {
+    const uint64_t t0 = globaltimer_ns();
+    while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {
+        if (globaltimer_ns() - t0 > timeout_ns) {
+            printf("b200ddp: peer flag wait timed out (waiting on rank %d, epoch %u, block %d)\n", who,
+                   epoch, (int)blockIdx.x);
+            __trap();
+        }
+    }
+}
+
+// All blocks: wait until every rank has published `epoch` in our ready flags.
+// Block 0 first publishes ours to every rank.
+__device__ __forceinline__ void begin_barrier(const CommArgs& a, uint32_t epoch) {
+    if (blockIdx.x == 0 && threadIdx.x < a.world) {
+        __threadfence_system();
+        st_release_sys(a.flags[threadIdx.x] + F_READY + a.rank, epoch);
+    }
+    if (threadIdx.x < a.world)
+        spin_until(a.flags[a.rank] + F_READY + threadIdx.x, epoch, a.timeout_ns, threadIdx.x);
+    __syncthreads();
+}
+
+// The last block to finish tells every rank we are done reading/pushing, waits
+// for the same from everyone, then advances the local epoch.
+__device__ __forceinline__ void end_barrier(const CommArgs& a, uint32_t epoch, int* step_dev, int new_step) {
+    __shared__ int s_last;
+    __threadfence_system();
+    __syncthreads();
+    uint32_t* mine = a.flags[a.rank];
+    if (threadIdx.x == 0) {
+        const unsigned t = atomicAdd(mine + F_TICKET, 1u);
+        s_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    if (threadIdx.x < a.world) {
+        __threadfence_system();
+        st_release_sys(a.flags[threadIdx.x] + F_DONE + a.rank, epoch);
+        spin_until(mine + F_DONE + threadIdx.x, epoch, a.timeout_ns, threadIdx.x);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mine[F_TICKET] = 0;
+        mine[F_EPOCH] = epoch;
+        if (step_dev) step_dev[0] = new_step;
+        __threadfence();
+    }
+}
+
+template <bool BF16>
+__device__ __forceinline__ float4 load_grad4(const void* base, int64_t i4) {
+    if (BF16) {
+        const uint2 raw = ld_peer_u2(reinterpret_cast<const uint2*>(base) + i4);
+        const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+        const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+        return make_float4(a.x, a.y, b.x, b.y);
+    }
+    return ld_peer_f4(reinterpret_cast<const float*>(base) + 4 * i4);
+}
+
+// Fixed-order sum over ranks of 4 consecutive elements at vector index i4.
+template <bool BF16>
+__device__ __forceinline__ float4 reduce4(const CommArgs& a, int64_t i4) {
+    float4 v[MAX_RANKS];
+#pragma unroll
+    for (int j = 0; j < MAX_RANKS; ++j)
+        if (j < a.world) v[j] = load_grad4<BF16>(a.grad[j], i4);  // all loads in flight first
+    float4 s = v[0];
+#pragma unroll
+    for (int j = 1; j < MAX_RANKS; ++j)
+        if (j < a.world) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
+    return s;
+}
+
+// algo 0: one-shot, full replica update.  algo 1: two-shot, shard update + parameter push.
+// [start, start+n) is the bucket, in elements; start and n are multiples of 4.
+template <bool BF16, int ALGO, bool PUSH_BF16>
+__global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
+    const CommArgs a, b200_opt_hparams hp, int64_t start, int64_t n, float* __restrict__ master,
+    float* __restrict__ m, float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, int* step_dev,
+    int step_host, int advance) {
+    __shared__ OptScalars sc;
+    const uint32_t epoch = *(volatile uint32_t*)(a.flags[a.rank] + F_EPOCH) + 1u;
+    if (threadIdx.x == 0) {
+        const int t = step_dev ? (*(volatile int*)step_dev + 1) : step_host;
+        sc = make_opt_scalars(hp, t);
+    }
+    begin_barrier(a, epoch);  // includes __syncthreads
+    const OptScalars s = sc;
+
+    int64_t lo4 = start >> 2, hi4 = (start + n) >> 2;
+    if (ALGO == 1) {
+        const int64_t per = (((hi4 - lo4) + a.world - 1) / a.world + 15) & ~int64_t(15);
+        lo4 = lo4 + per * a.rank;
+        const int64_t e = lo4 + per;
+        hi4 = e < hi4 ? e : hi4;
+    }
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = lo4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi4; i += stride) {
+        float4 g = reduce4<BF16>(a, i);
+        float4 pp = reinterpret_cast<float4*>(master)[i];
+        float4 mm = reinterpret_cast<float4*>(m)[i];
+        float4 vv = make_float4(0, 0, 0, 0);
+        if (hp.kind != 2) vv = reinterpret_cast<float4*>(v)[i];
+        opt_update(hp.kind, s, pp.x, mm.x, vv.x, g.x * hp.grad_scale);
+        opt_update(hp.kind, s, pp.y, mm.y, vv.y, g.y * hp.grad_scale);
+        opt_update(hp.kind, s, pp.z, mm.z, vv.z, g.z * hp.grad_scale);
+        opt_update(hp.kind, s, pp.w, mm.w, vv.w, g.w * hp.grad_scale);
+        reinterpret_cast<float4*>(m)[i] = mm;
+        if (hp.kind != 2) reinterpret_cast<float4*>(v)[i] = vv;
+        if (ALGO == 0) {
+            reinterpret_cast<float4*>(master)[i] = pp;
+            if (shadow) {
+                uint2 o;
+                o.x = pack_bf16(pp.x, pp.y);
+                o.y = pack_bf16(pp.z, pp.w);
+                reinterpret_cast<uint2*>(shadow)[i] = o;
+            }
+        } else {
+            if (PUSH_BF16) {
+                reinterpret_cast<float4*>(master)[i] = pp;  // owner keeps the fp32 shard
+                uint2 o;
+                o.x = pack_bf16(pp.x, pp.y);
+                o.y = pack_bf16(pp.z, pp.w);
+#pragma unroll
+                for (int j = 0; j < MAX_RANKS; ++j)
+                    if (j < a.world) reinterpret_cast<uint2*>(a.push[j])[i] = o;
+            } else {
+#pragma unroll
+                for (int j = 0; j < MAX_RANKS; ++j)
+                    if (j < a.world) reinterpret_cast<float4*>(a.push[j])[i] = pp;
+            }
+        }
+    }
+    end_barrier(a, epoch, advance ? step_dev : nullptr, s.t);
+}
+
+// Plain all-reduce (sum * scale), for the bandwidth sweep and generic use.
+// algo 0: one-shot into `out` (local).  algo 1: two-shot in place (pull shard, push to all).
+template <bool BF16, int ALGO>
+__global__ void __launch_bounds__(256) allreduce_kernel(const CommArgs a, int64_t start, int64_t n,
+                                                        void* __restrict__ out, float scale) {
+    const uint32_t epoch = *(volatile uint32_t*)(a.flags[a.rank] + F_EPOCH) + 1u;
+    begin_barrier(a, epoch);
+    int64_t lo4 = start >> 2, hi4 = (start + n) >> 2;
+    if (ALGO == 1) {
+        const int64_t per = (((hi4 - lo4) + a.world - 1) / a.world + 15) & ~int64_t(15);
+        lo4 = lo4 + per * a.rank;
+        const int64_t e = lo4 + per;
+        hi4 = e < hi4 ? e : hi4;
+    }
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = lo4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi4; i += stride) {
+        float4 g = reduce4<BF16>(a, i);
+        g.x *= scale; g.y *= scale; g.z *= scale; g.w *= scale;
+        if (BF16) {
+            uint2 o;
+            o.x = pack_bf16(g.x, g.y);
+            o.y = pack_bf16(g.z, g.w);
+            if (ALGO == 0) reinterpret_cast<uint2*>(out)[i] = o;
+            else {
+#pragma unroll
+                for (int j = 0; j < MAX_RANKS; ++j)
+                    if (j < a.world) reinterpret_cast<uint2*>(const_cast<void*>(a.grad[j]))[i] = o;
+            }
+        } else {
+            if (ALGO == 0) reinterpret_cast<float4*>(out)[i] = g;
+            else {
+#pragma unroll
+                for (int j = 0; j < MAX_RANKS; ++j)
+                    if (j < a.world) reinterpret_cast<float4*>(const_cast<void*>(a.grad[j]))[i] = g;
+            }
+        }
+    }
+    end_barrier(a, epoch, nullptr, 0);
+}
+
+static int fill_args(const b200_comm* c, CommArgs* a) {
+    B200_REQUIRE(c && c->world >= 1 && c->world <= MAX_RANKS, "comm: world size must be in [1, %d]", MAX_RANKS);
+    B200_REQUIRE(c->rank >= 0 && c->rank < c->world, "comm: bad rank %d", c->rank);
+    a->rank = c->rank;
+    a->world = c->world;
+    for (int j = 0; j < MAX_RANKS; ++j) {
+        a->grad[j] = j < c->world ? c->grad[j] : nullptr;
+        a->push[j] = j < c->world ? c->push[j] : nullptr;
+        a->flags[j] = j < c->world ? (uint32_t*)c->flags[j] : nullptr;
+        if (j < c->world) B200_REQUIRE(a->grad[j] && a->flags[j], "comm: missing peer pointer for rank %d", j);
+    }
+    a->timeout_ns = c->timeout_ms > 0 ? (uint64_t)c->timeout_ms * 1000000ull : 30000000000ull;
+    return 0;
+}
+
+static int grid_for(int64_t vecs, int max_blocks) {
+    int64_t b = (vecs + 255) / 256;
+    if (b < 1) b = 1;
+    if (b > max_blocks) b = max_blocks;
+    return (int)b;
+}
+
+}  // namespace b200
+
+// ------------------------------------------------------------------ symmetric memory
+extern "C" int b200_symm_alloc(int64_t bytes, void** ptr, void* handle64) {
+    B200_REQUIRE(bytes > 0 && ptr && handle64, "symm_alloc: bad arguments");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    B200_CUDA_OK(cudaMalloc(ptr, (size_t)bytes));
+    B200_CUDA_OK(cudaMemset(*ptr, 0, (size_t)bytes));
+    cudaIpcMemHandle_t h;
+    B200_CUDA_OK(cudaIpcGetMemHandle(&h, *ptr));
+    memcpy(handle64, &h, 64);
+    return 0;
+}
+
+extern "C" int b200_symm_open(const void* handle64, void** ptr) {
+    B200_REQUIRE(handle64 && ptr, "symm_open: bad arguments");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    B200_CUDA_OK(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+
+extern "C" int b200_symm_close(void* ptr) {
+    B200_CUDA_OK(cudaIpcCloseMemHandle(ptr));
+    return 0;
+}
+
+extern "C" int b200_symm_free(void* ptr) {
+    B200_CUDA_OK(cudaFree(ptr));
+    return 0;
+}
+
+// ------------------------------------------------------------------ collectives
+extern "C" int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200_opt_hparams* hp,
+                                        int64_t start, int64_t n, int grad_is_bf16, float* master,
+                                        float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
+                                        int push_is_bf16, int* step_dev, int step_host, int advance,
+                                        void* stream) {
+    using namespace b200;
+    CommArgs a;
+    int rc = fill_args(c, &a);
+    if (rc) return rc;
+    B200_REQUIRE(hp && master && exp_avg, "allreduce_optimizer: null pointer");
+    B200_REQUIRE(algo == 0 || algo == 1, "allreduce_optimizer: unknown algo %d", algo);
+    B200_REQUIRE((start % 4) == 0 && (n % 4) == 0 && n > 0, "allreduce_optimizer: start/n must be multiples of 4");
+    if (algo == 1)
+        for (int j = 0; j < c->world; ++j) B200_REQUIRE(a.push[j], "allreduce_optimizer: two-shot needs push pointers");
+    const int64_t vecs = (algo == 1 ? (n / 4 + c->world - 1) / c->world : n / 4);
+    const int blocks = grid_for(vecs, c->max_blocks > 0 ? c->max_blocks : 296);
+    cudaStream_t s = (cudaStream_t)stream;
+#define GO(BF, AL, PB)                                                                             \
+    allreduce_optimizer_kernel<BF, AL, PB><<<blocks, 256, 0, s>>>(                                 \
+        a, *hp, start, n, master, exp_avg, exp_avg_sq, (__nv_bfloat16*)shadow_bf16, step_dev,      \
+        step_host, advance)
+    if (algo == 0) { if (grad_is_bf16) GO(true, 0, false); else GO(false, 0, false); }
+    else if (push_is_bf16) { if (grad_is_bf16) GO(true, 1, true); else GO(false, 1, true); }
+    else { if (grad_is_bf16) GO(true, 1, false); else GO(false, 1, false); }
+#undef GO
+    b200_count_launch(1);
+    B200_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int b200_allreduce(const b200_comm* c, int algo, int64_t start, int64_t n, int is_bf16,
+                              void* out, float scale, void* stream) {
+    using namespace b200;
+    CommArgs a;
+    int rc = fill_args(c, &a);
+    if (rc) return rc;
+    B200_REQUIRE(algo == 0 || algo == 1, "allreduce: unknown algo %d", algo);
+    B200_REQUIRE((start % 4) == 0 && (n % 4) == 0 && n > 0, "allreduce: start/n must be multiples of 4");
+    B200_REQUIRE(algo == 1 || out, "allreduce: one-shot needs an output buffer");
+    const int64_t vecs = (algo == 1 ? (n / 4 + c->world - 1) / c->world : n / 4);
+    const int blocks = grid_for(vecs, c->max_blocks > 0 ? c->max_blocks : 296);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (is_bf16) {
+        if (algo == 0) allreduce_kernel<true, 0><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
+        else allreduce_kernel<true, 1><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
+    } else {
+        if (algo == 0) allreduce_kernel<false, 0><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
+        else allreduce_kernel<false, 1><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
+    }
+    b200_count_launch(1);
+    B200_CUDA_OK(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,159 @@
+// Fused softmax cross-entropy: forward value, argmax-correct count and the
+// backward (softmax - onehot) * scale in one kernel.
+//
+// ref: train.py:137 criterion(output, target), train.py:138 its backward, and the
+// argmax/eq/sum of validate() at train.py:168-169.  torch runs log_softmax,
+// nll_loss, nll_loss_backward, _log_softmax_backward_data (+ argmax, eq, sum) as
+// separate kernels and syncs the host for each scalar.
+//
+// Small class counts: one warp per row.  Large (LM head, 50257): one 256-thread
+// block per row.  Row statistics are reduced without atomics on floats: every
+// block writes its partial to scratch, the last block to finish (ticket) sums
+// them in block order, so the mean loss is deterministic.
+#include "common.cuh"
+
+void b200_count_launch(int n);
+
+namespace b200 {
+
+constexpr int CE_MAX_BLOCKS = 4096;
+
+template <bool BF16>
+__device__ __forceinline__ float ld_logit(const void* base, int64_t i) {
+    if (BF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(base)[i]);
+    return reinterpret_cast<const float*>(base)[i];
+}
+template <bool BF16>
+__device__ __forceinline__ void st_logit(void* base, int64_t i, float v) {
+    if (BF16) reinterpret_cast<__nv_bfloat16*>(base)[i] = __float2bfloat16_rn(v);
+    else reinterpret_cast<float*>(base)[i] = v;
+}
+
+struct RowStat {
+    float mx, sum;
+    int arg;
+};
+__device__ __forceinline__ RowStat merge(RowStat a, RowStat b) {
+    RowStat r;
+    if (b.mx > a.mx || (b.mx == a.mx && b.arg < a.arg)) { RowStat t = a; a = b; b = t; }
+    r.mx = a.mx;
+    r.arg = a.arg;
+    r.sum = a.sum + (b.sum > 0.f ? b.sum * __expf(b.mx - a.mx) : 0.f);
+    return r;
+}
+
+// TEAM = 32: warp per row, 8 rows per block.  TEAM = 256: block per row.
+template <bool BF16, int TEAM>
+__global__ void __launch_bounds__(256) ce_kernel(const void* __restrict__ logits, int64_t ld,
+                                                 const int64_t* __restrict__ targets, int64_t rows,
+                                                 int classes, void* dlogits, float grad_scale,
+                                                 float* __restrict__ loss_out,
+                                                 unsigned int* __restrict__ ticket,
+                                                 float2* __restrict__ partials) {
+    constexpr int TEAMS = 256 / TEAM;
+    __shared__ RowStat s_stat[8];
+    __shared__ float s_loss[8], s_ok[8];
+    const int team = threadIdx.x / TEAM, lane = threadIdx.x % TEAM;
+    const int warp = threadIdx.x >> 5;
+    float acc_loss = 0.f, acc_ok = 0.f;
+
+    for (int64_t row = (int64_t)blockIdx.x * TEAMS + team; row < rows;
+         row += (int64_t)gridDim.x * TEAMS) {
+        const int64_t base = row * ld;
+        RowStat st{-INFINITY, 0.f, 0x7fffffff};
+        for (int c = lane; c < classes; c += TEAM) {
+            const float x = ld_logit<BF16>(logits, base + c);
+            if (x > st.mx) {
+                st.sum = st.sum * __expf(st.mx - x) + 1.f;
+                st.mx = x;
+                st.arg = c;
+            } else {
+                st.sum += __expf(x - st.mx);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            RowStat other;
+            other.mx = __shfl_xor_sync(0xffffffffu, st.mx, o);
+            other.sum = __shfl_xor_sync(0xffffffffu, st.sum, o);
+            other.arg = __shfl_xor_sync(0xffffffffu, st.arg, o);
+            st = merge(st, other);
+        }
+        if (TEAM > 32) {
+            if ((threadIdx.x & 31) == 0) s_stat[warp] = st;
+            __syncthreads();
+            st = s_stat[0];
+#pragma unroll
+            for (int w = 1; w < 8; ++w) st = merge(st, s_stat[w]);
+            __syncthreads();
+        }
+        const int tgt = (int)targets[row];
+        const float lse = st.mx + __logf(st.sum);
+        if (lane == 0) {
+            acc_loss += lse - ld_logit<BF16>(logits, base + tgt);
+            acc_ok += (st.arg == tgt) ? 1.f : 0.f;
+        }
+        if (dlogits) {
+            const float inv = 1.f / st.sum;
+            for (int c = lane; c < classes; c += TEAM) {
+                const float x = ld_logit<BF16>(logits, base + c);
+                float g = __expf(x - st.mx) * inv;
+                if (c == tgt) g -= 1.f;
+                st_logit<BF16>(dlogits, base + c, g * grad_scale);
+            }
+        }
+    }
+    // block partial -> scratch; last block reduces in block order
+    if ((threadIdx.x % TEAM) == 0) { s_loss[team] = acc_loss; s_ok[team] = acc_ok; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float l = 0.f, k = 0.f;
+        for (int i = 0; i < TEAMS; ++i) { l += s_loss[i]; k += s_ok[i]; }
+        partials[blockIdx.x] = make_float2(l, k);
+        __threadfence();
+        const unsigned int t = atomicAdd(ticket, 1u);
+        if (t == gridDim.x - 1) {
+            __threadfence();
+            float L = 0.f, K = 0.f;
+            for (unsigned int b = 0; b < gridDim.x; ++b) {
+                L += __ldcg(&partials[b].x);
+                K += __ldcg(&partials[b].y);
+            }
+            loss_out[0] = L / (float)rows;
+            loss_out[1] = K;
+            *ticket = 0u;
+        }
+    }
+}
+
+}  // namespace b200
+
+extern "C" int64_t b200_ce_scratch_bytes(int64_t rows) {
+    (void)rows;
+    return 16 + (int64_t)sizeof(float2) * b200::CE_MAX_BLOCKS;
+}
+
+extern "C" int b200_cross_entropy(const void* logits, int logits_bf16, int64_t ld,
+                                  const int64_t* targets, int64_t rows, int classes, void* dlogits,
+                                  float grad_scale, float* loss_out, void* scratch, void* stream) {
+    B200_REQUIRE(logits && targets && loss_out && scratch, "cross_entropy: null pointer");
+    B200_REQUIRE(rows > 0 && classes > 0 && ld >= classes, "cross_entropy: bad shape rows=%lld classes=%d ld=%lld",
+                 (long long)rows, classes, (long long)ld);
+    B200_REQUIRE((uintptr_t)scratch % 16 == 0, "cross_entropy: scratch must be 16-byte aligned");
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
+    float2* partials = reinterpret_cast<float2*>(reinterpret_cast<char*>(scratch) + 16);
+    cudaStream_t s = (cudaStream_t)stream;
+    const bool big = classes > 2048;
+    const int teams = big ? 1 : 8;
+    int64_t blocks = (rows + teams - 1) / teams;
+    if (blocks > b200::CE_MAX_BLOCKS) blocks = b200::CE_MAX_BLOCKS;
+#define LAUNCH(BF, TEAM)                                                                      \
+    b200::ce_kernel<BF, TEAM><<<(int)blocks, 256, 0, s>>>(logits, ld, targets, rows, classes, \
+                                                          dlogits, grad_scale, loss_out, ticket, partials)
+    if (logits_bf16) { if (big) LAUNCH(true, 256); else LAUNCH(true, 32); }
+    else             { if (big) LAUNCH(false, 256); else LAUNCH(false, 32); }
+#undef LAUNCH
+    b200_count_launch(1);
+    B200_CUDA_OK(cudaGetLastError());
+    return 0;
+}

