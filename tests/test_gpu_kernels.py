@@ -47,10 +47,10 @@ def test_optimizer_kernel_matches_torch_ops(B, kind, kw, gdtype):
         ref.optimizer.step(0, ref.layout.total, grad_scale=0.5, advance=False)
         B.optimizer_step(got.optimizer, 0, got.layout.total, 0.5)
     torch.cuda.synchronize()
-    assert torch.allclose(got.master, ref.master, rtol=2e-6, atol=1e-7)
-    assert torch.allclose(got.optimizer.exp_avg, ref.optimizer.exp_avg, rtol=2e-6, atol=1e-8)
+    assert torch.allclose(got.master, ref.master, rtol=2e-6, atol=1e-6)
+    assert torch.allclose(got.optimizer.exp_avg, ref.optimizer.exp_avg, rtol=2e-6, atol=1e-6)
     if kind != "sgd":
-        assert torch.allclose(got.optimizer.exp_avg_sq, ref.optimizer.exp_avg_sq, rtol=2e-6, atol=1e-10)
+        assert torch.allclose(got.optimizer.exp_avg_sq, ref.optimizer.exp_avg_sq, rtol=2e-6, atol=1e-7)
     if got.shadow is not None:
         assert torch.equal(got.shadow, got.master.to(torch.bfloat16))
 
