@@ -152,6 +152,9 @@ class DataParallel(nn.Module):
         self._launched: List[bool] = [False] * len(self.layout.buckets)
         self._works: Dict[int, object] = {}
         self._in_backward = False
+        self._next_bucket = 0
+        self._step_t = 1
+        self.comm_max_blocks = 64
         self._comm_stream = torch.cuda.Stream(self.device) if self.is_cuda else None
         for p, slot in zip(self._params, self.layout.slots):
             p.register_post_accumulate_grad_hook(self._make_hook(slot.bucket))
@@ -250,7 +253,8 @@ class DataParallel(nn.Module):
             self._launched[b.index] = False
         self._works.clear()
         self._in_backward = True
-        self._first_in_step = True
+        self._next_bucket = 0
+        self._step_t = self.optimizer.step_count + 1
 
     def _make_hook(self, bucket_index: int):
         def hook(param):
@@ -258,10 +262,12 @@ class DataParallel(nn.Module):
                 return
             self._pending[bucket_index] -= 1
             if self._pending[bucket_index] == 0 and self.overlap:
-                self._launch_bucket(self.layout.buckets[bucket_index])
+                self._launch_ready()
         return hook
 
     def _launch_bucket(self, b: Bucket) -> None:
+        """Starts the reduction of one bucket.  Buckets go out strictly in index order on every
+        rank (the in-kernel collectives pair up by launch order)."""
         if self._launched[b.index]:
             return
         self._launched[b.index] = True
@@ -269,7 +275,13 @@ class DataParallel(nn.Module):
             return
         g = self.grad[b.start:b.end]
         if self.backend == "b200":
-            return  # fused with the optimizer in finish_step / bucket kernel
+            # fused all-reduce + optimizer on the side stream; a capped grid leaves SMs for
+            # the backward kernels that are still running
+            self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(self._comm_stream):
+                self.symm.launch_bucket(self, b, 1.0 / self.world_size, step_host=self._step_t,
+                                        max_blocks=self.comm_max_blocks if self._in_backward else 0)
+            return
         if self.is_cuda:
             self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(self._comm_stream):
@@ -277,19 +289,25 @@ class DataParallel(nn.Module):
         else:
             self._works[b.index] = dist.all_reduce(g, op=dist.ReduceOp.SUM, async_op=True)
 
+    def _launch_ready(self) -> None:
+        nb = len(self.layout.buckets)
+        while self._next_bucket < nb and self._pending[self._next_bucket] == 0:
+            self._launch_bucket(self.layout.buckets[self._next_bucket])
+            self._next_bucket += 1
+
     def finish_step(self) -> None:
         """Waits for every bucket's reduction and applies the optimizer."""
         self._in_backward = False
         opt = self.optimizer
         scale = 1.0 / self.world_size
-        opt.step_count += 1
-        for b in self.layout.buckets:
-            if not self._launched[b.index]:
-                self._launch_bucket(b)
+        for b in self.layout.buckets:  # parameters that received no gradient: reduce zeros
+            self._pending[b.index] = 0
+        self._launch_ready()
+        opt.step_count = self._step_t
         nat = _native() if self.is_cuda else None
         use_native = nat is not None and nat.available()
         if self.backend == "b200" and self.world_size > 1:
-            self.symm.allreduce_optimizer_step(self, scale)
+            torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
         else:
             for b in self.layout.buckets:
                 w = self._works.get(b.index)
@@ -300,6 +318,23 @@ class DataParallel(nn.Module):
                 else:
                     opt.step(b.start, b.end, grad_scale=scale, advance=False)
         self._step_index += 1
+
+    def consolidate_state(self) -> None:
+        """Makes master/exp_avg/exp_avg_sq complete on every rank (collective; call on all
+        ranks before a checkpoint).  Buckets updated by the two-shot kernel keep optimizer
+        state — and in bf16 mode the fp32 master — only on the shard owner."""
+        if self.symm is None or not self.symm.two_shot_buckets:
+            return
+        opt = self.optimizer
+        tensors = [opt.exp_avg] + ([opt.exp_avg_sq] if opt.kind != "sgd" else [])
+        if self.shadow is not None:
+            tensors.append(self.master)
+        for k in sorted(self.symm.two_shot_buckets):
+            b = self.layout.buckets[k]
+            for r, (lo, hi) in enumerate(self.symm.shard_ranges(b)):
+                if hi > lo:
+                    for t in tensors:
+                        dist.broadcast(t[lo:hi], src=r)
 
     # reference-style spelling: ``loss.backward(); optimizer.step()``
     def step(self) -> None:

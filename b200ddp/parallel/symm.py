@@ -59,6 +59,8 @@ class SymmetricArena:
         self._segments: List[Dict] = []
         self.flags_local, self.flags_peers = self._alloc_raw(FLAG_WORDS * 4)
         self.timeout_ms = int(os.environ.get("B200DDP_PEER_TIMEOUT_MS", "30000"))
+        self.two_shot_buckets = set()
+        self._comm_cache: Dict = {}
 
     def _alloc_raw(self, nbytes: int):
         nbytes = (nbytes + 255) // 256 * 256
@@ -97,27 +99,50 @@ class SymmetricArena:
         c.max_blocks = 0
         return c
 
-    # ------------------------------------------------------------------ engine hook
-    def allreduce_optimizer_step(self, engine, scale: float, *, device_step: bool = False) -> None:
-        """One fused kernel per bucket, in bucket order (identical on every rank)."""
+    # ------------------------------------------------------------------ engine hooks
+    def shard_ranges(self, b) -> List[tuple]:
+        """Element ranges [lo, hi) each rank owns in a two-shot bucket (mirrors comm.cu)."""
+        lo4, hi4 = b.start // 4, (b.start + b.numel) // 4
+        per = ((hi4 - lo4 + self.world - 1) // self.world + 15) // 16 * 16
+        out = []
+        for r in range(self.world):
+            s = lo4 + per * r
+            e = min(s + per, hi4)
+            out.append((4 * s, 4 * max(s, e)))
+        return out
+
+    def launch_bucket(self, engine, b, scale: float, *, step_host: int = 0,
+                      device_step: bool = False, advance: bool = False, max_blocks: int = 0) -> None:
+        """One fused kernel: all-reduce bucket `b` over peer memory, scale, optimizer update."""
         opt = engine.optimizer
         push = engine.shadow if engine.shadow is not None else engine.master
         can_push = hasattr(push, "_b200_peers")
-        c = self.comm(engine.grad, push if can_push else None)
-        hp = bindings.make_hparams(opt, scale)
         wire_bf16 = engine.grad.dtype == torch.bfloat16
         esize = 2 if wire_bf16 else 4
+        algo = 1 if (can_push and engine.allow_two_shot
+                     and b.numel * esize > ONE_SHOT_MAX_BYTES) else 0
+        if algo == 1:
+            self.two_shot_buckets.add(b.index)
+        key = (id(engine), can_push)
+        c = self._comm_cache.get(key)
+        if c is None:
+            c = self._comm_cache[key] = self.comm(engine.grad, push if can_push else None)
+        c.max_blocks = max_blocks
+        hp = bindings.make_hparams(opt, scale)
+        nat.check(self.L.b200_allreduce_optimizer(
+            C.byref(c), algo, C.byref(hp), b.start, b.numel, int(wire_bf16),
+            opt.master.data_ptr(), opt.exp_avg.data_ptr(),
+            opt.exp_avg_sq.data_ptr() if opt.kind != "sgd" else None,
+            opt.shadow.data_ptr() if opt.shadow is not None else None,
+            int(push.dtype == torch.bfloat16), opt.step_dev.data_ptr() if device_step else None,
+            step_host, int(advance), nat.stream_ptr(self.device)), "b200_allreduce_optimizer")
+
+    def allreduce_optimizer_step(self, engine, scale: float, *, device_step: bool = False) -> None:
+        """All buckets back to back, in bucket order (identical on every rank)."""
         nb = len(engine.layout.buckets)
         for k, b in enumerate(engine.layout.buckets):
-            algo = 1 if (can_push and b.numel * esize > ONE_SHOT_MAX_BYTES and engine.allow_two_shot) else 0
-            nat.check(self.L.b200_allreduce_optimizer(
-                C.byref(c), algo, C.byref(hp), b.start, b.numel, int(wire_bf16),
-                opt.master.data_ptr(), opt.exp_avg.data_ptr(),
-                opt.exp_avg_sq.data_ptr() if opt.kind != "sgd" else None,
-                opt.shadow.data_ptr() if opt.shadow is not None else None,
-                int(push.dtype == torch.bfloat16), opt.step_dev.data_ptr() if device_step else None,
-                opt.step_count, int(device_step and k == nb - 1),
-                nat.stream_ptr(self.device)), "b200_allreduce_optimizer")
+            self.launch_bucket(engine, b, scale, step_host=engine.optimizer.step_count,
+                               device_step=device_step, advance=device_step and k == nb - 1)
 
     def allreduce_(self, t: torch.Tensor, start: int, n: int, *, algo: int, scale: float = 1.0,
                    out: Optional[torch.Tensor] = None) -> None:

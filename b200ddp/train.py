@@ -191,6 +191,10 @@ def main(argv=None) -> int:
 
         epoch_time = time.time() - epoch_start
 
+        # two-shot buckets keep optimizer state on the shard owner; make it whole before the
+        # rank-0 save (collective, no-op otherwise)
+        engine.consolidate_state()
+
         if rank == 0:
             logger.info(f"Epoch {epoch} completed in {epoch_time:.2f}s")
             logger.info(f"  Train Loss: {avg_train_loss:.4f}")

@@ -1,0 +1,160 @@
+"""Multi-rank GPU checks, one process per GPU (launched by tests/test_gpu_multi.py or by hand:
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/multi_gpu_worker.py
+Numerics of the peer-memory kernels vs NCCL / torch ops; replicas stay bit-identical."""
+import copy
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch
+import torch.distributed as dist
+
+from b200ddp import DataParallel, SimpleNet
+from b200ddp import _native as nat
+from b200ddp.parallel import symm as symm_mod
+from b200ddp.parallel.process_group import setup_distributed
+from b200ddp.parallel.symm import SymmetricArena
+
+
+def log(*a):
+    if dist.get_rank() == 0:
+        print(*a, flush=True)
+
+
+def rel(a, b):
+    return ((a.float() - b.float()).norm() / b.float().norm().clamp_min(1e-20)).item()
+
+
+def check_plain_allreduce(arena, rank, world, dev):
+    for dtype in (torch.float32, torch.bfloat16):
+        for n in (1024, 1 << 20, 12 * (1 << 20) + 64):
+            buf = arena.alloc(n, dtype)
+            for algo in (0, 1):
+                torch.manual_seed(1000 * rank + n % 997 + algo)
+                src = torch.randn(n, device=dev).to(dtype)
+                buf.copy_(src)
+                want = src.float().clone()
+                dist.all_reduce(want)  # NCCL fp32 sum of the (possibly bf16-rounded) inputs
+                want = want * 0.5
+                out = torch.empty_like(buf) if algo == 0 else None
+                torch.cuda.synchronize(); dist.barrier()
+                arena.allreduce_(buf, 0, n, algo=algo, scale=0.5, out=out)
+                torch.cuda.synchronize()
+                got = out if algo == 0 else buf
+                tol = 1e-6 if dtype == torch.float32 else 4e-3
+                err = rel(got, want)
+                assert err < tol, (dtype, n, algo, err)
+                # identical bits on every rank
+                ref = got.clone(); dist.broadcast(ref, src=0)
+                assert torch.equal(ref, got), ("ranks differ", dtype, n, algo)
+                dist.barrier()
+    log("plain all-reduce: one-shot and two-shot match NCCL (fp32, bf16), ranks bit-identical")
+
+
+def check_fused_optimizer(rank, world, dev, compute_dtype, two_shot, kind):
+    """Engine on the b200 backend vs NCCL all-reduce + the torch-op optimizer."""
+    symm_mod.ONE_SHOT_MAX_BYTES = 0 if two_shot else 1 << 40
+    torch.manual_seed(5)
+    net = SimpleNet().to(dev)
+    eng = DataParallel(copy.deepcopy(net), optimizer=kind, lr=1e-2, backend="b200",
+                       compute_dtype=compute_dtype, use_program=False)
+    ref = DataParallel(copy.deepcopy(net), optimizer=kind, lr=1e-2, backend="nccl",
+                       compute_dtype=compute_dtype, use_program=False)
+    assert torch.equal(eng.master, ref.master)
+    for step in range(3):
+        torch.manual_seed(77 * rank + step)
+        g = torch.randn(eng.layout.total, device=dev)
+        eng.grad.copy_(g); ref.grad.copy_(g)
+        # reference: NCCL sum, then the torch-op update
+        gsum = ref.grad.float().clone(); dist.all_reduce(gsum)
+        ref.grad.copy_(gsum) if ref.grad.dtype == torch.float32 else None
+        ref.optimizer.step_count += 1
+        if ref.grad.dtype == torch.float32:
+            ref.optimizer.step(0, ref.layout.total, grad_scale=1.0 / world, advance=False)
+        else:
+            tmp = ref.optimizer.grad
+            ref.optimizer.grad = gsum
+            ref.optimizer.step(0, ref.layout.total, grad_scale=1.0 / world, advance=False)
+            ref.optimizer.grad = tmp
+        eng.begin_backward()
+        eng.finish_step()
+        torch.cuda.synchronize()
+    eng.consolidate_state()
+    torch.cuda.synchronize()
+    assert torch.allclose(eng.master, ref.master, rtol=3e-6, atol=2e-6), rel(eng.master, ref.master)
+    assert torch.allclose(eng.optimizer.exp_avg, ref.optimizer.exp_avg, rtol=3e-6, atol=2e-6)
+    if eng.shadow is not None:
+        assert torch.equal(eng.shadow, eng.master.to(torch.bfloat16))
+    got = [torch.empty_like(eng.master) for _ in range(world)]
+    dist.all_gather(got, eng.master)
+    assert all(torch.equal(got[0], t) for t in got), "replicas diverged"
+    if eng.shadow is not None:
+        gs = [torch.empty_like(eng.shadow) for _ in range(world)]
+        dist.all_gather(gs, eng.shadow)
+        assert all(torch.equal(gs[0], t) for t in gs), "shadow replicas diverged"
+    sd = eng.optimizer.state_dict()
+    if kind != "sgd":
+        assert float(sd["state"][0]["step"]) == 3.0
+    log(f"fused all-reduce+{kind}: {'two-shot' if two_shot else 'one-shot'} "
+        f"{str(compute_dtype).split('.')[-1]} matches NCCL + torch-op update; replicas identical")
+
+
+def check_program(rank, world, dev):
+    symm_mod.ONE_SHOT_MAX_BYTES = 2 << 20
+    torch.manual_seed(100 + rank)  # different init per rank: ctor broadcast must fix it
+    eng = DataParallel(SimpleNet().to(dev), backend="b200", compute_dtype=torch.bfloat16, lr=1e-3)
+    assert eng.program is not None
+    torch.manual_seed(200 + rank)
+    x = torch.randn(64, 784, device=dev); y = torch.randint(0, 10, (64,), device=dev)
+    losses = [eng.train_step(x, y) for _ in range(40)]
+    torch.cuda.synchronize()
+    l0, l1 = losses[0].item(), losses[-1].item()
+    assert l1 < 0.6 * l0, (l0, l1)
+    got = [torch.empty_like(eng.master) for _ in range(world)]
+    dist.all_gather(got, eng.master)
+    assert all(torch.equal(got[0], t) for t in got), "replicas diverged under the step program"
+    assert eng.optimizer.step_dev[0].item() == 40
+    log(f"fused step program at world {world}: loss {l0:.3f} -> {l1:.3f}, replicas bit-identical")
+
+
+def check_autograd_overlap(rank, world, dev):
+    """Generic autograd path with bucket hooks on the b200 backend vs the nccl backend."""
+    symm_mod.ONE_SHOT_MAX_BYTES = 64 * 1024  # mix of one-shot and two-shot buckets
+    torch.manual_seed(9)
+    net = SimpleNet(dropout=0.0).to(dev)
+    a = DataParallel(copy.deepcopy(net), backend="b200", compute_dtype=torch.float32,
+                     bucket_cap_mb=0.25, first_bucket_mb=0.01, use_program=False)
+    b = DataParallel(copy.deepcopy(net), backend="nccl", compute_dtype=torch.float32,
+                     bucket_cap_mb=0.25, first_bucket_mb=0.01, use_program=False)
+    assert len(a.layout.buckets) >= 3
+    for step in range(4):
+        torch.manual_seed(31 * rank + step)
+        x = torch.randn(32, 784, device=dev); y = torch.randint(0, 10, (32,), device=dev)
+        la = a.train_step(x, y); lb = b.train_step(x, y)
+    torch.cuda.synchronize()
+    a.consolidate_state()
+    assert abs(la.item() - lb.item()) < 1e-4
+    assert torch.allclose(a.master, b.master, rtol=1e-4, atol=1e-6), rel(a.master, b.master)
+    log(f"autograd path, {len(a.layout.buckets)} buckets overlapped with backward: b200 == nccl")
+
+
+def main():
+    rank, world, local = setup_distributed("nccl")
+    dev = torch.device("cuda", local)
+    assert nat.available()
+    arena = SymmetricArena(dev, rank, world)
+    check_plain_allreduce(arena, rank, world, dev)
+    for kind in ("adam", "sgd"):
+        for dtype in (torch.float32, torch.bfloat16):
+            for two_shot in (False, True):
+                check_fused_optimizer(rank, world, dev, dtype, two_shot, kind)
+    check_program(rank, world, dev)
+    check_autograd_overlap(rank, world, dev)
+    dist.barrier()
+    log("MULTI_GPU_OK")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
