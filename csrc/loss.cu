@@ -12,6 +12,8 @@
 // them in block order, so the mean loss is deterministic.
 #include "common.cuh"
 
+#include <mutex>
+
 void b200_count_launch(int n);
 
 namespace b200 {
@@ -147,6 +149,89 @@ extern "C" int b200_cross_entropy(const void* logits, int logits_bf16, int64_t l
     const int teams = big ? 1 : 8;
     int64_t blocks = (rows + teams - 1) / teams;
     if (blocks > b200::CE_MAX_BLOCKS) blocks = b200::CE_MAX_BLOCKS;
+#define LAUNCH(BF, TEAM)                                                                      \
+    b200::ce_kernel<BF, TEAM><<<(int)blocks, 256, 0, s>>>(logits, ld, targets, rows, classes, \
+                                                          dlogits, grad_scale, loss_out, ticket, partials)
+    if (logits_bf16) { if (big) LAUNCH(true, 256); else LAUNCH(true, 32); }
+    else             { if (big) LAUNCH(false, 256); else LAUNCH(false, 32); }
+#undef LAUNCH
+    b200_count_launch(1);
+    B200_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Allocation-free variant.
+//
+// Who needs it: code that sits inside somebody else's memory regime and is not
+// allowed to grow it.  Typical cases are a plugin running in a serving process
+// whose device memory was carved up front (a cudaMalloc there can fail, or stalls
+// every stream while the driver maps memory), a latency-critical loop where the
+// implicit device synchronisation of cudaMalloc/cudaFree is unacceptable, and
+// host code that has no allocator handle at all (a C caller that only holds the
+// tensors it was given).  Such callers cannot provide the partial-sum scratch
+// that b200_cross_entropy asks for, so this entry point brings its own: a fixed
+// array in the library's device image.
+//
+// Cost: every GPU that loads the library carries these B200_CE_STATIC_BYTES
+// until the process exits, whether or not the entry point is ever called.
+namespace b200 {
+constexpr int CE_STATIC_MAX_BLOCKS = B200_CE_STATIC_MAX_BLOCKS;
+constexpr size_t CE_STATIC_BYTES = 16 + sizeof(float2) * CE_STATIC_MAX_BLOCKS;
+}  // namespace b200
+
+// In host code this name is only a handle for the runtime, NOT a device address;
+// the address a kernel may use comes from cudaGetSymbolAddress (below).
+static __device__ __align__(256) unsigned char g_ce_static_scratch[b200::CE_STATIC_BYTES];
+
+namespace b200 {
+// Device address of the array on the current device, resolved once per device
+// with that device current.
+static int ce_static_scratch(void** out) {
+    constexpr int MAX_DEVICES = 64;
+    static std::mutex mu;
+    static void* addr[MAX_DEVICES] = {};
+    int dev = -1;
+    B200_CUDA_OK(cudaGetDevice(&dev));
+    B200_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "cross_entropy_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (addr[dev] == nullptr) {
+        void* p = nullptr;
+        B200_CUDA_OK(cudaGetSymbolAddress(&p, g_ce_static_scratch));
+        B200_REQUIRE(p != nullptr, "cross_entropy_static: cudaGetSymbolAddress returned null");
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return 0;
+}
+}  // namespace b200
+
+extern "C" int b200_cross_entropy_static(const void* logits, int logits_bf16, int64_t ld,
+                                         const int64_t* targets, int64_t rows, int classes,
+                                         void* dlogits, float grad_scale, float* loss_out,
+                                         void* stream) {
+    using namespace b200;
+    B200_REQUIRE(logits && targets && loss_out, "cross_entropy_static: null pointer");
+    B200_REQUIRE(rows > 0 && classes > 0 && ld >= classes,
+                 "cross_entropy_static: bad shape rows=%lld classes=%d ld=%lld", (long long)rows, classes,
+                 (long long)ld);
+    const bool big = classes > 2048;
+    const int teams = big ? 1 : 8;  // rows handled per block
+    const int64_t blocks = (rows + teams - 1) / teams;
+    B200_REQUIRE(blocks <= CE_STATIC_MAX_BLOCKS,
+                 "cross_entropy_static: %lld rows of %d classes need %lld partial slots but the built-in "
+                 "scratch holds %d (limit: %d rows up to 2048 classes, %d rows above); use "
+                 "b200_cross_entropy with caller-provided scratch",
+                 (long long)rows, classes, (long long)blocks, CE_STATIC_MAX_BLOCKS,
+                 CE_STATIC_MAX_BLOCKS * 8, CE_STATIC_MAX_BLOCKS);
+    void* scratch = nullptr;
+    if (int rc = ce_static_scratch(&scratch)) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    // The array still holds whatever the previous call left.  Partials are fully
+    // rewritten by this launch; the ticket counter is the one word that must be zero.
+    B200_CUDA_OK(cudaMemsetAsync(scratch, 0, 16, s));
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch);
+    float2* partials = reinterpret_cast<float2*>(reinterpret_cast<char*>(scratch) + 16);
 #define LAUNCH(BF, TEAM)                                                                      \
     b200::ce_kernel<BF, TEAM><<<(int)blocks, 256, 0, s>>>(logits, ld, targets, rows, classes, \
                                                           dlogits, grad_scale, loss_out, ticket, partials)

@@ -70,6 +70,40 @@ int b200_cross_entropy(const void* logits, int logits_bf16, int64_t ld, const in
                        int64_t rows, int classes, void* dlogits, float grad_scale, float* loss_out,
                        void* scratch, void* stream);
 
+/* Same computation and same results as b200_cross_entropy, for callers that
+ * must not allocate.  (No counterpart in the reference: it has no native code
+ * and no allocation-free path; this exists for embedders of this library.)
+ *
+ * Meant for code that lives inside another component's memory budget — a plugin
+ * in a serving process whose device memory is pre-partitioned, a latency-bound
+ * loop that cannot afford the device-wide stall of cudaMalloc/cudaFree, a plain
+ * C caller that holds only the tensors it was handed.  Those callers have nowhere
+ * to get the `scratch` buffer from, so the library carries one itself: a
+ * file-scope __device__ array of B200_CE_STATIC_BYTES that every GPU loading
+ * the library holds until the process exits.  The caller still passes all
+ * inputs and outputs.  The call performs no cudaMalloc/cudaFree and calls no
+ * allocating library routine.
+ *
+ * Limit: the array has B200_CE_STATIC_MAX_BLOCKS partial-sum slots, i.e. at
+ * most 8 * B200_CE_STATIC_MAX_BLOCKS rows when classes <= 2048 and at most
+ * B200_CE_STATIC_MAX_BLOCKS rows above that.  Larger problems are rejected
+ * with B200_ERR_INVALID and a message; use b200_cross_entropy for them.
+ *
+ * The first call on each device looks the array's device address up
+ * (cudaGetSymbolAddress, with that device current); make that first call
+ * before starting any stream capture.
+ *
+ * All calls on a device share the one array, and it keeps the previous call's
+ * contents; each call re-zeroes the word that has to start at zero (an async
+ * memset on `stream`) and overwrites the rest.  Two calls whose kernels can
+ * overlap on the GPU (different streams, no dependency) race on the array:
+ * serialise them. */
+#define B200_CE_STATIC_MAX_BLOCKS 1024
+#define B200_CE_STATIC_BYTES (16 + 8 * B200_CE_STATIC_MAX_BLOCKS)
+int b200_cross_entropy_static(const void* logits, int logits_bf16, int64_t ld,
+                              const int64_t* targets, int64_t rows, int classes, void* dlogits,
+                              float grad_scale, float* loss_out, void* stream);
+
 /* ---------------------------------------------------------------- GEMM
  * D[M,N] = epilogue(A[M,K] * B[N,K]^T) on tcgen05 tensor cores: operands staged
  * by TMA into 128B-swizzled shared memory, fp32 accumulators in TMEM (double
