@@ -59,6 +59,18 @@ def declare(L: C.CDLL) -> None:
     L.b200_stage_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                    C.c_int64, C.c_void_p]
     L.b200_stage_batch.restype = C.c_int
+    L.b200_layernorm_fwd.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p]
+    L.b200_layernorm_bwd.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                     C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
+    L.b200_colsum.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_void_p, C.c_int,
+                              C.c_void_p, C.c_void_p]
+    for name in ("b200_layernorm_bwd_scratch_bytes", "b200_colsum_scratch_bytes"):
+        getattr(L, name).argtypes = [C.c_int64, C.c_int]
+        getattr(L, name).restype = C.c_int64
+    for name in ("b200_layernorm_fwd", "b200_layernorm_bwd", "b200_colsum"):
+        getattr(L, name).restype = C.c_int
     for name in ("b200_device_info", "b200_optimizer_step", "b200_cross_entropy", "b200_gemm",
                  "b200_cast_f32_to_bf16", "b200_cast_bf16_to_f32"):
         getattr(L, name).restype = C.c_int

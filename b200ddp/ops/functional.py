@@ -1,0 +1,341 @@
+"""Autograd faces of the sm_100a kernels, used by the transformer model.
+
+Each function has two paths: on a B200 with bf16 tensors it runs our kernels
+(``csrc/gemm.cu``, ``norm.cu``, ``loss.cu``) through custom ``autograd.Function``s;
+anywhere else (CPU plumbing, fp32) it runs the equivalent torch ops, so models
+built on it work under ``--backend gloo`` too.
+
+Gradient routing: when the engine has placed a parameter in its flat arenas it
+tags it with ``_b200_grad`` (bf16/fp32 view of the gradient arena),
+``_b200_master`` (fp32 master view) and ``_b200_ready`` (bucket bookkeeping).
+Backward then writes weight/bias gradients **straight into the arena** from the
+wgrad GEMM / column-sum kernel — no ``.grad`` tensor, no accumulate pass — and
+signals the bucket, which launches its fused all-reduce+optimizer kernel while
+backward is still running.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+from .. import _native as nat
+
+_scratch = {}
+
+
+def _B():
+    from .._native import bindings
+    return bindings
+
+
+def native_ok(*tensors: torch.Tensor) -> bool:
+    return all(t.is_cuda and t.dtype == torch.bfloat16 for t in tensors) and nat.available()
+
+
+def _scratch_buf(device, nbytes: int) -> torch.Tensor:
+    key = (torch.device(device).index, "s")
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = _scratch[key] = torch.empty(max(nbytes, 16 << 20), dtype=torch.uint8, device=device)
+    return buf
+
+
+def _bias_f32(b: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    if b is None:
+        return None
+    m = getattr(b, "_b200_master", None)
+    return m if m is not None else b.float()
+
+
+def _colsum_into(x2: torch.Tensor, out: torch.Tensor) -> None:
+    L = nat.lib()
+    rows, cols = x2.shape
+    sc = _scratch_buf(x2.device, int(L.b200_colsum_scratch_bytes(rows, cols)))
+    nat.check(L.b200_colsum(x2.data_ptr(), x2.stride(0), rows, cols, out.data_ptr(),
+                            int(out.dtype == torch.bfloat16), sc.data_ptr(),
+                            nat.stream_ptr(x2.device)), "b200_colsum")
+
+
+def _emit_param_grad(p: torch.Tensor, compute_into, signal: bool = True):
+    """Runs compute_into(dst) with dst = the arena view when the engine owns p (returns None so
+    autograd does not accumulate), else into a fresh tensor that is returned to autograd."""
+    dst = getattr(p, "_b200_grad", None)
+    if dst is not None:
+        compute_into(dst)
+        if signal:
+            p._b200_ready()
+        return None
+    g = torch.empty_like(p)
+    compute_into(g)
+    return g
+
+
+def _wgrad_into(dy2: torch.Tensor, x2: torch.Tensor, dst: torch.Tensor) -> None:
+    # dW[n_out, n_in] = dy^T @ x : both operands read MN-major, nothing is transposed
+    n_out, n_in = dst.shape
+    _B().gemm(dy2, x2, dst, M=n_out, N=n_in, K=x2.shape[0], a_mn_major=True, b_mn_major=True)
+
+
+# ------------------------------------------------------------------ linear (+bias, +residual)
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b, residual):
+        B = _B()
+        K = w.shape[1]
+        x2 = x.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        M, N = x2.shape[0], w.shape[0]
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
+        r2 = residual.reshape(M, N) if residual is not None else None
+        B.gemm(x2, w, out, M=M, N=N, K=K, bias=_bias_f32(b), epilogue=B.EPI_NONE, aux=r2)
+        ctx.save_for_backward(x2)
+        ctx.w, ctx.b, ctx.has_res = w, b, residual is not None
+        ctx.x_shape = x.shape
+        return out.view(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        B = _B()
+        (x2,) = ctx.saved_tensors
+        w, b = ctx.w, ctx.b
+        N, K = w.shape
+        dy2 = dy.reshape(-1, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        M = dy2.shape[0]
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(M, K, dtype=torch.bfloat16, device=dy.device)
+            B.gemm(dy2, w, dx, M=M, N=K, K=N, b_mn_major=True)  # W stored [N_out, K_in] = [K, N]
+            dx = dx.view(ctx.x_shape)
+        gw = _emit_param_grad(w, lambda dst: _wgrad_into(dy2, x2, dst))
+        gb = _emit_param_grad(b, lambda dst: _colsum_into(dy2, dst)) if b is not None else None
+        return dx, gw, gb, (dy if ctx.has_res else None)
+
+
+def linear(x, w, b=None, residual=None):
+    if native_ok(x, w):
+        return _Linear.apply(x, w, b, residual)
+    y = F.linear(x, w, b)
+    return y + residual if residual is not None else y
+
+
+# ------------------------------------------------------------------ transformer MLP block
+class _MLP(torch.autograd.Function):
+    """y = gelu(x Wfc^T + bfc) Wproj^T + bproj + residual, GELU and its backward gate fused
+    into GEMM epilogues (the pre-activation is written by the first GEMM's epilogue)."""
+
+    @staticmethod
+    def forward(ctx, x, w_fc, b_fc, w_proj, b_proj, residual):
+        B = _B()
+        C_in = w_fc.shape[1]
+        x2 = x.reshape(-1, C_in)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        M, H, C_out = x2.shape[0], w_fc.shape[0], w_proj.shape[0]
+        z = torch.empty(M, H, dtype=torch.bfloat16, device=x.device)
+        h = torch.empty(M, H, dtype=torch.bfloat16, device=x.device)
+        B.gemm(x2, w_fc, h, M=M, N=H, K=C_in, bias=_bias_f32(b_fc), epilogue=B.EPI_GELU, aux_out=z)
+        y = torch.empty(M, C_out, dtype=torch.bfloat16, device=x.device)
+        r2 = residual.reshape(M, C_out) if residual is not None else None
+        B.gemm(h, w_proj, y, M=M, N=C_out, K=H, bias=_bias_f32(b_proj), epilogue=B.EPI_NONE, aux=r2)
+        ctx.save_for_backward(x2, z, h)
+        ctx.params = (w_fc, b_fc, w_proj, b_proj)
+        ctx.has_res = residual is not None
+        ctx.x_shape = x.shape
+        return y.view(*x.shape[:-1], C_out)
+
+    @staticmethod
+    def backward(ctx, dy):
+        B = _B()
+        x2, z, h = ctx.saved_tensors
+        w_fc, b_fc, w_proj, b_proj = ctx.params
+        H, C_in = w_fc.shape
+        C_out = w_proj.shape[0]
+        dy2 = dy.reshape(-1, C_out)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        M = dy2.shape[0]
+        # dz = (dy @ Wproj) * gelu'(z): dgrad GEMM with the gate in its epilogue
+        dz = torch.empty(M, H, dtype=torch.bfloat16, device=dy.device)
+        B.gemm(dy2, w_proj, dz, M=M, N=H, K=C_out, b_mn_major=True, epilogue=B.EPI_GELU_BWD, aux=z)
+        g_wp = _emit_param_grad(w_proj, lambda dst: _wgrad_into(dy2, h, dst))
+        g_bp = _emit_param_grad(b_proj, lambda dst: _colsum_into(dy2, dst))
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(M, C_in, dtype=torch.bfloat16, device=dy.device)
+            B.gemm(dz, w_fc, dx, M=M, N=C_in, K=H, b_mn_major=True)
+            dx = dx.view(ctx.x_shape)
+        g_wf = _emit_param_grad(w_fc, lambda dst: _wgrad_into(dz, x2, dst))
+        g_bf = _emit_param_grad(b_fc, lambda dst: _colsum_into(dz, dst))
+        return dx, g_wf, g_bf, g_wp, g_bp, (dy if ctx.has_res else None)
+
+
+def mlp(x, w_fc, b_fc, w_proj, b_proj, residual=None):
+    if native_ok(x, w_fc, w_proj):
+        return _MLP.apply(x, w_fc, b_fc, w_proj, b_proj, residual)
+    y = F.linear(F.gelu(F.linear(x, w_fc, b_fc), approximate="tanh"), w_proj, b_proj)
+    return y + residual if residual is not None else y
+
+
+# ------------------------------------------------------------------ layer norm
+class _LayerNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        L = nat.lib()
+        Cc = x.shape[-1]
+        x2 = x.reshape(-1, Cc)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        rows = x2.shape[0]
+        y = torch.empty_like(x2)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        nat.check(L.b200_layernorm_fwd(x2.data_ptr(), gamma.data_ptr(), beta.data_ptr(), y.data_ptr(),
+                                       mean.data_ptr(), rstd.data_ptr(), rows, Cc, eps,
+                                       nat.stream_ptr(x.device)), "b200_layernorm_fwd")
+        ctx.save_for_backward(x2, mean, rstd)
+        ctx.gamma, ctx.beta = gamma, beta
+        ctx.x_shape = x.shape
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = nat.lib()
+        x2, mean, rstd = ctx.saved_tensors
+        gamma, beta = ctx.gamma, ctx.beta
+        rows, Cc = x2.shape
+        dy2 = dy.reshape(rows, Cc)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx = torch.empty_like(x2)
+        sc = _scratch_buf(dy.device, int(L.b200_layernorm_bwd_scratch_bytes(rows, Cc)))
+        gdst = getattr(gamma, "_b200_grad", None)
+        bdst = getattr(beta, "_b200_grad", None)
+        owned = gdst is not None and bdst is not None
+        if not owned:
+            gdst, bdst = torch.empty_like(gamma), torch.empty_like(beta)
+        assert gdst.dtype == bdst.dtype
+        nat.check(L.b200_layernorm_bwd(dy2.data_ptr(), x2.data_ptr(), gamma.data_ptr(), mean.data_ptr(),
+                                       rstd.data_ptr(), dx.data_ptr(), None, gdst.data_ptr(),
+                                       bdst.data_ptr(), int(gdst.dtype == torch.bfloat16), rows, Cc,
+                                       sc.data_ptr(), nat.stream_ptr(dy.device)), "b200_layernorm_bwd")
+        if owned:
+            gamma._b200_ready()
+            beta._b200_ready()
+            return dx.view(ctx.x_shape), None, None, None
+        return dx.view(ctx.x_shape), gdst, bdst, None
+
+
+def layer_norm(x, gamma, beta, eps: float = 1e-5):
+    Cc = x.shape[-1]
+    if native_ok(x, gamma, beta) and Cc % 256 == 0 and 256 <= Cc <= 2048:
+        return _LayerNorm.apply(x, gamma, beta, eps)
+    return F.layer_norm(x, (Cc,), gamma, beta, eps)
+
+
+# ------------------------------------------------------------------ tied LM head + cross entropy
+class _LMHeadCE(torch.autograd.Function):
+    """loss = mean CE(x @ W^T, targets).  Logits live once, in bf16; the CE kernel overwrites
+    them with dlogits; dgrad and wgrad read that buffer (MN-major for wgrad)."""
+
+    @staticmethod
+    def forward(ctx, x, w, targets, signal_weight):
+        B = _B()
+        Cc = w.shape[1]
+        V = w.shape[0]
+        x2 = x.reshape(-1, Cc)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        M = x2.shape[0]
+        ld = (V + 7) // 8 * 8
+        logits = torch.empty(M, ld, dtype=torch.bfloat16, device=x.device)
+        B.gemm(x2, w, logits, M=M, N=V, K=Cc)
+        out = torch.empty(2, dtype=torch.float32, device=x.device)
+        lg = logits[:, :V]
+        B.cross_entropy(lg, targets.reshape(-1).contiguous(), lg, 1.0 / M, out)
+        ctx.save_for_backward(x2, logits)
+        ctx.w, ctx.V, ctx.signal = w, V, signal_weight
+        ctx.x_shape = x.shape
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, gout):
+        B = _B()
+        x2, dlogits = ctx.saved_tensors
+        w, V = ctx.w, ctx.V
+        M, Cc = x2.shape
+        dl = dlogits[:, :V]
+        dx = torch.empty(M, Cc, dtype=torch.bfloat16, device=x2.device)
+        B.gemm(dl, w, dx, M=M, N=Cc, K=V, b_mn_major=True)
+        gw = _emit_param_grad(w, lambda dst: _wgrad_into(dl, x2, dst), signal=ctx.signal)
+        # the kernels assume the loss is the root of backward (seed 1.0); honour other seeds
+        dx = dx.view(ctx.x_shape) * gout.to(dx.dtype)
+        if gw is not None:
+            gw = gw * gout.to(gw.dtype)
+        return dx, gw, None, None
+
+
+def lm_head_cross_entropy(x, w, targets, signal_weight: bool = True):
+    """Mean token cross-entropy of the (tied) LM head.  `signal_weight=False` when `w` receives
+    another gradient contribution later in backward (tied embedding)."""
+    if native_ok(x, w):
+        return _LMHeadCE.apply(x, w, targets, signal_weight)
+    logits = F.linear(x, w).float()
+    return F.cross_entropy(logits.view(-1, logits.shape[-1]), targets.reshape(-1))
+
+
+# ------------------------------------------------------------------ embedding (tied with the head)
+class _Embedding(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, idx, wte, wpe):
+        Bsz, T = idx.shape
+        x = wte[idx] + wpe[:T].unsqueeze(0)
+        ctx.save_for_backward(idx)
+        ctx.wte, ctx.wpe = wte, wpe
+        return x
+
+    @staticmethod
+    def backward(ctx, dx):
+        (idx,) = ctx.saved_tensors
+        wte, wpe = ctx.wte, ctx.wpe
+        Bsz, T = idx.shape
+        Cc = dx.shape[-1]
+
+        def wte_grad(dst):  # accumulates on top of the LM-head contribution already in the arena
+            dst.index_add_(0, idx.reshape(-1), dx.reshape(-1, Cc).to(dst.dtype))
+
+        def wpe_grad(dst):
+            dst.zero_()
+            dst[:T] = dx.float().sum(0).to(dst.dtype)
+
+        owned = getattr(wte, "_b200_grad", None) is not None
+        if owned:
+            g_wte = _emit_param_grad(wte, wte_grad)
+        else:
+            g_wte = torch.zeros_like(wte)
+            wte_grad(g_wte)
+        g_wpe = _emit_param_grad(wpe, wpe_grad)
+        return None, g_wte, g_wpe
+
+
+def embedding(idx, wte, wpe):
+    if native_ok(wte, wpe):
+        return _Embedding.apply(idx, wte, wpe)
+    T = idx.shape[1]
+    return F.embedding(idx, wte) + wpe[:T].unsqueeze(0)
+
+
+# ------------------------------------------------------------------ attention
+def causal_attention(qkv: torch.Tensor, n_head: int) -> torch.Tensor:
+    """qkv [B, T, 3C] -> [B, T, C].  Round 1 uses torch's fused SDPA (flash-attention
+    library kernel) for the softmax(QK^T)V core; the four GEMMs around it are ours."""
+    Bsz, T, C3 = qkv.shape
+    Cc = C3 // 3
+    q, k, v = qkv.view(Bsz, T, 3, n_head, Cc // n_head).permute(2, 0, 3, 1, 4)
+    y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+    return y.transpose(1, 2).reshape(Bsz, T, Cc)

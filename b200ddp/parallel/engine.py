@@ -157,7 +157,15 @@ class DataParallel(nn.Module):
         self.comm_max_blocks = 64
         self._comm_stream = torch.cuda.Stream(self.device) if self.is_cuda else None
         for p, slot in zip(self._params, self.layout.slots):
-            p.register_post_accumulate_grad_hook(self._make_hook(slot.bucket))
+            hook = self._make_hook(slot.bucket)
+            p.register_post_accumulate_grad_hook(hook)
+            if self.is_cuda:
+                # lets the native autograd ops write gradients straight into the arena
+                # (ops/functional.py) and signal the bucket themselves
+                sl = slice(slot.offset, slot.offset + slot.numel)
+                p._b200_grad = self.grad[sl].view(slot.shape)
+                p._b200_master = self.master[sl].view(slot.shape)
+                p._b200_ready = (lambda h=hook, q=p: h(q))
 
         # ---- fused step program (SimpleNet-class MLPs on a B200) ---------------------
         self.program = None
@@ -230,8 +238,11 @@ class DataParallel(nn.Module):
         self.module.train()
         self.zero_grad()
         self.begin_backward()
-        out = self(data)
-        loss = self.loss_fn(out.float(), target)
+        if getattr(self.module, "fused_loss", False):
+            loss = self(data, target)
+        else:
+            out = self(data)
+            loss = self.loss_fn(out.float(), target)
         loss.backward()
         self.finish_step()
         return loss.detach()
@@ -242,6 +253,8 @@ class DataParallel(nn.Module):
             return self.program.eval_step(data, target)
         with torch.no_grad():
             out = self(data).float()
+            if out.dim() > 2:  # token models: [B, T, V] vs [B, T]
+                out, target = out.reshape(-1, out.shape[-1]), target.reshape(-1)
             loss = self.loss_fn(out, target)
             correct = out.argmax(dim=1).eq(target).sum()
         return loss, correct

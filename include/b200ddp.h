@@ -163,6 +163,26 @@ int b200_cast_bf16_to_f32(const void* src, float* dst, int64_t n, void* stream);
 int b200_stage_batch(const float* x, const int64_t* y, void* x_bf16, int64_t* y_out, int64_t nx,
                      int64_t ny, void* stream);
 
+/* ---------------------------------------------------------------- normalisation / reductions
+ * For the transformer configuration (BASELINE.json config 4).  ref: not in the
+ * reference's own model; its GPT-2 baseline uses ATen native_layer_norm(+backward)
+ * and sum().  All tensors bf16 unless noted; cols must be a multiple of 256 in
+ * [256, 2048] for LayerNorm.  mean/rstd are fp32 [rows], saved for backward.
+ * layernorm_bwd: dx = LN'(dy) (+ dx_add when non-null: the residual-stream
+ * gradient joins in the same pass); dgamma/dbeta [cols] bf16 (grads_bf16) or
+ * fp32, reduced deterministically through `scratch`
+ * (b200_layernorm_bwd_scratch_bytes).  b200_colsum: out[c] = sum_r x[r, c]
+ * (bias gradient), scratch of b200_colsum_scratch_bytes. */
+int b200_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean,
+                       float* rstd, int64_t rows, int cols, float eps, void* stream);
+int64_t b200_layernorm_bwd_scratch_bytes(int64_t rows, int cols);
+int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean,
+                       const float* rstd, void* dx, const void* dx_add, void* dgamma, void* dbeta,
+                       int grads_bf16, int64_t rows, int cols, void* scratch, void* stream);
+int64_t b200_colsum_scratch_bytes(int64_t rows, int cols);
+int b200_colsum(const void* x, int64_t ld, int64_t rows, int cols, void* out, int out_bf16,
+                void* scratch, void* stream);
+
 /* ---------------------------------------------------------------- peer-memory collectives
  * Symmetric allocation: every rank allocates the same size and exchanges the
  * 64-byte CUDA IPC handle through the process group (the only host-side
