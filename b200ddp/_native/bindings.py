@@ -57,7 +57,7 @@ def declare(L: C.CDLL) -> None:
     L.b200_cast_f32_to_bf16.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     L.b200_cast_bf16_to_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     L.b200_stage_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
-                                   C.c_int64, C.c_void_p]
+                                   C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     L.b200_stage_batch.restype = C.c_int
     L.b200_layernorm_fwd.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p]
@@ -182,7 +182,20 @@ def cast_f32_to_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
                                       stream_ptr(src.device)), "b200_cast_f32_to_bf16")
 
 
-def stage_batch(x: torch.Tensor, y: torch.Tensor, x_bf16: torch.Tensor, y_out: torch.Tensor) -> None:
+def make_zero_list(tensors):
+    """(ptr array, count array, n) for stage_batch's zero regions; build once, reuse."""
+    n = len(tensors)
+    ptrs = (C.c_void_p * max(n, 1))(*[t.data_ptr() for t in tensors])
+    counts = (C.c_int * max(n, 1))(*[t.numel() for t in tensors])
+    for t in tensors:
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    return ptrs, counts, n
+
+
+def stage_batch(x: torch.Tensor, y: torch.Tensor, x_bf16: torch.Tensor, y_out: torch.Tensor,
+                zero_list=None) -> None:
     assert x.dtype == torch.float32 and x.is_contiguous() and y.dtype == torch.int64
+    ptrs, counts, n = zero_list if zero_list is not None else (None, None, 0)
     check(lib().b200_stage_batch(x.data_ptr(), y.data_ptr(), x_bf16.data_ptr(), y_out.data_ptr(),
-                                 x.numel(), y.numel(), stream_ptr(x.device)), "b200_stage_batch")
+                                 x.numel(), y.numel(), ptrs, counts, n, stream_ptr(x.device)),
+          "b200_stage_batch")

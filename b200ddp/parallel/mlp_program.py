@@ -5,7 +5,8 @@ copies, one all-reduce and 1-2 host syncs per step for ~77 MFLOP of math
 (SURVEY §2.5).  Here the whole step is a fixed schedule of sm_100a kernels that
 is captured once per batch size into a CUDA graph and replayed:
 
-    stage      x fp32 -> bf16, labels -> fixed buffer             (1 launch, outside the graph)
+    stage      x fp32 -> bf16, labels -> fixed buffer, clear the atomically
+               accumulated words (bias grads, loss)               (1 launch, outside the graph)
     forward    3 tcgen05 GEMMs; epilogues fuse bias+ReLU+dropout; the last one
                fuses softmax cross-entropy forward AND backward (dlogits), the
                bias-3 gradient and the loss/accuracy reduction
@@ -42,6 +43,9 @@ class _Buffers:
         self.dlogits = torch.zeros(bsz, self.ncls_ld, dtype=bf, device=dev)
         self.dz = [torch.zeros(bsz, d, dtype=bf, device=dev) for d in dims[1:-1]]
         self.loss = torch.zeros(2, dtype=torch.float32, device=dev)
+        # fp32 words the step adds into with atomics; the staging kernel clears them
+        self.zero_train = B.make_zero_list([l["gb"] for l in prog.layers] + [self.loss])
+        self.zero_eval = B.make_zero_list([self.loss])
         self.train_graph: torch.cuda.CUDAGraph | None = None
         self.eval_graph: torch.cuda.CUDAGraph | None = None
 
@@ -135,14 +139,13 @@ class MLPProgram:
                                  advance=(k == nb - 1))
 
     def _train_body(self, bufs: _Buffers) -> None:
-        self.engine.grad.zero_()  # bias gradients accumulate with atomics; weights overwrite
-        bufs.loss.zero_()
+        # no memsets: weight gradients are overwritten by the wgrad epilogues, the bias
+        # gradients and the loss accumulator were cleared by the staging kernel
         self._forward(bufs, True)
         self._backward(bufs)
         self._update()
 
     def _eval_body(self, bufs: _Buffers) -> None:
-        bufs.loss.zero_()
         self._forward(bufs, False)
 
     def _capture(self, body, bufs: _Buffers) -> torch.cuda.CUDAGraph:
@@ -162,13 +165,15 @@ class MLPProgram:
         return b
 
     # ------------------------------------------------------------------ public
-    def _stage(self, bufs: _Buffers, data: torch.Tensor, target: torch.Tensor) -> None:
+    def _stage(self, bufs: _Buffers, data: torch.Tensor, target: torch.Tensor,
+               train: bool = True) -> None:
         x = data.reshape(data.shape[0], -1)
         if x.dtype != torch.float32 or not x.is_contiguous():
             x = x.float().contiguous()
         if x.shape[1] != self.dims[0]:
             raise ValueError(f"expected {self.dims[0]} features, got {x.shape[1]}")
-        B.stage_batch(x, target.contiguous(), bufs.x, bufs.y)
+        B.stage_batch(x, target.contiguous(), bufs.x, bufs.y,
+                      bufs.zero_train if train else bufs.zero_eval)
 
     def train_step(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         bufs = self._get(int(data.shape[0]))
@@ -180,7 +185,7 @@ class MLPProgram:
 
     def eval_step(self, data: torch.Tensor, target: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
         bufs = self._get(int(data.shape[0]))
-        self._stage(bufs, data, target)
+        self._stage(bufs, data, target, train=False)
         if bufs.eval_graph is None:
             bufs.eval_graph = self._capture(self._eval_body, bufs)
         bufs.eval_graph.replay()
@@ -190,6 +195,7 @@ class MLPProgram:
     def logits(self, data: torch.Tensor) -> torch.Tensor:
         """Eval-mode logits [B, classes] fp32 (uncaptured; for tests and ad-hoc inference)."""
         bufs = self._get(int(data.shape[0]))
-        self._stage(bufs, data, torch.zeros(data.shape[0], dtype=torch.int64, device=self.device))
+        self._stage(bufs, data, torch.zeros(data.shape[0], dtype=torch.int64, device=self.device),
+                    train=False)
         self._eval_body(bufs)
         return bufs.dlogits[:, : self.dims[-1]].float()

@@ -27,8 +27,9 @@ from .._native.bindings_comm import FLAG_WORDS, MAX_RANKS, Comm
 _DT = {torch.float32: ("<f4", 4), torch.bfloat16: ("<u2", 2), torch.int32: ("<i4", 4),
        torch.uint8: ("|u1", 1)}
 
-# Buckets at or below this many bytes use the one-shot kernel (latency path);
-# larger ones use two-shot (bandwidth path).  Overridable for the sweep.
+# One-shot makes every rank pull the whole bucket from its W-1 peers; it is used while that
+# remote traffic, bucket_bytes * (W - 1), stays at or below this many bytes (latency path).
+# Larger buckets use two-shot (bandwidth path).  Overridable for the sweep.
 ONE_SHOT_MAX_BYTES = int(os.environ.get("B200DDP_ONE_SHOT_MAX_BYTES", 2 * 1024 * 1024))
 
 
@@ -60,6 +61,7 @@ class SymmetricArena:
         self.flags_local, self.flags_peers = self._alloc_raw(FLAG_WORDS * 4)
         self.timeout_ms = int(os.environ.get("B200DDP_PEER_TIMEOUT_MS", "30000"))
         self.two_shot_buckets = set()
+        self.vec_elems = 4
         self._comm_cache: Dict = {}
 
     def _alloc_raw(self, nbytes: int):
@@ -102,13 +104,14 @@ class SymmetricArena:
     # ------------------------------------------------------------------ engine hooks
     def shard_ranges(self, b) -> List[tuple]:
         """Element ranges [lo, hi) each rank owns in a two-shot bucket (mirrors comm.cu)."""
-        lo4, hi4 = b.start // 4, (b.start + b.numel) // 4
-        per = ((hi4 - lo4 + self.world - 1) // self.world + 15) // 16 * 16
+        w = self.vec_elems
+        lo, hi = b.start // w, (b.start + b.numel) // w
+        per = ((hi - lo + self.world - 1) // self.world + 15) // 16 * 16
         out = []
         for r in range(self.world):
-            s = lo4 + per * r
-            e = min(s + per, hi4)
-            out.append((4 * s, 4 * max(s, e)))
+            s = lo + per * r
+            e = min(s + per, hi)
+            out.append((w * s, w * max(s, e)))
         return out
 
     def launch_bucket(self, engine, b, scale: float, *, step_host: int = 0,
@@ -120,7 +123,8 @@ class SymmetricArena:
         wire_bf16 = engine.grad.dtype == torch.bfloat16
         esize = 2 if wire_bf16 else 4
         algo = 1 if (can_push and engine.allow_two_shot
-                     and b.numel * esize > ONE_SHOT_MAX_BYTES) else 0
+                     and b.numel * esize * (self.world - 1) > ONE_SHOT_MAX_BYTES) else 0
+        self.vec_elems = 8 if wire_bf16 else 4  # one 16-byte vector of the wire dtype
         if algo == 1:
             self.two_shot_buckets.add(b.index)
         key = (id(engine), can_push)

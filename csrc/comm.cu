@@ -50,63 +50,66 @@ struct CommArgs {
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
     uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
-    float4 v;
-    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+__device__ __forceinline__ uint4 ld_peer_16(const void* p) {
+    uint4 v;
+    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                  : "l"(p));
     return v;
 }
-__device__ __forceinline__ uint2 ld_peer_u2(const void* p) {
-    uint2 v;
-    asm volatile("ld.global.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
-    return v;
-}
 
+// Polls with relaxed loads (cheap: the flag lives in local memory) and fences once on
+// success; bounded so a dead peer traps instead of hanging the GPU.
 __device__ __forceinline__ void spin_until(const uint32_t* flag, uint32_t epoch, uint64_t timeout_ns,
                                            int who) {
-    const uint64_t t0 = globaltimer_ns();
-    while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {
-        if (globaltimer_ns() - t0 > timeout_ns) {
-            printf("b200ddp: peer flag wait timed out (waiting on rank %d, epoch %u, block %d)\n", who,
-                   epoch, (int)blockIdx.x);
-            __trap();
+    if ((int32_t)(ld_relaxed_sys(flag) - epoch) < 0) {
+        const uint64_t t0 = globaltimer_ns();
+        while ((int32_t)(ld_relaxed_sys(flag) - epoch) < 0) {
+            if (globaltimer_ns() - t0 > timeout_ns) {
+                printf("b200ddp: peer flag wait timed out (waiting on rank %d, epoch %u, block %d)\n",
+                       who, epoch, (int)blockIdx.x);
+                __trap();
+            }
         }
     }
+    fence_acq_rel_sys();
 }
 
 // All blocks: wait until every rank has published `epoch` in our ready flags.
-// Block 0 first publishes ours to every rank.
+// Block 0 first publishes ours to every rank.  The gradients being announced were
+// written by earlier kernels of this stream, so they are already visible at the
+// point of coherence; the release store orders the announcement after them.
 __device__ __forceinline__ void begin_barrier(const CommArgs& a, uint32_t epoch) {
-    if (blockIdx.x == 0 && threadIdx.x < a.world) {
-        __threadfence_system();
+    if (blockIdx.x == 0 && threadIdx.x < a.world)
         st_release_sys(a.flags[threadIdx.x] + F_READY + a.rank, epoch);
-    }
     if (threadIdx.x < a.world)
         spin_until(a.flags[a.rank] + F_READY + threadIdx.x, epoch, a.timeout_ns, threadIdx.x);
     __syncthreads();
 }
 
 // The last block to finish tells every rank we are done reading/pushing, waits
-// for the same from everyone, then advances the local epoch.
+// for the same from everyone, then advances the local epoch.  One thread per block
+// fences after the CTA barrier (cumulative over the block's remote stores).
+template <bool REMOTE_WRITES>
 __device__ __forceinline__ void end_barrier(const CommArgs& a, uint32_t epoch, int* step_dev, int new_step) {
     __shared__ int s_last;
-    __threadfence_system();
     __syncthreads();
     uint32_t* mine = a.flags[a.rank];
     if (threadIdx.x == 0) {
+        if (REMOTE_WRITES) fence_acq_rel_sys(); else __threadfence();
         const unsigned t = atomicAdd(mine + F_TICKET, 1u);
         s_last = (t == gridDim.x - 1);
     }
     __syncthreads();
     if (!s_last) return;
     if (threadIdx.x < a.world) {
-        __threadfence_system();
+        if (REMOTE_WRITES) fence_acq_rel_sys();
         st_release_sys(a.flags[threadIdx.x] + F_DONE + a.rank, epoch);
         spin_until(mine + F_DONE + threadIdx.x, epoch, a.timeout_ns, threadIdx.x);
     }
@@ -119,38 +122,64 @@ __device__ __forceinline__ void end_barrier(const CommArgs& a, uint32_t epoch, i
     }
 }
 
+// One "vector" is 16 bytes of gradient: 4 fp32 or 8 bf16 elements.
+template <bool BF16> struct Vec { static constexpr int N = BF16 ? 8 : 4; };
+
 template <bool BF16>
-__device__ __forceinline__ float4 load_grad4(const void* base, int64_t i4) {
-    if (BF16) {
-        const uint2 raw = ld_peer_u2(reinterpret_cast<const uint2*>(base) + i4);
-        const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
-        const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
-        return make_float4(a.x, a.y, b.x, b.y);
+__device__ __forceinline__ void unpack(const uint4& raw, float (&f)[Vec<BF16>::N]) {
+    if constexpr (BF16) {
+        const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[q]));
+            f[2 * q] = t.x;
+            f[2 * q + 1] = t.y;
+        }
+    } else {
+        f[0] = __uint_as_float(raw.x); f[1] = __uint_as_float(raw.y);
+        f[2] = __uint_as_float(raw.z); f[3] = __uint_as_float(raw.w);
     }
-    return ld_peer_f4(reinterpret_cast<const float*>(base) + 4 * i4);
 }
 
-// Fixed-order sum over ranks of 4 consecutive elements at vector index i4.
+// Fixed-order (rank 0..W-1) fp32 sum of vector i across all ranks' arenas.
 template <bool BF16>
-__device__ __forceinline__ float4 reduce4(const CommArgs& a, int64_t i4) {
-    float4 v[MAX_RANKS];
+__device__ __forceinline__ void reduce_vec(const CommArgs& a, int64_t i, float (&s)[Vec<BF16>::N]) {
+    constexpr int N = Vec<BF16>::N;
+    uint4 raw[MAX_RANKS];
 #pragma unroll
     for (int j = 0; j < MAX_RANKS; ++j)
-        if (j < a.world) v[j] = load_grad4<BF16>(a.grad[j], i4);  // all loads in flight first
-    float4 s = v[0];
+        if (j < a.world) raw[j] = ld_peer_16(reinterpret_cast<const uint4*>(a.grad[j]) + i);  // all in flight
+    unpack<BF16>(raw[0], s);
 #pragma unroll
     for (int j = 1; j < MAX_RANKS; ++j)
-        if (j < a.world) { s.x += v[j].x; s.y += v[j].y; s.z += v[j].z; s.w += v[j].w; }
-    return s;
+        if (j < a.world) {
+            float t[N];
+            unpack<BF16>(raw[j], t);
+#pragma unroll
+            for (int k = 0; k < N; ++k) s[k] += t[k];
+        }
+}
+
+// Range of vectors this rank handles: the whole bucket (one-shot) or its shard (two-shot).
+template <int ALGO>
+__device__ __forceinline__ void my_range(const CommArgs& a, int64_t lo, int64_t hi, int64_t& mlo, int64_t& mhi) {
+    mlo = lo; mhi = hi;
+    if (ALGO == 1) {
+        const int64_t per = (((hi - lo) + a.world - 1) / a.world + 15) & ~int64_t(15);
+        mlo = lo + per * a.rank;
+        const int64_t e = mlo + per;
+        mhi = e < hi ? e : hi;
+    }
 }
 
 // algo 0: one-shot, full replica update.  algo 1: two-shot, shard update + parameter push.
-// [start, start+n) is the bucket, in elements; start and n are multiples of 4.
+// [start, start+n) is the bucket, in elements; start and n are multiples of the vector width.
 template <bool BF16, int ALGO, bool PUSH_BF16>
 __global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
     const CommArgs a, b200_opt_hparams hp, int64_t start, int64_t n, float* __restrict__ master,
     float* __restrict__ m, float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, int* step_dev,
     int step_host, int advance) {
+    constexpr int N = Vec<BF16>::N;
     __shared__ OptScalars sc;
     const uint32_t epoch = *(volatile uint32_t*)(a.flags[a.rank] + F_EPOCH) + 1u;
     if (threadIdx.x == 0) {
@@ -160,51 +189,60 @@ __global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
     begin_barrier(a, epoch);  // includes __syncthreads
     const OptScalars s = sc;
 
-    int64_t lo4 = start >> 2, hi4 = (start + n) >> 2;
-    if (ALGO == 1) {
-        const int64_t per = (((hi4 - lo4) + a.world - 1) / a.world + 15) & ~int64_t(15);
-        lo4 = lo4 + per * a.rank;
-        const int64_t e = lo4 + per;
-        hi4 = e < hi4 ? e : hi4;
-    }
+    int64_t lo, hi;
+    my_range<ALGO>(a, start / N, (start + n) / N, lo, hi);
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = lo4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi4; i += stride) {
-        float4 g = reduce4<BF16>(a, i);
-        float4 pp = reinterpret_cast<float4*>(master)[i];
-        float4 mm = reinterpret_cast<float4*>(m)[i];
-        float4 vv = make_float4(0, 0, 0, 0);
-        if (hp.kind != 2) vv = reinterpret_cast<float4*>(v)[i];
-        opt_update(hp.kind, s, pp.x, mm.x, vv.x, g.x * hp.grad_scale);
-        opt_update(hp.kind, s, pp.y, mm.y, vv.y, g.y * hp.grad_scale);
-        opt_update(hp.kind, s, pp.z, mm.z, vv.z, g.z * hp.grad_scale);
-        opt_update(hp.kind, s, pp.w, mm.w, vv.w, g.w * hp.grad_scale);
-        reinterpret_cast<float4*>(m)[i] = mm;
-        if (hp.kind != 2) reinterpret_cast<float4*>(v)[i] = vv;
+    for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+        float g[N];
+        reduce_vec<BF16>(a, i, g);
+        float pp[N], mm[N], vv[N];
+#pragma unroll
+        for (int q = 0; q < N / 4; ++q) {
+            const float4 p4 = reinterpret_cast<const float4*>(master)[i * (N / 4) + q];
+            const float4 m4 = reinterpret_cast<const float4*>(m)[i * (N / 4) + q];
+            float4 v4 = make_float4(0, 0, 0, 0);
+            if (hp.kind != 2) v4 = reinterpret_cast<const float4*>(v)[i * (N / 4) + q];
+            pp[4 * q] = p4.x; pp[4 * q + 1] = p4.y; pp[4 * q + 2] = p4.z; pp[4 * q + 3] = p4.w;
+            mm[4 * q] = m4.x; mm[4 * q + 1] = m4.y; mm[4 * q + 2] = m4.z; mm[4 * q + 3] = m4.w;
+            vv[4 * q] = v4.x; vv[4 * q + 1] = v4.y; vv[4 * q + 2] = v4.z; vv[4 * q + 3] = v4.w;
+        }
+#pragma unroll
+        for (int k = 0; k < N; ++k) opt_update(hp.kind, s, pp[k], mm[k], vv[k], g[k] * hp.grad_scale);
+#pragma unroll
+        for (int q = 0; q < N / 4; ++q) {
+            reinterpret_cast<float4*>(m)[i * (N / 4) + q] = make_float4(mm[4 * q], mm[4 * q + 1], mm[4 * q + 2], mm[4 * q + 3]);
+            if (hp.kind != 2)
+                reinterpret_cast<float4*>(v)[i * (N / 4) + q] = make_float4(vv[4 * q], vv[4 * q + 1], vv[4 * q + 2], vv[4 * q + 3]);
+            // fp32 master: local in every mode (two-shot fp32 push overwrites it below, same value)
+            reinterpret_cast<float4*>(master)[i * (N / 4) + q] = make_float4(pp[4 * q], pp[4 * q + 1], pp[4 * q + 2], pp[4 * q + 3]);
+        }
+        uint32_t packed[N / 2];
+#pragma unroll
+        for (int k = 0; k < N / 2; ++k) packed[k] = pack_bf16(pp[2 * k], pp[2 * k + 1]);
         if (ALGO == 0) {
-            reinterpret_cast<float4*>(master)[i] = pp;
             if (shadow) {
-                uint2 o;
-                o.x = pack_bf16(pp.x, pp.y);
-                o.y = pack_bf16(pp.z, pp.w);
-                reinterpret_cast<uint2*>(shadow)[i] = o;
+                if constexpr (N == 8) reinterpret_cast<uint4*>(shadow)[i] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+                else reinterpret_cast<uint2*>(shadow)[i] = make_uint2(packed[0], packed[1]);
             }
+        } else if (PUSH_BF16) {
+#pragma unroll
+            for (int j = 0; j < MAX_RANKS; ++j)
+                if (j < a.world) {
+                    if constexpr (N == 8) reinterpret_cast<uint4*>(a.push[j])[i] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+                    else reinterpret_cast<uint2*>(a.push[j])[i] = make_uint2(packed[0], packed[1]);
+                }
         } else {
-            if (PUSH_BF16) {
-                reinterpret_cast<float4*>(master)[i] = pp;  // owner keeps the fp32 shard
-                uint2 o;
-                o.x = pack_bf16(pp.x, pp.y);
-                o.y = pack_bf16(pp.z, pp.w);
 #pragma unroll
-                for (int j = 0; j < MAX_RANKS; ++j)
-                    if (j < a.world) reinterpret_cast<uint2*>(a.push[j])[i] = o;
-            } else {
+            for (int j = 0; j < MAX_RANKS; ++j)
+                if (j < a.world && j != a.rank) {
 #pragma unroll
-                for (int j = 0; j < MAX_RANKS; ++j)
-                    if (j < a.world) reinterpret_cast<float4*>(a.push[j])[i] = pp;
-            }
+                    for (int q = 0; q < N / 4; ++q)
+                        reinterpret_cast<float4*>(a.push[j])[i * (N / 4) + q] =
+                            make_float4(pp[4 * q], pp[4 * q + 1], pp[4 * q + 2], pp[4 * q + 3]);
+                }
         }
     }
-    end_barrier(a, epoch, advance ? step_dev : nullptr, s.t);
+    end_barrier<ALGO == 1>(a, epoch, advance ? step_dev : nullptr, s.t);
 }
 
 // Plain all-reduce (sum * scale), for the bandwidth sweep and generic use.
@@ -212,39 +250,31 @@ __global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
 template <bool BF16, int ALGO>
 __global__ void __launch_bounds__(256) allreduce_kernel(const CommArgs a, int64_t start, int64_t n,
                                                         void* __restrict__ out, float scale) {
+    constexpr int N = Vec<BF16>::N;
     const uint32_t epoch = *(volatile uint32_t*)(a.flags[a.rank] + F_EPOCH) + 1u;
     begin_barrier(a, epoch);
-    int64_t lo4 = start >> 2, hi4 = (start + n) >> 2;
-    if (ALGO == 1) {
-        const int64_t per = (((hi4 - lo4) + a.world - 1) / a.world + 15) & ~int64_t(15);
-        lo4 = lo4 + per * a.rank;
-        const int64_t e = lo4 + per;
-        hi4 = e < hi4 ? e : hi4;
-    }
+    int64_t lo, hi;
+    my_range<ALGO>(a, start / N, (start + n) / N, lo, hi);
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = lo4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi4; i += stride) {
-        float4 g = reduce4<BF16>(a, i);
-        g.x *= scale; g.y *= scale; g.z *= scale; g.w *= scale;
-        if (BF16) {
-            uint2 o;
-            o.x = pack_bf16(g.x, g.y);
-            o.y = pack_bf16(g.z, g.w);
-            if (ALGO == 0) reinterpret_cast<uint2*>(out)[i] = o;
-            else {
-#pragma unroll
-                for (int j = 0; j < MAX_RANKS; ++j)
-                    if (j < a.world) reinterpret_cast<uint2*>(const_cast<void*>(a.grad[j]))[i] = o;
-            }
+    for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+        float g[N];
+        reduce_vec<BF16>(a, i, g);
+        uint4 o;
+        if constexpr (BF16) {
+            o = make_uint4(pack_bf16(g[0] * scale, g[1] * scale), pack_bf16(g[2] * scale, g[3] * scale),
+                           pack_bf16(g[4] * scale, g[5] * scale), pack_bf16(g[6] * scale, g[7] * scale));
         } else {
-            if (ALGO == 0) reinterpret_cast<float4*>(out)[i] = g;
-            else {
+            o = make_uint4(__float_as_uint(g[0] * scale), __float_as_uint(g[1] * scale),
+                           __float_as_uint(g[2] * scale), __float_as_uint(g[3] * scale));
+        }
+        if (ALGO == 0) reinterpret_cast<uint4*>(out)[i] = o;
+        else {
 #pragma unroll
-                for (int j = 0; j < MAX_RANKS; ++j)
-                    if (j < a.world) reinterpret_cast<float4*>(const_cast<void*>(a.grad[j]))[i] = g;
-            }
+            for (int j = 0; j < MAX_RANKS; ++j)
+                if (j < a.world) reinterpret_cast<uint4*>(const_cast<void*>(a.grad[j]))[i] = o;
         }
     }
-    end_barrier(a, epoch, nullptr, 0);
+    end_barrier<ALGO == 1>(a, epoch, nullptr, 0);
 }
 
 static int fill_args(const b200_comm* c, CommArgs* a) {
@@ -313,10 +343,11 @@ extern "C" int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200
     if (rc) return rc;
     B200_REQUIRE(hp && master && exp_avg, "allreduce_optimizer: null pointer");
     B200_REQUIRE(algo == 0 || algo == 1, "allreduce_optimizer: unknown algo %d", algo);
-    B200_REQUIRE((start % 4) == 0 && (n % 4) == 0 && n > 0, "allreduce_optimizer: start/n must be multiples of 4");
+    B200_REQUIRE((start % 8) == 0 && (n % 8) == 0 && n > 0, "allreduce_optimizer: start/n must be multiples of 8");
     if (algo == 1)
         for (int j = 0; j < c->world; ++j) B200_REQUIRE(a.push[j], "allreduce_optimizer: two-shot needs push pointers");
-    const int64_t vecs = (algo == 1 ? (n / 4 + c->world - 1) / c->world : n / 4);
+    const int64_t nv = n / (grad_is_bf16 ? 8 : 4);
+    const int64_t vecs = (algo == 1 ? (nv + c->world - 1) / c->world : nv);
     const int blocks = grid_for(vecs, c->max_blocks > 0 ? c->max_blocks : 296);
     cudaStream_t s = (cudaStream_t)stream;
 #define GO(BF, AL, PB)                                                                             \
@@ -339,9 +370,10 @@ extern "C" int b200_allreduce(const b200_comm* c, int algo, int64_t start, int64
     int rc = fill_args(c, &a);
     if (rc) return rc;
     B200_REQUIRE(algo == 0 || algo == 1, "allreduce: unknown algo %d", algo);
-    B200_REQUIRE((start % 4) == 0 && (n % 4) == 0 && n > 0, "allreduce: start/n must be multiples of 4");
+    B200_REQUIRE((start % 8) == 0 && (n % 8) == 0 && n > 0, "allreduce: start/n must be multiples of 8");
     B200_REQUIRE(algo == 1 || out, "allreduce: one-shot needs an output buffer");
-    const int64_t vecs = (algo == 1 ? (n / 4 + c->world - 1) / c->world : n / 4);
+    const int64_t nv = n / (is_bf16 ? 8 : 4);
+    const int64_t vecs = (algo == 1 ? (nv + c->world - 1) / c->world : nv);
     const int blocks = grid_for(vecs, c->max_blocks > 0 ? c->max_blocks : 296);
     cudaStream_t s = (cudaStream_t)stream;
     if (is_bf16) {

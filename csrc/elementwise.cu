@@ -33,12 +33,23 @@ __global__ void __launch_bounds__(256) cast_bf16_f32(const __nv_bfloat16* __rest
 
 // Batch staging for the captured step program: cast the fp32 features to bf16 and copy
 // the int64 labels into the graph's fixed input buffers, in one launch.
+// It also zeroes the few fp32 words the step accumulates into with atomics (bias
+// gradients, loss) so the captured graph needs no memset nodes.
+struct ZeroList {
+    float* ptr[B200_STAGE_MAX_ZERO];
+    int count[B200_STAGE_MAX_ZERO];
+    int n;
+};
+
 __global__ void __launch_bounds__(256) stage_batch(const float* __restrict__ x,
                                                    const int64_t* __restrict__ y,
                                                    __nv_bfloat16* __restrict__ xo,
-                                                   int64_t* __restrict__ yo, int64_t nx, int64_t ny) {
+                                                   int64_t* __restrict__ yo, int64_t nx, int64_t ny,
+                                                   const ZeroList zl) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (int r = 0; r < zl.n; ++r)
+        for (int64_t i = tid; i < zl.count[r]; i += stride) zl.ptr[r][i] = 0.f;
     const int64_t n4 = nx >> 2;
     for (int64_t i = tid; i < n4; i += stride) {
         const float4 a = reinterpret_cast<const float4*>(x)[i];
@@ -82,11 +93,16 @@ extern "C" int b200_cast_bf16_to_f32(const void* src, float* dst, int64_t n, voi
 }
 
 extern "C" int b200_stage_batch(const float* x, const int64_t* y, void* x_bf16, int64_t* y_out,
-                                int64_t nx, int64_t ny, void* stream) {
+                                int64_t nx, int64_t ny, float* const* zero_ptrs,
+                                const int* zero_counts, int nzero, void* stream) {
     B200_REQUIRE(x && y && x_bf16 && y_out && nx >= 0 && ny >= 0, "stage_batch: bad arguments");
+    B200_REQUIRE(nzero >= 0 && nzero <= B200_STAGE_MAX_ZERO, "stage_batch: at most %d zero regions", B200_STAGE_MAX_ZERO);
+    b200::ZeroList zl{};
+    zl.n = nzero;
+    for (int r = 0; r < nzero; ++r) { zl.ptr[r] = zero_ptrs[r]; zl.count[r] = zero_counts[r]; }
     B200_REQUIRE(((uintptr_t)x % 16 == 0) && ((uintptr_t)x_bf16 % 8 == 0), "stage_batch: x must be 16-byte aligned");
     b200::stage_batch<<<b200::grid_for(nx / 4), 256, 0, (cudaStream_t)stream>>>(
-        x, y, (__nv_bfloat16*)x_bf16, y_out, nx, ny);
+        x, y, (__nv_bfloat16*)x_bf16, y_out, nx, ny, zl);
     b200_count_launch(1);
     B200_CUDA_OK(cudaGetLastError());
     return 0;

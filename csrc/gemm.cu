@@ -26,6 +26,7 @@
 // Ragged edges in M, N and K are zero-filled by TMA; stores are masked.
 #include "common.cuh"
 
+#include <cstdlib>
 #include <mutex>
 
 void b200_count_launch(int n);
@@ -256,12 +257,27 @@ __device__ __forceinline__ void epilogue_ce(const GemmParams& p, int row, bool r
 
 template <int NC>
 __device__ __forceinline__ void colsum_chunk(const GemmParams& p, bool row_ok, int n, const float (&f)[NC]) {
-    // Sum over the warp's 32 rows, one atomic per column per warp.
+    // Sum over the warp's 32 rows with a transposing butterfly: NC-1 shuffles instead of
+    // 5*NC, after which lane L holds the total of column L; then ONE coalesced atomic
+    // instruction per warp.
+    const int lane = threadIdx.x & 31;
+    float v[NC];
 #pragma unroll
-    for (int j = 0; j < NC; ++j) {
-        const float s = warp_sum(row_ok ? f[j] : 0.f);
-        if ((threadIdx.x & 31) == 0 && n + j < p.N) atomicAdd(p.colsum + n + j, s);
+    for (int j = 0; j < NC; ++j) v[j] = row_ok ? f[j] : 0.f;
+#pragma unroll
+    for (int o = NC / 2; o >= 1; o >>= 1) {
+        const bool upper = (lane & o) != 0;
+#pragma unroll
+        for (int k = 0; k < o; ++k) {
+            const float send = upper ? v[k] : v[k + o];
+            const float keep = upper ? v[k + o] : v[k];
+            v[k] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
     }
+#pragma unroll
+    for (int o = NC; o < 32; o <<= 1) v[0] += __shfl_xor_sync(0xffffffffu, v[0], o);
+    const int col = lane % NC;
+    if (lane < NC && n + col < p.N) atomicAdd(p.colsum + n + col, v[0]);
 }
 
 template <int BN>
@@ -287,6 +303,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tma_a);
@@ -309,6 +326,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // Everything above touched only shared memory, TMEM and kernel parameters.  From here
+    // on we read what earlier kernels wrote: wait for them (no-op without PDL).
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -457,7 +477,21 @@ static int make_map(CUtensorMap* map, const void* base, int64_t inner, int64_t o
 template <int BN>
 static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int ctas, cudaStream_t s) {
     constexpr uint32_t smem = gemm_smem_bytes<BN>();
-    gemm_kernel<BN><<<ctas, GEMM_THREADS, smem, s>>>(ma, mb, p);
+    // Programmatic dependent launch: the next GEMM's prologue (barrier init, TMEM
+    // allocation, descriptor prefetch) overlaps this one's tail; every global access in
+    // the kernel sits behind griddepcontrol.wait.  B200DDP_NO_PDL=1 disables it.
+    static const bool pdl = getenv("B200DDP_NO_PDL") == nullptr;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)ctas);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel<BN>, ma, mb, p));
     b200_count_launch(1);
     B200_CUDA_OK(cudaGetLastError());
     return 0;

@@ -160,8 +160,13 @@ int b200_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream);
 int b200_cast_bf16_to_f32(const void* src, float* dst, int64_t n, void* stream);
 /* Stage one batch into the captured step program's fixed input buffers: features
  * fp32 -> bf16 and labels copied, one launch.  ref: train.py:133. */
+#define B200_STAGE_MAX_ZERO 8
+/* zero_ptrs/zero_counts (host arrays, nzero <= B200_STAGE_MAX_ZERO): fp32 regions the same
+ * launch clears — the bias-gradient slots and the loss accumulator that the step's GEMM
+ * epilogues add into with atomics — so the captured step graph carries no memset nodes. */
 int b200_stage_batch(const float* x, const int64_t* y, void* x_bf16, int64_t* y_out, int64_t nx,
-                     int64_t ny, void* stream);
+                     int64_t ny, float* const* zero_ptrs, const int* zero_counts, int nzero,
+                     void* stream);
 
 /* ---------------------------------------------------------------- normalisation / reductions
  * For the transformer configuration (BASELINE.json config 4).  ref: not in the
@@ -207,7 +212,7 @@ typedef struct {
 } b200_comm;
 #define B200_COMM_FLAG_WORDS (2 * B200_MAX_RANKS + 2)
 
-/* One bucket [start, start+n) (elements, multiples of 4) of the gradient arena:
+/* One bucket [start, start+n) (elements, multiples of 8) of the gradient arena:
  * all-reduce over peer memory, scale by hp->grad_scale, optimizer update, all in
  * one kernel.  ref: train.py:138 (DDP hook all-reduce + divide) and :139
  * (optimizer.step).  algo 0 = one-shot (every rank updates its full replica),
