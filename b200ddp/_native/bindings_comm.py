@@ -11,6 +11,7 @@ class Comm(C.Structure):
     _fields_ = [("rank", C.c_int), ("world", C.c_int),
                 ("grad", C.c_void_p * MAX_RANKS), ("push", C.c_void_p * MAX_RANKS),
                 ("flags", C.c_void_p * MAX_RANKS),
+                ("grad_mc", C.c_void_p), ("push_mc", C.c_void_p),
                 ("timeout_ms", C.c_int), ("max_blocks", C.c_int)]
 
 

@@ -99,6 +99,9 @@ def main():
         if nbytes <= (32 << 20):
             t_one = time_it(lambda i: arena.allreduce_(buf, (i % slots) * n, n, algo=0, scale=1.0, out=out), iters)
         t_two = time_it(lambda i: arena.allreduce_(buf, (i % slots) * n, n, algo=1, scale=1.0 / world), iters)
+        t_nvls = None
+        if arena.nvls:
+            t_nvls = time_it(lambda i: arena.allreduce_(buf, (i % slots) * n, n, algo=2, scale=1.0 / world), iters)
 
         # fused: gradient bucket of n elements -> Adam on the owner's shard -> bf16 parameter push
         t_fused = None
@@ -114,7 +117,7 @@ def main():
 
             def fused(i):
                 nat.check(arena.L.b200_allreduce_optimizer(
-                    C.byref(c), 1, C.byref(hp), 0, n, int(dtype == torch.bfloat16), master.data_ptr(),
+                    C.byref(c), 2 if (arena.nvls and world > 2) else 1, C.byref(hp), 0, n, int(dtype == torch.bfloat16), master.data_ptr(),
                     m.data_ptr(), v.data_ptr(), shadow.data_ptr(), 1, None, 10 + i, 0,
                     nat.stream_ptr(dev)), "fused")
             t_fused = time_it(fused, iters)
@@ -124,7 +127,9 @@ def main():
         roof_ar = 2 * nbytes * f / (LINK_GBS * 1e9) * 1e3          # ms, two-shot traffic per direction
         roof_fused = max((nbytes * f + n * 2 * f) / (LINK_GBS * 1e9), (n / world) * 28 / (hbm * 1e9)) * 1e3
         row = {"bytes": nbytes, "dtype": args.dtype, "world": world,
-               "nccl_ms": t_nccl, "oneshot_ms": t_one, "twoshot_ms": t_two, "fused_adam_ms": t_fused,
+               "nccl_ms": t_nccl, "oneshot_ms": t_one, "twoshot_ms": t_two, "nvls_ms": t_nvls,
+               "nvls_busbw_gbs": (nbytes * 2 * f / t_nvls / 1e6) if t_nvls else None,
+               "fused_adam_ms": t_fused, "fused_algo": "nvls" if (arena.nvls and world > 2) else "two-shot",
                "nccl_busbw_gbs": nbytes * 2 * f / t_nccl / 1e6,
                "twoshot_busbw_gbs": nbytes * 2 * f / t_two / 1e6,
                "oneshot_busbw_gbs": (nbytes * 2 * f / t_one / 1e6) if t_one else None,
@@ -135,9 +140,11 @@ def main():
         if rank == 0:
             one = f"{t_one * 1e3:9.1f}" if t_one else "        -"
             fu = f"{t_fused * 1e3:9.1f} ({row['fused_roofline_frac']:.2f})" if t_fused else "        -"
+            nv = f"{t_nvls * 1e3:9.1f} ({row['nvls_busbw_gbs']:6.1f} GB/s)" if t_nvls else "        -"
             print(f"{nbytes:>11d} B  nccl {t_nccl * 1e3:9.1f} us  one-shot {one} us  two-shot "
                   f"{t_two * 1e3:9.1f} us ({row['twoshot_busbw_gbs']:6.1f} GB/s bus, "
-                  f"{row['twoshot_roofline_frac']:.2f} of link roofline)  fused+adam {fu} us", flush=True)
+                  f"{row['twoshot_roofline_frac']:.2f} of link roofline)  nvls {nv} us  "
+                  f"fused+adam[{row['fused_algo']}] {fu} us", flush=True)
         del buf, out, nccl_bufs
         torch.cuda.empty_cache()
     if rank == 0 and args.out:

@@ -22,6 +22,12 @@
 // stores / acquire loads at .sys scope, and a bounded spin: a dead peer raises
 // a trap on the survivors instead of wedging seven GPUs.
 //
+//   NVLS      (algo 2, when the arenas are bound to an NVSwitch multicast object)  same
+//             sharding as two-shot, but the reduce-scatter is ONE multimem.ld_reduce per
+//             vector (summed in the switch) and the parameter all-gather ONE multimem.st
+//             (replicated by the switch): link traffic per rank drops from
+//             2 S (W-1)/W to about S/W + S_param/W.
+//
 // Also here: the symmetric allocator (cudaMalloc + CUDA IPC handles exchanged by
 // the Python process group) and a plain in-kernel all-reduce for benchmarking.
 #include "common.cuh"
@@ -44,6 +50,8 @@ struct CommArgs {
     const void* grad[MAX_RANKS];  // peer-mapped gradient arenas (same layout on every rank)
     void* push[MAX_RANKS];        // peer-mapped parameter arenas written by two-shot (or null)
     uint32_t* flags[MAX_RANKS];   // peer-mapped flag blocks
+    const void* grad_mc;          // NVLS: multicast address of the gradient arenas (or null)
+    void* push_mc;                // NVLS: multicast address of the parameter arenas (or null)
     uint64_t timeout_ns;
 };
 
@@ -160,11 +168,43 @@ __device__ __forceinline__ void reduce_vec(const CommArgs& a, int64_t i, float (
         }
 }
 
+// NVLS: one load returns the sum over every rank's copy, reduced inside the NVSwitch
+// (fp32 accumulation for bf16 inputs).  The address is the multicast mapping of the arenas.
+template <bool BF16>
+__device__ __forceinline__ void reduce_vec_mc(const void* mc_base, int64_t i, float (&s)[Vec<BF16>::N]) {
+    const uint4* p = reinterpret_cast<const uint4*>(mc_base) + i;
+    if constexpr (BF16) {
+        uint4 raw;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(raw.x), "=r"(raw.y), "=r"(raw.z), "=r"(raw.w)
+                     : "l"(p)
+                     : "memory");
+        unpack<true>(raw, s);
+    } else {
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(s[0]), "=f"(s[1]), "=f"(s[2]), "=f"(s[3])
+                     : "l"(p)
+                     : "memory");
+    }
+}
+// NVLS: one store lands in every rank's copy (the switch replicates it).
+__device__ __forceinline__ void st_mc_16(void* p, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p),
+                 "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)),
+                 "f"(__uint_as_float(v.w))
+                 : "memory");
+}
+__device__ __forceinline__ void st_mc_8(void* p, const uint2& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(p),
+                 "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y))
+                 : "memory");
+}
+
 // Range of vectors this rank handles: the whole bucket (one-shot) or its shard (two-shot).
 template <int ALGO>
 __device__ __forceinline__ void my_range(const CommArgs& a, int64_t lo, int64_t hi, int64_t& mlo, int64_t& mhi) {
     mlo = lo; mhi = hi;
-    if (ALGO == 1) {
+    if (ALGO >= 1) {
         const int64_t per = (((hi - lo) + a.world - 1) / a.world + 15) & ~int64_t(15);
         mlo = lo + per * a.rank;
         const int64_t e = mlo + per;
@@ -194,7 +234,8 @@ __global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
         float g[N];
-        reduce_vec<BF16>(a, i, g);
+        if (ALGO == 2) reduce_vec_mc<BF16>(a.grad_mc, i, g);
+        else reduce_vec<BF16>(a, i, g);
         float pp[N], mm[N], vv[N];
 #pragma unroll
         for (int q = 0; q < N / 4; ++q) {
@@ -224,6 +265,17 @@ __global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
                 if constexpr (N == 8) reinterpret_cast<uint4*>(shadow)[i] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
                 else reinterpret_cast<uint2*>(shadow)[i] = make_uint2(packed[0], packed[1]);
             }
+        } else if (ALGO == 2) {
+            if (PUSH_BF16) {
+                if constexpr (N == 8) st_mc_16(reinterpret_cast<uint4*>(a.push_mc) + i, make_uint4(packed[0], packed[1], packed[2], packed[3]));
+                else st_mc_8(reinterpret_cast<uint2*>(a.push_mc) + i, make_uint2(packed[0], packed[1]));
+            } else {
+#pragma unroll
+                for (int q = 0; q < N / 4; ++q)
+                    st_mc_16(reinterpret_cast<uint4*>(a.push_mc) + i * (N / 4) + q,
+                             make_uint4(__float_as_uint(pp[4 * q]), __float_as_uint(pp[4 * q + 1]),
+                                        __float_as_uint(pp[4 * q + 2]), __float_as_uint(pp[4 * q + 3])));
+            }
         } else if (PUSH_BF16) {
 #pragma unroll
             for (int j = 0; j < MAX_RANKS; ++j)
@@ -242,7 +294,7 @@ __global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
                 }
         }
     }
-    end_barrier<ALGO == 1>(a, epoch, advance ? step_dev : nullptr, s.t);
+    end_barrier<ALGO >= 1>(a, epoch, advance ? step_dev : nullptr, s.t);
 }
 
 // Plain all-reduce (sum * scale), for the bandwidth sweep and generic use.
@@ -258,7 +310,8 @@ __global__ void __launch_bounds__(256) allreduce_kernel(const CommArgs a, int64_
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
         float g[N];
-        reduce_vec<BF16>(a, i, g);
+        if (ALGO == 2) reduce_vec_mc<BF16>(a.grad_mc, i, g);
+        else reduce_vec<BF16>(a, i, g);
         uint4 o;
         if constexpr (BF16) {
             o = make_uint4(pack_bf16(g[0] * scale, g[1] * scale), pack_bf16(g[2] * scale, g[3] * scale),
@@ -268,13 +321,14 @@ __global__ void __launch_bounds__(256) allreduce_kernel(const CommArgs a, int64_
                            __float_as_uint(g[2] * scale), __float_as_uint(g[3] * scale));
         }
         if (ALGO == 0) reinterpret_cast<uint4*>(out)[i] = o;
+        else if (ALGO == 2) st_mc_16(reinterpret_cast<uint4*>(const_cast<void*>(a.grad_mc)) + i, o);
         else {
 #pragma unroll
             for (int j = 0; j < MAX_RANKS; ++j)
                 if (j < a.world) reinterpret_cast<uint4*>(const_cast<void*>(a.grad[j]))[i] = o;
         }
     }
-    end_barrier<ALGO == 1>(a, epoch, nullptr, 0);
+    end_barrier<ALGO >= 1>(a, epoch, nullptr, 0);
 }
 
 static int fill_args(const b200_comm* c, CommArgs* a) {
@@ -288,6 +342,8 @@ static int fill_args(const b200_comm* c, CommArgs* a) {
         a->flags[j] = j < c->world ? (uint32_t*)c->flags[j] : nullptr;
         if (j < c->world) B200_REQUIRE(a->grad[j] && a->flags[j], "comm: missing peer pointer for rank %d", j);
     }
+    a->grad_mc = c->grad_mc;
+    a->push_mc = c->push_mc;
     a->timeout_ns = c->timeout_ms > 0 ? (uint64_t)c->timeout_ms * 1000000ull : 30000000000ull;
     return 0;
 }
@@ -342,12 +398,13 @@ extern "C" int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200
     int rc = fill_args(c, &a);
     if (rc) return rc;
     B200_REQUIRE(hp && master && exp_avg, "allreduce_optimizer: null pointer");
-    B200_REQUIRE(algo == 0 || algo == 1, "allreduce_optimizer: unknown algo %d", algo);
+    B200_REQUIRE(algo >= 0 && algo <= 2, "allreduce_optimizer: unknown algo %d", algo);
+    B200_REQUIRE(algo != 2 || (c->grad_mc && c->push_mc), "allreduce_optimizer: NVLS needs multicast addresses");
     B200_REQUIRE((start % 8) == 0 && (n % 8) == 0 && n > 0, "allreduce_optimizer: start/n must be multiples of 8");
     if (algo == 1)
         for (int j = 0; j < c->world; ++j) B200_REQUIRE(a.push[j], "allreduce_optimizer: two-shot needs push pointers");
     const int64_t nv = n / (grad_is_bf16 ? 8 : 4);
-    const int64_t vecs = (algo == 1 ? (nv + c->world - 1) / c->world : nv);
+    const int64_t vecs = (algo >= 1 ? (nv + c->world - 1) / c->world : nv);
     const int blocks = grid_for(vecs, c->max_blocks > 0 ? c->max_blocks : 296);
     cudaStream_t s = (cudaStream_t)stream;
 #define GO(BF, AL, PB)                                                                             \
@@ -355,6 +412,10 @@ extern "C" int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200
         a, *hp, start, n, master, exp_avg, exp_avg_sq, (__nv_bfloat16*)shadow_bf16, step_dev,      \
         step_host, advance)
     if (algo == 0) { if (grad_is_bf16) GO(true, 0, false); else GO(false, 0, false); }
+    else if (algo == 2) {
+        if (push_is_bf16) { if (grad_is_bf16) GO(true, 2, true); else GO(false, 2, true); }
+        else { if (grad_is_bf16) GO(true, 2, false); else GO(false, 2, false); }
+    }
     else if (push_is_bf16) { if (grad_is_bf16) GO(true, 1, true); else GO(false, 1, true); }
     else { if (grad_is_bf16) GO(true, 1, false); else GO(false, 1, false); }
 #undef GO
@@ -369,19 +430,22 @@ extern "C" int b200_allreduce(const b200_comm* c, int algo, int64_t start, int64
     CommArgs a;
     int rc = fill_args(c, &a);
     if (rc) return rc;
-    B200_REQUIRE(algo == 0 || algo == 1, "allreduce: unknown algo %d", algo);
+    B200_REQUIRE(algo >= 0 && algo <= 2, "allreduce: unknown algo %d", algo);
+    B200_REQUIRE(algo != 2 || c->grad_mc, "allreduce: NVLS needs the multicast address");
     B200_REQUIRE((start % 8) == 0 && (n % 8) == 0 && n > 0, "allreduce: start/n must be multiples of 8");
-    B200_REQUIRE(algo == 1 || out, "allreduce: one-shot needs an output buffer");
+    B200_REQUIRE(algo >= 1 || out, "allreduce: one-shot needs an output buffer");
     const int64_t nv = n / (is_bf16 ? 8 : 4);
-    const int64_t vecs = (algo == 1 ? (nv + c->world - 1) / c->world : nv);
+    const int64_t vecs = (algo >= 1 ? (nv + c->world - 1) / c->world : nv);
     const int blocks = grid_for(vecs, c->max_blocks > 0 ? c->max_blocks : 296);
     cudaStream_t s = (cudaStream_t)stream;
     if (is_bf16) {
         if (algo == 0) allreduce_kernel<true, 0><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
-        else allreduce_kernel<true, 1><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
+        else if (algo == 1) allreduce_kernel<true, 1><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
+        else allreduce_kernel<true, 2><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
     } else {
         if (algo == 0) allreduce_kernel<false, 0><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
-        else allreduce_kernel<false, 1><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
+        else if (algo == 1) allreduce_kernel<false, 1><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
+        else allreduce_kernel<false, 2><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
     }
     b200_count_launch(1);
     B200_CUDA_OK(cudaGetLastError());

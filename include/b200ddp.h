@@ -207,6 +207,8 @@ typedef struct {
     void* grad[B200_MAX_RANKS];  /* rank j's gradient arena as mapped in this process */
     void* push[B200_MAX_RANKS];  /* rank j's parameter arena (two-shot writes it) or null */
     void* flags[B200_MAX_RANKS]; /* rank j's flag block: (2*B200_MAX_RANKS+2) uint32, zero-initialised */
+    void* grad_mc;               /* NVLS multicast address of all gradient arenas, or null */
+    void* push_mc;               /* NVLS multicast address of all parameter arenas, or null */
     int timeout_ms;              /* spin bound before the kernel traps; 0 = 30 s */
     int max_blocks;              /* 0 = default */
 } b200_comm;
@@ -220,6 +222,8 @@ typedef struct {
  * writes the new parameters into every rank's `push` arena: bf16 when
  * push_is_bf16, else fp32).  master/exp_avg/exp_avg_sq/shadow are arena BASE
  * pointers (the kernel indexes them with the same element offsets as grad).
+ * algo 2 = NVLS: two-shot sharding with multimem.ld_reduce (in-switch reduction)
+ * and multimem.st (in-switch broadcast); needs grad_mc/push_mc.
  * Must be launched by every rank, in the same order, or peers time out. */
 int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200_opt_hparams* hp,
                              int64_t start, int64_t n, int grad_is_bf16, float* master,

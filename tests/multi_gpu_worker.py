@@ -30,7 +30,7 @@ def check_plain_allreduce(arena, rank, world, dev):
     for dtype in (torch.float32, torch.bfloat16):
         for n in (1024, 1 << 20, 12 * (1 << 20) + 64):
             buf = arena.alloc(n, dtype)
-            for algo in (0, 1):
+            for algo in (0, 1, 2) if arena.nvls else (0, 1):
                 torch.manual_seed(1000 * rank + n % 997 + algo)
                 src = torch.randn(n, device=dev).to(dtype)
                 buf.copy_(src)
@@ -49,7 +49,8 @@ def check_plain_allreduce(arena, rank, world, dev):
                 ref = got.clone(); dist.broadcast(ref, src=0)
                 assert torch.equal(ref, got), ("ranks differ", dtype, n, algo)
                 dist.barrier()
-    log("plain all-reduce: one-shot and two-shot match NCCL (fp32, bf16), ranks bit-identical")
+    log(f"plain all-reduce: one-shot, two-shot{' and NVLS multimem' if arena.nvls else ''} match NCCL "
+        f"(fp32, bf16), ranks bit-identical")
 
 
 def check_fused_optimizer(rank, world, dev, compute_dtype, two_shot, kind):
@@ -62,12 +63,16 @@ def check_fused_optimizer(rank, world, dev, compute_dtype, two_shot, kind):
     ref = DataParallel(copy.deepcopy(net), optimizer=kind, lr=1e-2, backend="nccl",
                        compute_dtype=compute_dtype, use_program=False)
     assert torch.equal(eng.master, ref.master)
+    nvls_bf16 = bool(two_shot and compute_dtype == torch.bfloat16 and eng.symm.nvls)
+    rtol, atol = (2e-3, 3e-4) if nvls_bf16 else (3e-6, 2e-6)
     for step in range(3):
         torch.manual_seed(77 * rank + step)
         g = torch.randn(eng.layout.total, device=dev)
         eng.grad.copy_(g); ref.grad.copy_(g)
         # reference: NCCL sum, then the torch-op update
         gsum = ref.grad.float().clone(); dist.all_reduce(gsum)
+        if nvls_bf16:  # the switch returns the fp32-accumulated sum rounded to bf16
+            gsum = gsum.to(torch.bfloat16).float()
         ref.grad.copy_(gsum) if ref.grad.dtype == torch.float32 else None
         ref.optimizer.step_count += 1
         if ref.grad.dtype == torch.float32:
@@ -82,8 +87,11 @@ def check_fused_optimizer(rank, world, dev, compute_dtype, two_shot, kind):
         torch.cuda.synchronize()
     eng.consolidate_state()
     torch.cuda.synchronize()
-    assert torch.allclose(eng.master, ref.master, rtol=3e-6, atol=2e-6), rel(eng.master, ref.master)
-    assert torch.allclose(eng.optimizer.exp_avg, ref.optimizer.exp_avg, rtol=3e-6, atol=2e-6)
+    assert torch.allclose(eng.master, ref.master, rtol=rtol, atol=atol), rel(eng.master, ref.master)
+    # in-switch bf16 reduction rounds more than one fp32 accumulation would (hardware property,
+    # same class of error as an NCCL bf16 all-reduce): the moments get a looser bound
+    assert torch.allclose(eng.optimizer.exp_avg, ref.optimizer.exp_avg, rtol=2e-2 if nvls_bf16 else rtol,
+                          atol=5e-3 if nvls_bf16 else atol)
     if eng.shadow is not None:
         assert torch.equal(eng.shadow, eng.master.to(torch.bfloat16))
     got = [torch.empty_like(eng.master) for _ in range(world)]
@@ -96,7 +104,8 @@ def check_fused_optimizer(rank, world, dev, compute_dtype, two_shot, kind):
     sd = eng.optimizer.state_dict()
     if kind != "sgd":
         assert float(sd["state"][0]["step"]) == 3.0
-    log(f"fused all-reduce+{kind}: {'two-shot' if two_shot else 'one-shot'} "
+    algo = ("NVLS" if eng.symm.nvls else "two-shot") if two_shot else "one-shot"
+    log(f"fused all-reduce+{kind}: {algo} "
         f"{str(compute_dtype).split('.')[-1]} matches NCCL + torch-op update; replicas identical")
 
 
@@ -111,6 +120,10 @@ def check_program(rank, world, dev):
     torch.cuda.synchronize()
     l0, l1 = losses[0].item(), losses[-1].item()
     assert l1 < 0.6 * l0, (l0, l1)
+    gs = [torch.empty_like(eng.shadow) for _ in range(world)]
+    dist.all_gather(gs, eng.shadow)
+    assert all(torch.equal(gs[0], t) for t in gs), "bf16 replicas diverged under the step program"
+    eng.consolidate_state()  # two-shot/NVLS buckets keep the fp32 master on the shard owner
     got = [torch.empty_like(eng.master) for _ in range(world)]
     dist.all_gather(got, eng.master)
     assert all(torch.equal(got[0], t) for t in got), "replicas diverged under the step program"
@@ -144,6 +157,7 @@ def main():
     dev = torch.device("cuda", local)
     assert nat.available()
     arena = SymmetricArena(dev, rank, world)
+    log(f"world {world}: NVLS multicast memory {'available' if arena.nvls else 'unavailable: ' + getattr(arena, '_nvls_error', 'disabled')}")
     check_plain_allreduce(arena, rank, world, dev)
     for kind in ("adam", "sgd"):
         for dtype in (torch.float32, torch.bfloat16):
