@@ -1,0 +1,95 @@
+"""ResNet-50 (BASELINE.json config 3: "ResNet-50 DDP on synthetic 224x224 batches").
+
+Not part of the reference repository; the comparator is torchvision's ``resnet50``
+under the reference's DDP loop.  Same architecture (v1.5: stride on
+the 3x3 convolution), same 25,557,032 parameters and the same state-dict keys as
+torchvision, so weights are interchangeable.
+
+What the framework contributes for this config: the flat parameter / gradient /
+buffer arenas, bucketed overlap with backward, the fused NVLS all-reduce +
+optimizer kernel per bucket, one coalesced buffer broadcast per step for the
+BatchNorm running statistics, bf16 compute with fp32 master
+weights, and the fused cross-entropy kernel.  Convolutions and BatchNorm run on
+cuDNN through torch in round 1, in channels-last bf16 (see DESIGN.md §9 for the
+implicit-GEMM plan on the tcgen05 GEMM).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class _BN(nn.BatchNorm2d):
+    """BatchNorm with fp32 statistics/affine math on bf16 activations (cuDNN mixed mode);
+    the affine parameters may live in a bf16 arena."""
+
+    def forward(self, x):
+        if self.training and self.track_running_stats and self.num_batches_tracked is not None:
+            self.num_batches_tracked.add_(1)
+        return F.batch_norm(x, self.running_mean, self.running_var, self.weight.float(),
+                            self.bias.float(), self.training, self.momentum, self.eps)
+
+
+class Bottleneck(nn.Module):
+    expansion = 4
+
+    def __init__(self, inplanes: int, planes: int, stride: int = 1, downsample: nn.Module | None = None):
+        super().__init__()
+        self.conv1 = nn.Conv2d(inplanes, planes, 1, bias=False)
+        self.bn1 = _BN(planes)
+        self.conv2 = nn.Conv2d(planes, planes, 3, stride=stride, padding=1, bias=False)
+        self.bn2 = _BN(planes)
+        self.conv3 = nn.Conv2d(planes, planes * 4, 1, bias=False)
+        self.bn3 = _BN(planes * 4)
+        self.downsample = downsample
+
+    def forward(self, x):
+        idt = x if self.downsample is None else self.downsample(x)
+        out = F.relu(self.bn1(self.conv1(x)), inplace=True)
+        out = F.relu(self.bn2(self.conv2(out)), inplace=True)
+        out = self.bn3(self.conv3(out))
+        return F.relu(out + idt, inplace=True)
+
+
+class ResNet50(nn.Module):
+    def __init__(self, num_classes: int = 1000):
+        super().__init__()
+        self.inplanes = 64
+        self.conv1 = nn.Conv2d(3, 64, 7, stride=2, padding=3, bias=False)
+        self.bn1 = _BN(64)
+        self.maxpool = nn.MaxPool2d(3, stride=2, padding=1)
+        self.layer1 = self._make_layer(64, 3)
+        self.layer2 = self._make_layer(128, 4, stride=2)
+        self.layer3 = self._make_layer(256, 6, stride=2)
+        self.layer4 = self._make_layer(512, 3, stride=2)
+        self.fc = nn.Linear(2048, num_classes)
+        for m in self.modules():
+            if isinstance(m, nn.Conv2d):
+                nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+
+    def _make_layer(self, planes: int, blocks: int, stride: int = 1) -> nn.Sequential:
+        down = None
+        if stride != 1 or self.inplanes != planes * 4:
+            down = nn.Sequential(nn.Conv2d(self.inplanes, planes * 4, 1, stride=stride, bias=False),
+                                 _BN(planes * 4))
+        layers = [Bottleneck(self.inplanes, planes, stride, down)]
+        self.inplanes = planes * 4
+        layers += [Bottleneck(self.inplanes, planes) for _ in range(1, blocks)]
+        return nn.Sequential(*layers)
+
+    def forward(self, x):
+        w = self.conv1.weight
+        if x.dtype != w.dtype:
+            x = x.to(w.dtype)
+        if x.is_cuda:
+            x = x.contiguous(memory_format=torch.channels_last)
+        x = self.maxpool(F.relu(self.bn1(self.conv1(x)), inplace=True))
+        x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
+        x = torch.flatten(F.adaptive_avg_pool2d(x, 1), 1)
+        from ..ops import functional as Fn
+        return Fn.linear(x, self.fc.weight, self.fc.bias)
+
+
+def resnet50(num_classes: int = 1000) -> ResNet50:
+    return ResNet50(num_classes)

@@ -117,8 +117,13 @@ class _Linear(torch.autograd.Function):
         return dx, gw, gb, (dy if ctx.has_res else None)
 
 
+def _tma_dims_ok(*ws: torch.Tensor) -> bool:
+    """Every weight dimension becomes a TMA row pitch in forward, dgrad or wgrad (16-byte rule)."""
+    return all(d % 8 == 0 for w in ws for d in w.shape)
+
+
 def linear(x, w, b=None, residual=None):
-    if native_ok(x, w):
+    if native_ok(x, w) and _tma_dims_ok(w):
         return _Linear.apply(x, w, b, residual)
     y = F.linear(x, w, b)
     return y + residual if residual is not None else y
@@ -176,7 +181,7 @@ class _MLP(torch.autograd.Function):
 
 
 def mlp(x, w_fc, b_fc, w_proj, b_proj, residual=None):
-    if native_ok(x, w_fc, w_proj):
+    if native_ok(x, w_fc, w_proj) and _tma_dims_ok(w_fc, w_proj):
         return _MLP.apply(x, w_fc, b_fc, w_proj, b_proj, residual)
     y = F.linear(F.gelu(F.linear(x, w_fc, b_fc), approximate="tanh"), w_proj, b_proj)
     return y + residual if residual is not None else y
@@ -339,3 +344,30 @@ def causal_attention(qkv: torch.Tensor, n_head: int) -> torch.Tensor:
     q, k, v = qkv.view(Bsz, T, 3, n_head, Cc // n_head).permute(2, 0, 3, 1, 4)
     y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
     return y.transpose(1, 2).reshape(Bsz, T, Cc)
+
+
+# ------------------------------------------------------------------ stand-alone cross entropy
+class _CrossEntropy(torch.autograd.Function):
+    """Mean CE over rows with our fused kernel: the forward pass already produces dlogits."""
+
+    @staticmethod
+    def forward(ctx, logits, targets):
+        lg = logits if logits.stride(-1) == 1 else logits.contiguous()
+        dl = torch.empty_like(lg)
+        out = torch.empty(2, dtype=torch.float32, device=lg.device)
+        _B().cross_entropy(lg, targets.contiguous(), dl, 1.0 / lg.shape[0], out)
+        ctx.save_for_backward(dl)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, gout):
+        (dl,) = ctx.saved_tensors
+        return dl * gout.to(dl.dtype), None
+
+
+def cross_entropy(logits, targets):
+    """F.cross_entropy(mean) for [rows, classes] logits; fused fwd+bwd kernel on a B200."""
+    if (logits.is_cuda and logits.dim() == 2 and logits.dtype in (torch.bfloat16, torch.float32)
+            and targets.dtype == torch.int64 and nat.available()):
+        return _CrossEntropy.apply(logits, targets)
+    return F.cross_entropy(logits.float(), targets)

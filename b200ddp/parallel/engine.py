@@ -96,7 +96,9 @@ class DataParallel(nn.Module):
         self.wire_dtype = wire_dtype
         want_program = want_program and wire_dtype == torch.float32
         self.broadcast_buffers = broadcast_buffers
-        self.loss_fn = loss_fn or F.cross_entropy
+        if loss_fn is None:
+            from ..ops.functional import cross_entropy as loss_fn  # fused kernel on CUDA, torch on CPU
+        self.loss_fn = loss_fn
         self.overlap = overlap
         self.seed = seed
         self._step_index = 0
@@ -135,10 +137,21 @@ class DataParallel(nn.Module):
             if self.wire_dtype == p.dtype:
                 p.grad = self.grad[sl].view(slot.shape)
         self._params = [p for _, p in params]
-        if compute_dtype != torch.float32:
-            for b in module.buffers():
-                if b.is_floating_point():
-                    b.data = b.data.to(compute_dtype)
+        # Module buffers (BatchNorm running statistics) move into one flat arena per dtype and
+        # become views of it, so the per-step rank-0 broadcast is one collective
+        # per dtype with no gather/scatter copies.  They keep their dtype (fp32 statistics).
+        self._buffer_arenas: List[torch.Tensor] = []
+        by_dtype: Dict[torch.dtype, List[torch.Tensor]] = {}
+        for b in module.buffers():
+            by_dtype.setdefault(b.dtype, []).append(b)
+        for dtype, group in by_dtype.items():
+            flat = torch.zeros(sum(b.numel() for b in group), dtype=dtype, device=self.device)
+            off = 0
+            for b in group:
+                flat[off:off + b.numel()].copy_(b.detach().reshape(-1))
+                b.data = flat[off:off + b.numel()].view(b.shape)
+                off += b.numel()
+            self._buffer_arenas.append(flat)
 
         if init_sync and self.world_size > 1:
             self._broadcast_state()
@@ -198,19 +211,8 @@ class DataParallel(nn.Module):
     def _sync_buffers(self) -> None:
         if self.world_size == 1:
             return
-        bufs = [b for b in self.module.buffers()]
-        if not bufs:
-            return
-        by_dtype: Dict[torch.dtype, List[torch.Tensor]] = {}
-        for b in bufs:
-            by_dtype.setdefault(b.dtype, []).append(b)
-        for dtype, group in by_dtype.items():
-            flat = torch.cat([b.reshape(-1) for b in group])
+        for flat in self._buffer_arenas:  # buffers are views of these (see __init__)
             dist.broadcast(flat, src=0)
-            off = 0
-            for b in group:
-                b.copy_(flat[off:off + b.numel()].view_as(b))
-                off += b.numel()
 
     # ------------------------------------------------------------------ nn.Module
     def forward(self, *args, **kwargs):
@@ -242,7 +244,7 @@ class DataParallel(nn.Module):
             loss = self(data, target)
         else:
             out = self(data)
-            loss = self.loss_fn(out.float(), target)
+            loss = self.loss_fn(out, target)
         loss.backward()
         self.finish_step()
         return loss.detach()

@@ -429,3 +429,21 @@ def test_gpt2_engine_step_writes_arena_and_trains():
     assert losses[-1] < 0.7 * losses[0], losses[::5]
     assert eng.optimizer.step_count == 30
     assert torch.equal(eng.shadow, eng.master.to(torch.bfloat16))
+
+
+def test_resnet50_engine_step():
+    """Config 3 smoke: a ResNet-50 step through the engine (bf16, channels-last) trains."""
+    from b200ddp.models.resnet50 import resnet50
+    from b200ddp.parallel.engine import DataParallel
+    torch.manual_seed(15)
+    dev = torch.device("cuda")
+    eng = DataParallel(resnet50(num_classes=10).to(dev), optimizer="sgd", lr=0.05, momentum=0.9,
+                       backend="b200", compute_dtype=torch.bfloat16)
+    assert eng.parameters_count() == 25_557_032 - 2048 * 990 - 990
+    assert len(eng._buffer_arenas) == 2 and len(eng.layout.buckets) >= 2
+    x = torch.randn(8, 3, 64, 64, device=dev)
+    y = torch.randint(0, 10, (8,), device=dev)
+    losses = [eng.train_step(x, y).item() for _ in range(25)]
+    assert losses[-1] < 0.7 * losses[0], losses[::4]
+    loss, correct = eng.eval_step(x, y)
+    assert torch.isfinite(loss)
