@@ -39,6 +39,7 @@ class GemmDesc(C.Structure):
         ("ce_write_grad", C.c_int),
         ("tile_n", C.c_int),
         ("max_ctas", C.c_int),
+        ("split_k", C.c_int),
     ]
 
 
@@ -69,6 +70,9 @@ def declare(L: C.CDLL) -> None:
     for name in ("b200_layernorm_bwd_scratch_bytes", "b200_colsum_scratch_bytes"):
         getattr(L, name).argtypes = [C.c_int64, C.c_int]
         getattr(L, name).restype = C.c_int64
+    for name in ("b200_im2col", "b200_col2im"):
+        getattr(L, name).argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 8 + [C.c_void_p]
+        getattr(L, name).restype = C.c_int
     for name in ("b200_layernorm_fwd", "b200_layernorm_bwd", "b200_colsum"):
         getattr(L, name).restype = C.c_int
     for name in ("b200_device_info", "b200_optimizer_step", "b200_cross_entropy", "b200_gemm",
@@ -144,7 +148,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, M: int, N: int,
          step_dev: Optional[torch.Tensor] = None, layer_id: int = 0,
          targets: Optional[torch.Tensor] = None, ce_grad_scale: float = 1.0,
          loss_out: Optional[torch.Tensor] = None, loss_scale: float = 1.0,
-         ce_write_grad: bool = True, tile_n: int = 0, max_ctas: int = 0) -> None:
+         ce_write_grad: bool = True, tile_n: int = 0, max_ctas: int = 0, split_k: int = 0) -> None:
     """out[M,N] = epilogue(A @ B^T).  A is [M,K] (K-major) or stored [K,M] (a_mn_major);
     B is [N,K] or stored [K,N] (b_mn_major).  Strides are taken from the tensors."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
@@ -171,7 +175,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, M: int, N: int,
     d.loss_out = _ptr(loss_out)
     d.loss_scale = loss_scale
     d.ce_write_grad = int(ce_write_grad)
-    d.tile_n, d.max_ctas = tile_n, max_ctas
+    d.tile_n, d.max_ctas, d.split_k = tile_n, max_ctas, split_k
     check(lib().b200_gemm(C.byref(d), stream_ptr(a.device)), "b200_gemm")
 
 

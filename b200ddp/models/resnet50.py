@@ -9,9 +9,11 @@ What the framework contributes for this config: the flat parameter / gradient /
 buffer arenas, bucketed overlap with backward, the fused NVLS all-reduce +
 optimizer kernel per bucket, one coalesced buffer broadcast per step for the
 BatchNorm running statistics, bf16 compute with fp32 master
-weights, and the fused cross-entropy kernel.  Convolutions and BatchNorm run on
-cuDNN through torch in round 1, in channels-last bf16 (see DESIGN.md §9 for the
-implicit-GEMM plan on the tcgen05 GEMM).
+weights, the fused cross-entropy kernel, and every convolution (forward, dgrad,
+wgrad) and the classifier on the tcgen05 GEMM: 1x1 convolutions feed the NHWC
+activation to the GEMM directly, 3x3/7x7 and strided ones go through the
+im2col/col2im gather kernels (``csrc/conv.cu``).  BatchNorm, ReLU and pooling run
+through torch on the same channels-last tensors (zero-copy views) in round 1.
 """
 from __future__ import annotations
 
@@ -31,16 +33,25 @@ class _BN(nn.BatchNorm2d):
                             self.bias.float(), self.training, self.momentum, self.eps)
 
 
+class _Conv(nn.Conv2d):
+    """nn.Conv2d container (same state-dict keys as torchvision) whose forward runs on the
+    tcgen05 GEMM through im2col/col2im (ops/functional.py) on a B200, cuDNN elsewhere."""
+
+    def forward(self, x):
+        from ..ops import functional as Fn
+        return Fn.conv2d(x, self.weight, self.stride[0], self.padding[0])
+
+
 class Bottleneck(nn.Module):
     expansion = 4
 
     def __init__(self, inplanes: int, planes: int, stride: int = 1, downsample: nn.Module | None = None):
         super().__init__()
-        self.conv1 = nn.Conv2d(inplanes, planes, 1, bias=False)
+        self.conv1 = _Conv(inplanes, planes, 1, bias=False)
         self.bn1 = _BN(planes)
-        self.conv2 = nn.Conv2d(planes, planes, 3, stride=stride, padding=1, bias=False)
+        self.conv2 = _Conv(planes, planes, 3, stride=stride, padding=1, bias=False)
         self.bn2 = _BN(planes)
-        self.conv3 = nn.Conv2d(planes, planes * 4, 1, bias=False)
+        self.conv3 = _Conv(planes, planes * 4, 1, bias=False)
         self.bn3 = _BN(planes * 4)
         self.downsample = downsample
 
@@ -56,7 +67,7 @@ class ResNet50(nn.Module):
     def __init__(self, num_classes: int = 1000):
         super().__init__()
         self.inplanes = 64
-        self.conv1 = nn.Conv2d(3, 64, 7, stride=2, padding=3, bias=False)
+        self.conv1 = _Conv(3, 64, 7, stride=2, padding=3, bias=False)
         self.bn1 = _BN(64)
         self.maxpool = nn.MaxPool2d(3, stride=2, padding=1)
         self.layer1 = self._make_layer(64, 3)
@@ -71,7 +82,7 @@ class ResNet50(nn.Module):
     def _make_layer(self, planes: int, blocks: int, stride: int = 1) -> nn.Sequential:
         down = None
         if stride != 1 or self.inplanes != planes * 4:
-            down = nn.Sequential(nn.Conv2d(self.inplanes, planes * 4, 1, stride=stride, bias=False),
+            down = nn.Sequential(_Conv(self.inplanes, planes * 4, 1, stride=stride, bias=False),
                                  _BN(planes * 4))
         layers = [Bottleneck(self.inplanes, planes, stride, down)]
         self.inplanes = planes * 4

@@ -371,3 +371,90 @@ def cross_entropy(logits, targets):
             and targets.dtype == torch.int64 and nat.available()):
         return _CrossEntropy.apply(logits, targets)
     return F.cross_entropy(logits.float(), targets)
+
+
+# ------------------------------------------------------------------ convolution (ResNet-50)
+def _im2col(x_nhwc: torch.Tensor, R: int, S: int, stride: int, pad: int) -> torch.Tensor:
+    N, H, W, Cc = x_nhwc.shape
+    P = (H + 2 * pad - R) // stride + 1
+    Q = (W + 2 * pad - S) // stride + 1
+    col = torch.empty(N * P * Q, R * S * Cc, dtype=torch.bfloat16, device=x_nhwc.device)
+    nat.check(nat.lib().b200_im2col(x_nhwc.data_ptr(), col.data_ptr(), N, H, W, Cc, R, S, stride, pad,
+                                    nat.stream_ptr(x_nhwc.device)), "b200_im2col")
+    return col
+
+
+class _Conv2d(torch.autograd.Function):
+    """Convolution on the tcgen05 GEMM.  `x` is a logical-NCHW tensor in channels-last memory
+    (i.e. NHWC storage); weights keep the torch [Cout, Cin, R, S] layout in the arenas and are
+    re-laid to [Cout, R*S*Cin] per call (a few tens of MB per step for ResNet-50)."""
+
+    @staticmethod
+    def forward(ctx, x, w, stride, pad):
+        B = _B()
+        Cout, Cin, R, S = w.shape
+        xh = x.permute(0, 2, 3, 1)
+        if not xh.is_contiguous():
+            xh = xh.contiguous()
+        cpad = (-Cin) % 8
+        if cpad:  # stem: 3 input channels -> 8
+            xh = F.pad(xh, (0, cpad))
+        w2 = w.permute(0, 2, 3, 1)
+        if cpad:
+            w2 = F.pad(w2, (0, cpad))
+        w2 = w2.reshape(Cout, -1).contiguous()
+        N, H, W_, Cp = xh.shape
+        direct = R == 1 and S == 1 and stride == 1 and pad == 0
+        a = xh.view(N * H * W_, Cp) if direct else _im2col(xh, R, S, stride, pad)
+        P = (H + 2 * pad - R) // stride + 1
+        Q = (W_ + 2 * pad - S) // stride + 1
+        y = torch.empty(N * P * Q, Cout, dtype=torch.bfloat16, device=x.device)
+        B.gemm(a, w2, y, M=N * P * Q, N=Cout, K=w2.shape[1])
+        ctx.save_for_backward(xh, w2)
+        ctx.w, ctx.geom = w, (R, S, stride, pad, direct, cpad, Cin, P, Q)
+        return y.view(N, P, Q, Cout).permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        B = _B()
+        xh, w2 = ctx.saved_tensors
+        w = ctx.w
+        R, S, stride, pad, direct, cpad, Cin, P, Q = ctx.geom
+        N, H, W_, Cp = xh.shape
+        Cout, Kt = w2.shape
+        M = N * P * Q
+        dyh = dy.permute(0, 2, 3, 1)
+        if not dyh.is_contiguous():
+            dyh = dyh.contiguous()
+        dy2 = dyh.view(M, Cout)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dcol = torch.empty(M, Kt, dtype=torch.bfloat16, device=dy.device)
+            B.gemm(dy2, w2, dcol, M=M, N=Kt, K=Cout, b_mn_major=True)  # W2 stored [Cout, Kt] = [K, N]
+            if direct:
+                dxh = dcol.view(N, H, W_, Cp)
+            else:
+                dxh = torch.empty(N, H, W_, Cp, dtype=torch.bfloat16, device=dy.device)
+                nat.check(nat.lib().b200_col2im(dcol.data_ptr(), dxh.data_ptr(), N, H, W_, Cp, R, S, stride,
+                                                pad, nat.stream_ptr(dy.device)), "b200_col2im")
+            if cpad:
+                dxh = dxh[..., :Cin]
+            dx = dxh.permute(0, 3, 1, 2)
+        a = xh.view(N * H * W_, Cp) if direct else _im2col(xh, R, S, stride, pad)  # recomputed, not stored
+        # reduction over all N*P*Q pixels into a small [Cout, R*S*Cin] output: split-K across SMs
+        dw2 = torch.zeros(Cout, Kt, dtype=torch.float32, device=dy.device)
+        B.gemm(dy2, a, dw2, M=Cout, N=Kt, K=M, a_mn_major=True, b_mn_major=True, split_k=1)
+        dw = dw2.view(Cout, R, S, Cp)[..., :Cin].permute(0, 3, 1, 2)  # back to [Cout, Cin, R, S]
+
+        def emit(dst):
+            dst.copy_(dw)
+        gw = _emit_param_grad(w, emit)
+        return dx, gw, None, None
+
+
+def conv2d(x, w, stride: int = 1, pad: int = 0):
+    """Bias-free 2-D convolution (square stride/padding).  tcgen05 GEMM path for bf16 CUDA
+    tensors with Cout a multiple of 8; torch otherwise."""
+    if native_ok(x, w) and w.shape[0] % 8 == 0:
+        return _Conv2d.apply(x, w, stride, pad)
+    return F.conv2d(x, w, None, stride, pad)

@@ -58,6 +58,8 @@ struct GemmParams {
     int ce_write_grad;
     uint32_t idesc;
     int num_m_blocks, num_n_blocks, num_k_blocks;
+    int k_splits, kb_per_split;  // split-K: tile index also selects a K slice; partials are
+                                 // combined with vector atomics into a zeroed fp32 D
 };
 
 template <int BN> struct StagesFor { static constexpr int value = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8); };
@@ -109,6 +111,21 @@ __device__ __forceinline__ void store_row(const GemmParams& p, int row, int n, c
             for (int j = 0; j < NC; ++j)
                 if (n + j < p.N) dst[j] = __float2bfloat16_rn(f[j]);
         }
+    }
+}
+
+// Split-K partial: D (fp32, zeroed by the caller) += f, 16-byte vector atomics.
+template <int NC>
+__device__ __forceinline__ void add_row(const GemmParams& p, int row, int n, const float (&f)[NC]) {
+    float* dst = reinterpret_cast<float*>(p.D) + (int64_t)row * p.ldd + n;
+    if (n + NC <= p.N && (p.ldd & 3) == 0 && ((uintptr_t)p.D & 15) == 0) {
+#pragma unroll
+        for (int j = 0; j < NC; j += 4)
+            atomicAdd(reinterpret_cast<float4*>(dst + j), make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]));
+    } else {
+#pragma unroll
+        for (int j = 0; j < NC; ++j)
+            if (n + j < p.N) atomicAdd(dst + j, f[j]);
     }
 }
 
@@ -302,7 +319,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    const int mn_tiles = p.num_m_blocks * p.num_n_blocks;
+    const int num_tiles = mn_tiles * p.k_splits;
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     if (warp == 0 && lane == 0) {
@@ -335,9 +353,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         if (lane == 0) {
             uint32_t stage = 0, phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m0 = (tile % p.num_m_blocks) * BM;
-                const int n0 = (tile / p.num_m_blocks) * BN;
-                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                const int mn = tile % mn_tiles, ks = tile / mn_tiles;
+                const int m0 = (mn % p.num_m_blocks) * BM;
+                const int n0 = (mn / p.num_m_blocks) * BN;
+                const int kb0 = ks * p.kb_per_split;
+                const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     mbar_arrive_expect_tx(&full_bar[stage], A_STAGE_BYTES + B_STAGE_BYTES);
                     uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
@@ -376,7 +397,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                 mbar_wait(&tmem_empty[as], ((it >> 1) & 1) ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * BN;
-                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                const int kb0 = (tile / mn_tiles) * p.kb_per_split;
+                const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
@@ -385,7 +408,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                     for (int k = 0; k < BK / 16; ++k) {
                         const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024u);
                         const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024u);
-                        umma_bf16(d_tmem, da, db, p.idesc, (kb | k) != 0 ? 1u : 0u);
+                        umma_bf16(d_tmem, da, db, p.idesc, ((kb - kb0) | k) != 0 ? 1u : 0u);
                     }
                     umma_commit(&empty_bar[stage]);  // slot reusable once these MMAs retire
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -400,8 +423,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         if (p.step_dev) step = (uint32_t)__ldg(p.step_dev);
         int it = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-            const int m0 = (tile % p.num_m_blocks) * BM;
-            const int n0 = (tile / p.num_m_blocks) * BN;
+            const int mn = tile % mn_tiles;
+            const int m0 = (mn % p.num_m_blocks) * BM;
+            const int n0 = (mn / p.num_m_blocks) * BN;
             const uint32_t as = it & 1;
             mbar_wait(&tmem_full[as], (it >> 1) & 1);
             tc_fence_after();
@@ -419,6 +443,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                 for (int j = 0; j < NC; ++j) f[j] = __uint_as_float(v[j]);
                 const int n = n0 + c * NC;
                 if (n >= p.N) continue;
+                if (p.k_splits > 1) {  // partial sum of one K slice
+                    if (row_ok) add_row<NC>(p, row, n, f);
+                    continue;
+                }
                 if (p.epilogue == B200_EPI_SOFTMAX_CE) epilogue_ce<NC>(p, row, row_ok, f);
                 else epilogue_chunk<NC>(p, row, row_ok, n, f, step);
                 if (p.colsum) colsum_chunk<NC>(p, row_ok, n, f);
@@ -581,7 +609,23 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
     p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(d->a_mn_major ? 1 : 0) << 15) |
               ((uint32_t)(d->b_mn_major ? 1 : 0) << 16) | ((uint32_t)(bn >> 3) << 17) |
               ((uint32_t)(BM >> 4) << 24);
-    const int tiles = p.num_m_blocks * p.num_n_blocks;
+    // split-K (wgrad with a long reduction and few output tiles): enough K slices to give
+    // every SM about two tiles, at least 4 k-blocks each
+    p.k_splits = 1;
+    p.kb_per_split = p.num_k_blocks;
+    if (d->split_k) {
+        B200_REQUIRE(d->d_fp32 && d->epilogue == B200_EPI_NONE && !d->bias && !d->aux && !d->colsum,
+                     "gemm: split_k needs a plain fp32 output (zeroed by the caller)");
+        const int mn = p.num_m_blocks * p.num_n_blocks;
+        int want = d->split_k > 1 ? d->split_k : (2 * sms + mn - 1) / mn;
+        const int max_by_k = p.num_k_blocks / 4 > 0 ? p.num_k_blocks / 4 : 1;
+        if (want > max_by_k) want = max_by_k;
+        if (want > 1) {
+            p.kb_per_split = (p.num_k_blocks + want - 1) / want;
+            p.k_splits = (p.num_k_blocks + p.kb_per_split - 1) / p.kb_per_split;
+        }
+    }
+    const int tiles = p.num_m_blocks * p.num_n_blocks * p.k_splits;
     int ctas = d->max_ctas > 0 ? d->max_ctas : sms;
     if (ctas > tiles) ctas = tiles;
     cudaStream_t s = (cudaStream_t)stream;

@@ -149,6 +149,9 @@ typedef struct {
     int ce_write_grad;                          /* 1: D receives dlogits (training); 0: D receives logits */
     int tile_n;                                 /* 0 = choose; else one of 16,32,64,128,256 */
     int max_ctas;                               /* 0 = one per SM */
+    int split_k;                                /* 0 = off; 1 = choose; >1 = that many K slices.  Plain
+                                                 * fp32 D only, zeroed by the caller: slices are combined
+                                                 * with 16-byte vector atomics (wgrad: long K, few tiles) */
 } b200_gemm_desc;
 
 int b200_gemm(const b200_gemm_desc* d, void* stream);
@@ -187,6 +190,18 @@ int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const f
 int64_t b200_colsum_scratch_bytes(int64_t rows, int cols);
 int b200_colsum(const void* x, int64_t ld, int64_t rows, int cols, void* out, int out_bf16,
                 void* scratch, void* stream);
+
+/* ---------------------------------------------------------------- convolution as GEMM
+ * For BASELINE.json config 3 (ResNet-50).  ref: none in the reference itself; its
+ * ResNet-50 baseline calls cuDNN.  NHWC bf16 tensors, C a multiple of 8.
+ * im2col: col[(n,p,q), (r,s,c)] = x[n, p*stride+r-pad, q*stride+s-pad, c] (zero outside);
+ * the forward/wgrad GEMMs of b200_gemm consume it.  col2im: the adjoint gather (no
+ * atomics) that turns the dgrad GEMM's output back into dx[n,h,w,c].  1x1 stride-1
+ * convolutions need neither. */
+int b200_im2col(const void* x, void* col, int N, int H, int W, int C, int R, int S, int stride,
+                int pad, void* stream);
+int b200_col2im(const void* dcol, void* dx, int N, int H, int W, int C, int R, int S, int stride,
+                int pad, void* stream);
 
 /* ---------------------------------------------------------------- peer-memory collectives
  * Symmetric allocation: every rank allocates the same size and exchanges the

@@ -447,3 +447,37 @@ def test_resnet50_engine_step():
     assert losses[-1] < 0.7 * losses[0], losses[::4]
     loss, correct = eng.eval_step(x, y)
     assert torch.isfinite(loss)
+
+
+@pytest.mark.parametrize("Cin,Cout,k,stride,pad,H", [
+    (64, 64, 1, 1, 0, 14), (256, 512, 1, 2, 0, 14), (64, 64, 3, 1, 1, 14), (128, 128, 3, 2, 1, 15),
+    (3, 64, 7, 2, 3, 32)])
+def test_conv2d_on_gemm_matches_torch(Cin, Cout, k, stride, pad, H):
+    from b200ddp.ops import functional as Fn
+    torch.manual_seed(16)
+    dev = torch.device("cuda")
+    x = bf(torch.randn(4, Cin, H, H, device=dev)).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    w = bf(torch.randn(Cout, Cin, k, k, device=dev) * (1.0 / (Cin * k * k) ** 0.5)).requires_grad_(True)
+    y = Fn.conv2d(x, w, stride, pad)
+    dy = bf(torch.randn_like(y))
+    y.backward(dy)
+    xr, wr = x.detach().float().requires_grad_(True), w.detach().float().requires_grad_(True)
+    yr = F.conv2d(xr, wr, None, stride, pad)
+    yr.backward(dy.float())
+    assert y.shape == yr.shape
+    assert rel_err(y, yr) < 6e-3
+    assert rel_err(x.grad, xr.grad) < 8e-3
+    assert rel_err(w.grad, wr.grad) < 8e-3
+
+
+def test_gemm_split_k(B):
+    """wgrad-shaped problem: tiny output, very long reduction, K slices combined with atomics."""
+    torch.manual_seed(17)
+    dev = torch.device("cuda")
+    for M, N, K, splits in ((64, 576, 50000, 1), (256, 64, 200704, 1), (128, 1152, 12544, 7)):
+        a = bf(torch.randn(K, M, device=dev) * 0.05)   # stored [K, M]  (dY)
+        b = bf(torch.randn(K, N, device=dev) * 0.05)   # stored [K, N]  (im2col(X))
+        out = torch.zeros(M, N, dtype=torch.float32, device=dev)
+        B.gemm(a, b, out, M=M, N=N, K=K, a_mn_major=True, b_mn_major=True, split_k=splits)
+        want = a.float().t() @ b.float()
+        assert rel_err(out, want) < 1e-4, (M, N, K, rel_err(out, want))
