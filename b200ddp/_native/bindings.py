@@ -39,6 +39,11 @@ class GemmDesc(C.Structure):
         ("ce_write_grad", C.c_int),
         ("tile_n", C.c_int),
         ("max_ctas", C.c_int),
+        ("batch_inner", C.c_int), ("batch_outer", C.c_int),
+        ("a_stride_inner", C.c_int64), ("a_stride_outer", C.c_int64),
+        ("b_stride_inner", C.c_int64), ("b_stride_outer", C.c_int64),
+        ("d_stride_inner", C.c_int64), ("d_stride_outer", C.c_int64),
+        ("causal", C.c_int),
         ("split_k", C.c_int),
     ]
 
@@ -70,6 +75,9 @@ def declare(L: C.CDLL) -> None:
     for name in ("b200_layernorm_bwd_scratch_bytes", "b200_colsum_scratch_bytes"):
         getattr(L, name).argtypes = [C.c_int64, C.c_int]
         getattr(L, name).restype = C.c_int64
+    L.b200_causal_softmax_fwd.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p]
+    L.b200_causal_softmax_bwd.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p]
+    L.b200_causal_softmax_fwd.restype = L.b200_causal_softmax_bwd.restype = C.c_int
     for name in ("b200_im2col", "b200_col2im"):
         getattr(L, name).argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 8 + [C.c_void_p]
         getattr(L, name).restype = C.c_int
@@ -148,19 +156,28 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, M: int, N: int,
          step_dev: Optional[torch.Tensor] = None, layer_id: int = 0,
          targets: Optional[torch.Tensor] = None, ce_grad_scale: float = 1.0,
          loss_out: Optional[torch.Tensor] = None, loss_scale: float = 1.0,
-         ce_write_grad: bool = True, tile_n: int = 0, max_ctas: int = 0, split_k: int = 0) -> None:
+         ce_write_grad: bool = True, tile_n: int = 0, max_ctas: int = 0, split_k: int = 0,
+         batch=None, causal: int = 0, lda=None, ldb=None, ldd=None) -> None:
     """out[M,N] = epilogue(A @ B^T).  A is [M,K] (K-major) or stored [K,M] (a_mn_major);
     B is [N,K] or stored [K,N] (b_mn_major).  Strides are taken from the tensors."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
     assert a.stride(-1) == 1 and b.stride(-1) == 1 and out.stride(-1) == 1
+    if batch is None:
+        assert a.dim() == 2 and b.dim() == 2 and out.dim() == 2
     assert out.dtype in (torch.bfloat16, torch.float32)
     if bias is not None:
         assert bias.dtype == torch.float32
     d = GemmDesc()
     d.M, d.N, d.K = M, N, K
-    d.A, d.lda, d.a_mn_major = a.data_ptr(), a.stride(0), int(a_mn_major)
-    d.B, d.ldb, d.b_mn_major = b.data_ptr(), b.stride(0), int(b_mn_major)
-    d.D, d.ldd, d.d_fp32 = out.data_ptr(), out.stride(0), int(out.dtype == torch.float32)
+    d.A, d.lda, d.a_mn_major = a.data_ptr(), (lda if lda is not None else a.stride(0)), int(a_mn_major)
+    d.B, d.ldb, d.b_mn_major = b.data_ptr(), (ldb if ldb is not None else b.stride(0)), int(b_mn_major)
+    d.D, d.ldd, d.d_fp32 = out.data_ptr(), (ldd if ldd is not None else out.stride(0)), int(out.dtype == torch.float32)
+    if batch is not None:
+        # batch = (n_inner, n_outer, (a_si, a_so), (b_si, b_so), (d_si, d_so)), strides in elements
+        d.batch_inner, d.batch_outer = batch[0], batch[1]
+        (d.a_stride_inner, d.a_stride_outer), (d.b_stride_inner, d.b_stride_outer), \
+            (d.d_stride_inner, d.d_stride_outer) = batch[2], batch[3], batch[4]
+    d.causal = causal
     d.bias = _ptr(bias)
     d.epilogue = epilogue
     d.aux, d.ldaux = _ptr(aux), (aux.stride(0) if aux is not None else 0)

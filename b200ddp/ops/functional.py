@@ -16,6 +16,7 @@ backward is still running.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import torch
@@ -336,12 +337,87 @@ def embedding(idx, wte, wpe):
 
 
 # ------------------------------------------------------------------ attention
+class _CausalAttention(torch.autograd.Function):
+    """softmax(Q K^T / sqrt(d)) V with a causal mask, from our own kernels only: batched causal
+    tcgen05 GEMMs (tiles and K ranges outside the triangle are skipped) around the row-softmax
+    kernels of csrc/attention.cu.  Q, K, V are read in place from the packed qkv activation and
+    dQ, dK, dV are written in place into one packed gradient — no head split/merge copies."""
+
+    @staticmethod
+    def forward(ctx, qkv, n_head):
+        B = _B()
+        L = nat.lib()
+        Bs, T, C3 = qkv.shape
+        Cc = C3 // 3
+        D = Cc // n_head
+        if not qkv.is_contiguous():
+            qkv = qkv.contiguous()
+        q3 = qkv.view(Bs, T, 3, Cc)
+        q, k, v = q3[:, :, 0], q3[:, :, 1], q3[:, :, 2]      # views: data_ptr carries the offset
+        BH = Bs * n_head
+        qkv_b = (D, T * C3)                                   # (head stride, sequence stride)
+        s_b = (T * T, n_head * T * T)
+        scale = 1.0 / (D ** 0.5)
+        S = torch.empty(BH, T, T, dtype=torch.bfloat16, device=qkv.device)
+        B.gemm(q, k, S, M=T, N=T, K=D, lda=C3, ldb=C3, ldd=T, causal=1,
+               batch=(n_head, Bs, qkv_b, qkv_b, s_b))
+        nat.check(L.b200_causal_softmax_fwd(S.data_ptr(), BH, T, scale, nat.stream_ptr(qkv.device)),
+                  "b200_causal_softmax_fwd")
+        out = torch.empty(Bs, T, Cc, dtype=torch.bfloat16, device=qkv.device)
+        B.gemm(S, v, out, M=T, N=D, K=T, lda=T, ldb=C3, ldd=Cc, b_mn_major=True, causal=2,
+               batch=(n_head, Bs, s_b, qkv_b, (D, T * Cc)))
+        ctx.save_for_backward(qkv, S)
+        ctx.n_head = n_head
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        B = _B()
+        L = nat.lib()
+        qkv, P = ctx.saved_tensors
+        n_head = ctx.n_head
+        Bs, T, C3 = qkv.shape
+        Cc = C3 // 3
+        D = Cc // n_head
+        BH = Bs * n_head
+        if not dout.is_contiguous():
+            dout = dout.contiguous()
+        q3 = qkv.view(Bs, T, 3, Cc)
+        q, k, v = q3[:, :, 0], q3[:, :, 1], q3[:, :, 2]
+        dqkv = torch.empty_like(qkv)
+        d3 = dqkv.view(Bs, T, 3, Cc)
+        dq, dk, dv = d3[:, :, 0], d3[:, :, 1], d3[:, :, 2]
+        qkv_b, s_b, o_b = (D, T * C3), (T * T, n_head * T * T), (D, T * Cc)
+        scale = 1.0 / (D ** 0.5)
+        # dP = dO V^T   (lower triangle only)
+        dP = torch.empty(BH, T, T, dtype=torch.bfloat16, device=qkv.device)
+        B.gemm(dout, v, dP, M=T, N=T, K=D, lda=Cc, ldb=C3, ldd=T, causal=1,
+               batch=(n_head, Bs, o_b, qkv_b, s_b))
+        # dV = P^T dO   (queries >= key tile start)
+        B.gemm(P, dout, dv, M=T, N=D, K=T, lda=T, ldb=Cc, ldd=C3, a_mn_major=True, b_mn_major=True,
+               causal=3, batch=(n_head, Bs, s_b, o_b, qkv_b))
+        nat.check(L.b200_causal_softmax_bwd(P.data_ptr(), dP.data_ptr(), BH, T, scale,
+                                            nat.stream_ptr(qkv.device)), "b200_causal_softmax_bwd")
+        dS = dP
+        # dQ = dS K     (keys <= query tile end)
+        B.gemm(dS, k, dq, M=T, N=D, K=T, lda=T, ldb=C3, ldd=C3, b_mn_major=True, causal=2,
+               batch=(n_head, Bs, s_b, qkv_b, qkv_b))
+        # dK = dS^T Q   (queries >= key tile start)
+        B.gemm(dS, q, dk, M=T, N=D, K=T, lda=T, ldb=C3, ldd=C3, a_mn_major=True, b_mn_major=True,
+               causal=3, batch=(n_head, Bs, s_b, qkv_b, qkv_b))
+        return dqkv, None
+
+
 def causal_attention(qkv: torch.Tensor, n_head: int) -> torch.Tensor:
-    """qkv [B, T, 3C] -> [B, T, C].  Round 1 uses torch's fused SDPA (flash-attention
-    library kernel) for the softmax(QK^T)V core; the four GEMMs around it are ours."""
+    """qkv [B, T, 3C] -> [B, T, C].  Own kernels on a B200 (B200DDP_ATTENTION=sdpa selects torch's
+    fused SDPA library kernel instead, for comparison); torch SDPA elsewhere."""
     Bsz, T, C3 = qkv.shape
     Cc = C3 // 3
-    q, k, v = qkv.view(Bsz, T, 3, n_head, Cc // n_head).permute(2, 0, 3, 1, 4)
+    D = Cc // n_head
+    if (native_ok(qkv) and D % 64 == 0 and T % 128 == 0
+            and os.environ.get("B200DDP_ATTENTION", "native") != "sdpa"):
+        return _CausalAttention.apply(qkv, n_head)
+    q, k, v = qkv.view(Bsz, T, 3, n_head, D).permute(2, 0, 3, 1, 4)
     y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
     return y.transpose(1, 2).reshape(Bsz, T, Cc)
 

@@ -58,6 +58,9 @@ struct GemmParams {
     int ce_write_grad;
     uint32_t idesc;
     int num_m_blocks, num_n_blocks, num_k_blocks;
+    int batch_inner, batch_outer;          // two-level batch (e.g. heads, then sequences)
+    int64_t d_stride_inner, d_stride_outer;  // output offsets per batch index, in elements
+    int causal;                            // 0 none, 1 skip tiles above the diagonal, 2 k < m0+BM, 3 k >= m0
     int k_splits, kb_per_split;  // split-K: tile index also selects a K slice; partials are
                                  // combined with vector atomics into a zeroed fp32 D
 };
@@ -82,9 +85,9 @@ __device__ __forceinline__ float gelu_tanh_grad(float z) {
 
 // Store NC consecutive columns of one row; vector path when aligned and in range.
 template <int NC>
-__device__ __forceinline__ void store_row(const GemmParams& p, int row, int n, const float (&f)[NC]) {
+__device__ __forceinline__ void store_row(const GemmParams& p, int64_t d_off, int row, int n, const float (&f)[NC]) {
     if (p.d_fp32) {
-        float* dst = reinterpret_cast<float*>(p.D) + (int64_t)row * p.ldd + n;
+        float* dst = reinterpret_cast<float*>(p.D) + d_off + (int64_t)row * p.ldd + n;
         if (n + NC <= p.N && (p.ldd & 3) == 0 && ((uintptr_t)p.D & 15) == 0) {
 #pragma unroll
             for (int j = 0; j < NC; j += 4)
@@ -95,8 +98,8 @@ __device__ __forceinline__ void store_row(const GemmParams& p, int row, int n, c
                 if (n + j < p.N) dst[j] = f[j];
         }
     } else {
-        __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + (int64_t)row * p.ldd + n;
-        if (n + NC <= p.N && (p.ldd & 7) == 0 && ((uintptr_t)p.D & 15) == 0) {
+        __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + d_off + (int64_t)row * p.ldd + n;
+        if (n + NC <= p.N && (p.ldd & 7) == 0 && ((uintptr_t)dst & 15) == 0) {
 #pragma unroll
             for (int j = 0; j < NC; j += 8) {
                 uint4 o;
@@ -116,8 +119,8 @@ __device__ __forceinline__ void store_row(const GemmParams& p, int row, int n, c
 
 // Split-K partial: D (fp32, zeroed by the caller) += f, 16-byte vector atomics.
 template <int NC>
-__device__ __forceinline__ void add_row(const GemmParams& p, int row, int n, const float (&f)[NC]) {
-    float* dst = reinterpret_cast<float*>(p.D) + (int64_t)row * p.ldd + n;
+__device__ __forceinline__ void add_row(const GemmParams& p, int64_t d_off, int row, int n, const float (&f)[NC]) {
+    float* dst = reinterpret_cast<float*>(p.D) + d_off + (int64_t)row * p.ldd + n;
     if (n + NC <= p.N && (p.ldd & 3) == 0 && ((uintptr_t)p.D & 15) == 0) {
 #pragma unroll
         for (int j = 0; j < NC; j += 4)
@@ -297,6 +300,34 @@ __device__ __forceinline__ void colsum_chunk(const GemmParams& p, bool row_ok, i
     if (lane < NC && n + col < p.N) atomicAdd(p.colsum + n + col, v[0]);
 }
 
+struct TileInfo {
+    int m0, n0, kb0, kb1, hb, bb;
+    bool skip;
+};
+// tile index -> (batch, K slice, output tile) and the k-block range it covers.  Causal modes
+// (attention): 1 = the output is lower-triangular, tiles strictly above the diagonal are not
+// computed; 2 = A is lower-triangular [rows, k <= row]; 3 = A^T is (rows k >= m0).
+template <int BN>
+__device__ __forceinline__ TileInfo decode_tile(const GemmParams& p, int tile) {
+    TileInfo t;
+    const int mn_tiles = p.num_m_blocks * p.num_n_blocks;
+    const int per_batch = mn_tiles * p.k_splits;
+    const int bt = tile / per_batch;
+    const int r = tile - bt * per_batch;
+    const int ks = r / mn_tiles, mn = r - ks * mn_tiles;
+    t.m0 = (mn % p.num_m_blocks) * BM;
+    t.n0 = (mn / p.num_m_blocks) * BN;
+    t.hb = bt % p.batch_inner;
+    t.bb = bt / p.batch_inner;
+    t.kb0 = ks * p.kb_per_split;
+    t.kb1 = min(p.num_k_blocks, t.kb0 + p.kb_per_split);
+    t.skip = false;
+    if (p.causal == 1) t.skip = t.n0 >= t.m0 + BM;
+    else if (p.causal == 2) t.kb1 = min(t.kb1, (t.m0 + BM + BK - 1) / BK);
+    else if (p.causal == 3) t.kb0 = max(t.kb0, t.m0 / BK);
+    return t;
+}
+
 template <int BN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -319,8 +350,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int mn_tiles = p.num_m_blocks * p.num_n_blocks;
-    const int num_tiles = mn_tiles * p.k_splits;
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks * p.k_splits * p.batch_inner * p.batch_outer;
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     if (warp == 0 && lane == 0) {
@@ -353,30 +383,28 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         if (lane == 0) {
             uint32_t stage = 0, phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int mn = tile % mn_tiles, ks = tile / mn_tiles;
-                const int m0 = (mn % p.num_m_blocks) * BM;
-                const int n0 = (mn / p.num_m_blocks) * BN;
-                const int kb0 = ks * p.kb_per_split;
-                const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
-                for (int kb = kb0; kb < kb1; ++kb) {
+                const TileInfo t = decode_tile<BN>(p, tile);
+                if (t.skip) continue;
+                const int m0 = t.m0, n0 = t.n0;
+                for (int kb = t.kb0; kb < t.kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     mbar_arrive_expect_tx(&full_bar[stage], A_STAGE_BYTES + B_STAGE_BYTES);
                     uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
                     uint8_t* sb = smem_b + stage * B_STAGE_BYTES;
                     const int k0 = kb * BK;
                     if (!p.a_mn) {
-                        tma_load_2d(sa, &tma_a, &full_bar[stage], k0, m0);
+                        tma_load_4d(sa, &tma_a, &full_bar[stage], k0, m0, t.hb, t.bb);
                     } else {
 #pragma unroll
                         for (int j = 0; j < BM / 64; ++j)
-                            tma_load_2d(sa + j * 8192, &tma_a, &full_bar[stage], m0 + j * 64, k0);
+                            tma_load_4d(sa + j * 8192, &tma_a, &full_bar[stage], m0 + j * 64, k0, t.hb, t.bb);
                     }
                     if (!p.b_mn) {
-                        tma_load_2d(sb, &tma_b, &full_bar[stage], k0, n0);
+                        tma_load_4d(sb, &tma_b, &full_bar[stage], k0, n0, t.hb, t.bb);
                     } else {
 #pragma unroll
                         for (int j = 0; j < (BN >= 64 ? BN / 64 : 1); ++j)
-                            tma_load_2d(sb + j * 8192, &tma_b, &full_bar[stage], n0 + j * 64, k0);
+                            tma_load_4d(sb + j * 8192, &tma_b, &full_bar[stage], n0 + j * 64, k0, t.hb, t.bb);
                     }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -392,13 +420,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
             //           K advances 16 rows = 2048 B.
             const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
             const uint32_t a_kstep = p.a_mn ? 2048u : 32u, b_kstep = p.b_mn ? 2048u : 32u;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const TileInfo t = decode_tile<BN>(p, tile);
+                if (t.skip) continue;
                 const uint32_t as = it & 1;
                 mbar_wait(&tmem_empty[as], ((it >> 1) & 1) ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * BN;
-                const int kb0 = (tile / mn_tiles) * p.kb_per_split;
-                const int kb1 = min(p.num_k_blocks, kb0 + p.kb_per_split);
+                const int kb0 = t.kb0, kb1 = t.kb1;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
@@ -414,6 +443,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(&tmem_full[as]);  // accumulator complete
+                ++it;
             }
         }
     } else {
@@ -422,10 +452,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         uint32_t step = 0;
         if (p.step_dev) step = (uint32_t)__ldg(p.step_dev);
         int it = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-            const int mn = tile % mn_tiles;
-            const int m0 = (mn % p.num_m_blocks) * BM;
-            const int n0 = (mn / p.num_m_blocks) * BN;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const TileInfo t = decode_tile<BN>(p, tile);
+            if (t.skip) continue;
+            const int m0 = t.m0, n0 = t.n0;
+            const int64_t d_off = t.hb * p.d_stride_inner + t.bb * p.d_stride_outer;
             const uint32_t as = it & 1;
             mbar_wait(&tmem_full[as], (it >> 1) & 1);
             tc_fence_after();
@@ -444,17 +475,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                 const int n = n0 + c * NC;
                 if (n >= p.N) continue;
                 if (p.k_splits > 1) {  // partial sum of one K slice
-                    if (row_ok) add_row<NC>(p, row, n, f);
+                    if (row_ok) add_row<NC>(p, d_off, row, n, f);
                     continue;
                 }
                 if (p.epilogue == B200_EPI_SOFTMAX_CE) epilogue_ce<NC>(p, row, row_ok, f);
                 else epilogue_chunk<NC>(p, row, row_ok, n, f, step);
                 if (p.colsum) colsum_chunk<NC>(p, row_ok, n, f);
-                if (row_ok) store_row<NC>(p, row, n, f);
+                if (row_ok) store_row<NC>(p, d_off, row, n, f);
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty[as]);
+            ++it;
         }
     }
 
@@ -486,15 +518,20 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld elements.
+// Rank-4 map: [batch_outer][batch_inner][outer rows][inner contiguous]; plain GEMMs use 1x1 batches.
 static int make_map(CUtensorMap* map, const void* base, int64_t inner, int64_t outer, int64_t ld,
-                    int box_inner, int box_outer) {
+                    int box_inner, int box_outer, int nbi = 1, int64_t sbi = 0, int nbo = 1,
+                    int64_t sbo = 0) {
     EncodeTiledFn enc = get_encode_fn();
     B200_REQUIRE(enc != nullptr, "gemm: cuTensorMapEncodeTiled is unavailable from this driver");
-    cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
-    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-    cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+    if (nbi <= 1) { nbi = 1; sbi = ld * outer; }
+    if (nbo <= 1) { nbo = 1; sbo = sbi * nbi; }
+    B200_REQUIRE((sbi % 8) == 0 && (sbo % 8) == 0, "gemm: batch strides must be multiples of 8 elements");
+    cuuint64_t dims[4] = {(cuuint64_t)inner, (cuuint64_t)outer, (cuuint64_t)nbi, (cuuint64_t)nbo};
+    cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)sbi * 2, (cuuint64_t)sbo * 2};
+    cuuint32_t box[4] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides,
                      box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     B200_REQUIRE(r == CUDA_SUCCESS, "gemm: cuTensorMapEncodeTiled failed (%d) inner=%lld outer=%lld ld=%lld box=%dx%d",
@@ -584,11 +621,16 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
 
     CUtensorMap ma, mb;
     int rc;
-    if (!d->a_mn_major) rc = make_map(&ma, d->A, d->K, d->M, d->lda, BK, BM);
-    else rc = make_map(&ma, d->A, d->M, d->K, d->lda, 64, BK);
+    const int nbi = d->batch_inner > 1 ? d->batch_inner : 1, nbo = d->batch_outer > 1 ? d->batch_outer : 1;
+    if (nbi * nbo > 1)
+        B200_REQUIRE(d->epilogue == B200_EPI_NONE && !d->aux && !d->bias && !d->colsum && !d->split_k,
+                     "gemm: batched mode supports the plain epilogue only");
+    B200_REQUIRE(d->causal >= 0 && d->causal <= 3, "gemm: causal mode %d unknown", d->causal);
+    if (!d->a_mn_major) rc = make_map(&ma, d->A, d->K, d->M, d->lda, BK, BM, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
+    else rc = make_map(&ma, d->A, d->M, d->K, d->lda, 64, BK, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
     if (rc) return rc;
-    if (!d->b_mn_major) rc = make_map(&mb, d->B, d->K, d->N, d->ldb, BK, bn);
-    else rc = make_map(&mb, d->B, d->N, d->K, d->ldb, 64, BK);
+    if (!d->b_mn_major) rc = make_map(&mb, d->B, d->K, d->N, d->ldb, BK, bn, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
+    else rc = make_map(&mb, d->B, d->N, d->K, d->ldb, 64, BK, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
     if (rc) return rc;
 
     GemmParams p{};
@@ -609,6 +651,9 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
     p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(d->a_mn_major ? 1 : 0) << 15) |
               ((uint32_t)(d->b_mn_major ? 1 : 0) << 16) | ((uint32_t)(bn >> 3) << 17) |
               ((uint32_t)(BM >> 4) << 24);
+    p.batch_inner = nbi; p.batch_outer = nbo;
+    p.d_stride_inner = d->d_stride_inner; p.d_stride_outer = d->d_stride_outer;
+    p.causal = d->causal;
     // split-K (wgrad with a long reduction and few output tiles): enough K slices to give
     // every SM about two tiles, at least 4 k-blocks each
     p.k_splits = 1;
@@ -625,7 +670,7 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
             p.k_splits = (p.num_k_blocks + p.kb_per_split - 1) / p.kb_per_split;
         }
     }
-    const int tiles = p.num_m_blocks * p.num_n_blocks * p.k_splits;
+    const int tiles = p.num_m_blocks * p.num_n_blocks * p.k_splits * nbi * nbo;
     int ctas = d->max_ctas > 0 ? d->max_ctas : sms;
     if (ctas > tiles) ctas = tiles;
     cudaStream_t s = (cudaStream_t)stream;

@@ -149,6 +149,13 @@ typedef struct {
     int ce_write_grad;                          /* 1: D receives dlogits (training); 0: D receives logits */
     int tile_n;                                 /* 0 = choose; else one of 16,32,64,128,256 */
     int max_ctas;                               /* 0 = one per SM */
+    /* Batched GEMM (attention): batch index = outer * batch_inner + inner (e.g. sequence, head);
+     * per-operand element strides; strides multiples of 8.  Plain epilogue only. */
+    int batch_inner, batch_outer;               /* 0/1 = not batched */
+    int64_t a_stride_inner, a_stride_outer, b_stride_inner, b_stride_outer, d_stride_inner, d_stride_outer;
+    int causal;                                 /* 0 none; 1 output lower-triangular: tiles above the diagonal
+                                                 * are skipped (never written); 2 reduce k < row tile end (A is
+                                                 * lower-triangular); 3 reduce k >= row tile start (A^T is) */
     int split_k;                                /* 0 = off; 1 = choose; >1 = that many K slices.  Plain
                                                  * fp32 D only, zeroed by the caller: slices are combined
                                                  * with 16-byte vector atomics (wgrad: long K, few tiles) */
@@ -190,6 +197,18 @@ int b200_layernorm_bwd(const void* dy, const void* x, const void* gamma, const f
 int64_t b200_colsum_scratch_bytes(int64_t rows, int cols);
 int b200_colsum(const void* x, int64_t ld, int64_t rows, int cols, void* out, int out_bf16,
                 void* scratch, void* stream);
+
+/* ---------------------------------------------------------------- attention (GPT-2 config)
+ * Row kernels of the causal attention core; the matrix products around them are batched
+ * causal b200_gemm calls (see batch_* / causal in b200_gemm_desc).  ref: none in the
+ * reference; its GPT-2 baseline uses a library flash-attention kernel via torch SDPA.
+ * scores: [batch_heads, T, T] bf16 row-major, in place.  fwd: P = softmax(scale * S) over
+ * columns <= row; bwd: dS = P * (dP - rowsum(dP * P)) * scale written over dP.  Both zero the
+ * columns between the row index and the end of its 128-row block (the consuming GEMMs read
+ * whole tiles up to that boundary); columns beyond are never read. */
+int b200_causal_softmax_fwd(void* scores, int64_t batch_heads, int T, float scale, void* stream);
+int b200_causal_softmax_bwd(const void* probs, void* dprobs, int64_t batch_heads, int T, float scale,
+                            void* stream);
 
 /* ---------------------------------------------------------------- convolution as GEMM
  * For BASELINE.json config 3 (ResNet-50).  ref: none in the reference itself; its

@@ -481,3 +481,22 @@ def test_gemm_split_k(B):
         B.gemm(a, b, out, M=M, N=N, K=K, a_mn_major=True, b_mn_major=True, split_k=splits)
         want = a.float().t() @ b.float()
         assert rel_err(out, want) < 1e-4, (M, N, K, rel_err(out, want))
+
+
+@pytest.mark.parametrize("Bs,H,T,D", [(2, 4, 256, 64), (1, 12, 1024, 64), (3, 2, 128, 128)])
+def test_causal_attention_own_kernels(Bs, H, T, D):
+    """Batched causal tcgen05 GEMMs + row softmax kernels vs fp32 SDPA, forward and backward."""
+    from b200ddp.ops import functional as Fn
+    torch.manual_seed(18)
+    dev = torch.device("cuda")
+    C = H * D
+    qkv = bf(torch.randn(Bs, T, 3 * C, device=dev)).requires_grad_(True)
+    out = Fn.causal_attention(qkv, H)
+    dout = bf(torch.randn_like(out))
+    out.backward(dout)
+    ref_in = qkv.detach().float().requires_grad_(True)
+    q, k, v = ref_in.view(Bs, T, 3, H, D).permute(2, 0, 3, 1, 4)
+    ref = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(Bs, T, C)
+    ref.backward(dout.float())
+    assert rel_err(out, ref) < 1e-2, rel_err(out, ref)
+    assert rel_err(qkv.grad, ref_in.grad) < 2e-2, rel_err(qkv.grad, ref_in.grad)
