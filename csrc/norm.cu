@@ -133,28 +133,49 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
             dxr[it * 32 + lane] = pack8(o);
         }
     }
-    float* p = partials + ((int64_t)blockIdx.x * LN_WARPS + warp) * 2 * C;
+    // block-level reduction over the 8 warps (fixed order), one partial row per block;
+    // the [8][C] staging buffer is used twice (dgamma, then dbeta): 8*2048*4 = 64 KB at most
+    extern __shared__ float ln_stage[];
+    float* p = partials + (int64_t)blockIdx.x * 2 * C;
 #pragma unroll
-    for (int it = 0; it < ITER; ++it) {
-        float4* pg = reinterpret_cast<float4*>(p + (it * 32 + lane) * 8);
-        float4* pb = reinterpret_cast<float4*>(p + C + (it * 32 + lane) * 8);
-        pg[0] = make_float4(dg[it][0], dg[it][1], dg[it][2], dg[it][3]);
-        pg[1] = make_float4(dg[it][4], dg[it][5], dg[it][6], dg[it][7]);
-        pb[0] = make_float4(db[it][0], db[it][1], db[it][2], db[it][3]);
-        pb[1] = make_float4(db[it][4], db[it][5], db[it][6], db[it][7]);
+    for (int pass = 0; pass < 2; ++pass) {
+#pragma unroll
+        for (int it = 0; it < ITER; ++it)
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                ln_stage[warp * C + (it * 32 + lane) * 8 + k] = pass == 0 ? dg[it][k] : db[it][k];
+        __syncthreads();
+        for (int c = threadIdx.x; c < C; c += LN_WARPS * 32) {
+            float t = 0.f;
+#pragma unroll
+            for (int w = 0; w < LN_WARPS; ++w) t += ln_stage[w * C + c];
+            p[pass * C + c] = t;
+        }
+        __syncthreads();
     }
 }
 
-// out[c] = sum_p partials[p * pstride + c], p in fixed order.  Output bf16 or fp32.
+// out[c] = sum_p partials[p * pstride + c].  Block = 32 columns x 8 row groups: thread (x, y)
+// sums rows y, y+8, ... (coalesced 128-byte reads), then the 8 groups are added in a fixed
+// order through shared memory -> deterministic.  Output bf16 or fp32.
 __global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ partials,
                                                               int64_t nparts, int64_t pstride, int cols,
                                                               void* __restrict__ out, int out_bf16) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= cols) return;
+    __shared__ float sm[8][33];
+    const int x = threadIdx.x & 31, y = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + x;
     float s = 0.f;
-    for (int64_t p = 0; p < nparts; ++p) s += partials[p * pstride + c];
-    if (out_bf16) reinterpret_cast<__nv_bfloat16*>(out)[c] = __float2bfloat16_rn(s);
-    else reinterpret_cast<float*>(out)[c] = s;
+    if (c < cols)
+        for (int64_t p = y; p < nparts; p += 8) s += partials[p * pstride + c];
+    sm[y][x] = s;
+    __syncthreads();
+    if (y == 0 && c < cols) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += sm[k][x];
+        if (out_bf16) reinterpret_cast<__nv_bfloat16*>(out)[c] = __float2bfloat16_rn(t);
+        else reinterpret_cast<float*>(out)[c] = t;
+    }
 }
 
 // Stage 1 of a column sum: block (bx, by) sums rows [by*rows_per, ...) of the 8-column
@@ -197,7 +218,7 @@ static int ln_grid(int64_t rows) {
 }  // namespace b200
 
 extern "C" int64_t b200_layernorm_bwd_scratch_bytes(int64_t rows, int cols) {
-    return (int64_t)b200::ln_grid(rows) * b200::LN_WARPS * 2 * cols * (int64_t)sizeof(float);
+    return (int64_t)b200::ln_grid(rows) * 2 * cols * (int64_t)sizeof(float);
 }
 
 extern "C" int b200_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y,
@@ -229,13 +250,20 @@ extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gam
     const int grid = ln_grid(rows);
     cudaStream_t s = (cudaStream_t)stream;
     float* partials = (float*)scratch;
-#define LN_BWD(I) case I: layernorm_bwd_kernel<I><<<grid, LN_WARPS * 32, 0, s>>>(                       \
+    const size_t ln_smem = (size_t)LN_WARPS * cols * sizeof(float);
+    static bool ln_attr = false;
+    if (!ln_attr) {  // > 48 KB for cols > 1536
+        cudaFuncSetAttribute(layernorm_bwd_kernel<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        cudaFuncSetAttribute(layernorm_bwd_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        ln_attr = true;
+    }
+#define LN_BWD(I) case I: layernorm_bwd_kernel<I><<<grid, LN_WARPS * 32, ln_smem, s>>>(                       \
         (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)gamma, mean, rstd,     \
         (__nv_bfloat16*)dx, (const __nv_bfloat16*)dx_add, partials, rows); break;
     switch (cols / 256) { LN_BWD(1) LN_BWD(2) LN_BWD(3) LN_BWD(4) LN_BWD(5) LN_BWD(6) LN_BWD(7) LN_BWD(8) }
 #undef LN_BWD
-    const int64_t nparts = (int64_t)grid * LN_WARPS;
-    const int rb = (cols + 255) / 256;
+    const int64_t nparts = (int64_t)grid;
+    const int rb = (cols + 31) / 32;
     reduce_partials_kernel<<<rb, 256, 0, s>>>(partials, nparts, 2 * (int64_t)cols, cols, dgamma, grads_bf16);
     reduce_partials_kernel<<<rb, 256, 0, s>>>(partials + cols, nparts, 2 * (int64_t)cols, cols, dbeta, grads_bf16);
     b200_count_launch(3);
@@ -260,7 +288,7 @@ extern "C" int b200_colsum(const void* x, int64_t ld, int64_t rows, int cols, vo
     cudaStream_t s = (cudaStream_t)stream;
     colsum_stage1_kernel<<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, ld, rows, cols, rows_per,
                                              (float*)scratch, pstride);
-    reduce_partials_kernel<<<(cols + 255) / 256, 256, 0, s>>>((const float*)scratch, chunks, pstride, cols,
+    reduce_partials_kernel<<<(cols + 31) / 32, 256, 0, s>>>((const float*)scratch, chunks, pstride, cols,
                                                               out, out_bf16);
     b200_count_launch(2);
     B200_CUDA_OK(cudaGetLastError());
