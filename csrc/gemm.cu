@@ -610,6 +610,16 @@ static int ensure_init() {
 extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
     using namespace b200;
     if (int rc = ensure_init()) return rc;
+    // cuTensorMapEncodeTiled is a driver call and needs the primary context current on THIS
+    // thread (CUDA_ERROR_INVALID_CONTEXT otherwise).  Autograd runs backward on worker threads
+    // whose first CUDA work may be this GEMM, so bind the context once per thread.
+    static thread_local bool ctx_bound = false;
+    if (!ctx_bound) {
+        int dev = 0;
+        B200_CUDA_OK(cudaGetDevice(&dev));
+        B200_CUDA_OK(cudaSetDevice(dev));  // binds the primary context; legal during stream capture
+        ctx_bound = true;
+    }
     B200_REQUIRE(d && d->A && d->B && d->D, "gemm: null pointer");
     B200_REQUIRE(d->M > 0 && d->N > 0 && d->K > 0, "gemm: bad shape %dx%dx%d", d->M, d->N, d->K);
     B200_REQUIRE((d->lda % 8) == 0 && (d->ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements (got %lld, %lld)",

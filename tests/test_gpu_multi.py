@@ -23,3 +23,41 @@ def test_peer_memory_collectives_and_engine():
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-3000:])
     assert "MULTI_GPU_OK" in r.stdout
+
+
+def test_dead_peer_is_contained(tmp_path):
+    """SURVEY §5 fault containment: a rank that dies before a fused collective must not wedge
+    the others.  The survivor's kernel spins on the dead peer's flag, hits its bound
+    (B200DDP_PEER_TIMEOUT_MS), traps; that rank exits non-zero and the launcher ends the job."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs on the box")
+    script = tmp_path / "dead_peer.py"
+    script.write_text("""
+import os, sys, time, torch
+from b200ddp import DataParallel, SimpleNet, setup_distributed
+rank, world, local = setup_distributed("nccl")
+dev = torch.device("cuda", local)
+eng = DataParallel(SimpleNet().to(dev), backend="b200", compute_dtype=torch.bfloat16)
+x = torch.randn(64, 784, device=dev); y = torch.randint(0, 10, (64,), device=dev)
+eng.train_step(x, y); torch.cuda.synchronize()
+print("STEP_OK", rank, flush=True)
+if rank == 1:
+    os._exit(3)                       # dies between steps
+t0 = time.time()
+try:
+    eng.train_step(x, y); torch.cuda.synchronize()
+except Exception as e:
+    print("SURVIVOR_ERROR after %.1fs: %s" % (time.time() - t0, type(e).__name__), flush=True)
+    os._exit(9)
+print("UNEXPECTED_SUCCESS", flush=True)
+""")
+    env = {**os.environ, "PYTHONPATH": ROOT, "B200DDP_PEER_TIMEOUT_MS": "2000"}
+    import time
+    t0 = time.time()
+    r = subprocess.run([sys.executable, "-m", "b200ddp.launch", "--nproc-per-node=2",
+                        f"--master-port={free_port()}", str(script)],
+                       cwd=ROOT, capture_output=True, text=True, timeout=180, env=env)
+    assert r.returncode != 0
+    assert "STEP_OK 0" in r.stdout and "STEP_OK 1" in r.stdout
+    assert "UNEXPECTED_SUCCESS" not in r.stdout
+    assert time.time() - t0 < 120
