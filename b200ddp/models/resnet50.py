@@ -12,8 +12,9 @@ BatchNorm running statistics, bf16 compute with fp32 master
 weights, the fused cross-entropy kernel, and every convolution (forward, dgrad,
 wgrad) and the classifier on the tcgen05 GEMM: 1x1 convolutions feed the NHWC
 activation to the GEMM directly, 3x3/7x7 and strided ones go through the
-im2col/col2im gather kernels (``csrc/conv.cu``).  BatchNorm, ReLU and pooling run
-through torch on the same channels-last tensors (zero-copy views) in round 1.
+im2col/col2im gather kernels (``csrc/conv.cu``); BatchNorm is our kernel too, fused
+with ReLU and the residual add (``csrc/batchnorm.cu``: 2 passes forward, 2 backward).
+Max/avg pooling run through torch on the same channels-last tensors (zero-copy views).
 """
 from __future__ import annotations
 
@@ -26,11 +27,12 @@ class _BN(nn.BatchNorm2d):
     """BatchNorm with fp32 statistics/affine math on bf16 activations (cuDNN mixed mode);
     the affine parameters may live in a bf16 arena."""
 
-    def forward(self, x):
+    def forward(self, x, relu: bool = False, residual=None):
+        from ..ops import functional as Fn
         if self.training and self.track_running_stats and self.num_batches_tracked is not None:
             self.num_batches_tracked.add_(1)
-        return F.batch_norm(x, self.running_mean, self.running_var, self.weight.float(),
-                            self.bias.float(), self.training, self.momentum, self.eps)
+        return Fn.batch_norm_act(x, self.weight, self.bias, self.running_mean, self.running_var,
+                                 self.training, self.momentum, self.eps, relu=relu, residual=residual)
 
 
 class _Conv(nn.Conv2d):
@@ -57,10 +59,9 @@ class Bottleneck(nn.Module):
 
     def forward(self, x):
         idt = x if self.downsample is None else self.downsample(x)
-        out = F.relu(self.bn1(self.conv1(x)), inplace=True)
-        out = F.relu(self.bn2(self.conv2(out)), inplace=True)
-        out = self.bn3(self.conv3(out))
-        return F.relu(out + idt, inplace=True)
+        out = self.bn1(self.conv1(x), relu=True)
+        out = self.bn2(self.conv2(out), relu=True)
+        return self.bn3(self.conv3(out), relu=True, residual=idt)  # add + ReLU fused into the BN pass
 
 
 class ResNet50(nn.Module):
@@ -95,7 +96,7 @@ class ResNet50(nn.Module):
             x = x.to(w.dtype)
         if x.is_cuda:
             x = x.contiguous(memory_format=torch.channels_last)
-        x = self.maxpool(F.relu(self.bn1(self.conv1(x)), inplace=True))
+        x = self.maxpool(self.bn1(self.conv1(x), relu=True))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = torch.flatten(F.adaptive_avg_pool2d(x, 1), 1)
         from ..ops import functional as Fn

@@ -534,3 +534,95 @@ def conv2d(x, w, stride: int = 1, pad: int = 0):
     if native_ok(x, w) and w.shape[0] % 8 == 0:
         return _Conv2d.apply(x, w, stride, pad)
     return F.conv2d(x, w, None, stride, pad)
+
+
+# ------------------------------------------------------------------ batch norm (+ReLU, +residual)
+def _f32_param(p: torch.Tensor) -> torch.Tensor:
+    m = getattr(p, "_b200_master", None)
+    return m if m is not None else p.float()
+
+
+class _BatchNormAct(torch.autograd.Function):
+    """y = relu?(BN(x) (+ residual)) on channels-last bf16 activations: 2 passes forward,
+    2 backward (csrc/batchnorm.cu); running statistics are updated in the statistics pass."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, running_mean, running_var, training, momentum, eps, relu, residual):
+        L = nat.lib()
+        xh = x.permute(0, 2, 3, 1)
+        if not xh.is_contiguous():
+            xh = xh.contiguous()
+        N, H, W, Cc = xh.shape
+        rows = N * H * W
+        rh = None
+        if residual is not None:
+            rh = residual.permute(0, 2, 3, 1)
+            if not rh.is_contiguous():
+                rh = rh.contiguous()
+        y = torch.empty_like(xh)
+        gamma, beta = _f32_param(weight), _f32_param(bias)
+        sc = _scratch_buf(x.device, int(L.b200_batchnorm_scratch_bytes(Cc)))
+        if training:
+            mean = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            rstd = torch.empty(Cc, dtype=torch.float32, device=x.device)
+        else:
+            mean = running_mean
+            rstd = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            nat.check(L.b200_batchnorm_eval_rstd(running_var.data_ptr(), rstd.data_ptr(), Cc, eps,
+                                                 nat.stream_ptr(x.device)), "b200_batchnorm_eval_rstd")
+        nat.check(L.b200_batchnorm_fwd(
+            xh.data_ptr(), rh.data_ptr() if rh is not None else None, y.data_ptr(), gamma.data_ptr(),
+            beta.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+            running_mean.data_ptr() if training else None, running_var.data_ptr() if training else None,
+            rows, Cc, eps, momentum, int(training), int(relu), sc.data_ptr(), nat.stream_ptr(x.device)),
+            "b200_batchnorm_fwd")
+        ctx.save_for_backward(xh, y if relu else xh, mean, rstd)
+        ctx.weight, ctx.bias = weight, bias
+        ctx.relu, ctx.has_res = relu, residual is not None
+        return y.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = nat.lib()
+        xh, y, mean, rstd = ctx.saved_tensors
+        weight, bias = ctx.weight, ctx.bias
+        N, H, W, Cc = xh.shape
+        rows = N * H * W
+        dyh = dy.permute(0, 2, 3, 1)
+        if not dyh.is_contiguous():
+            dyh = dyh.contiguous()
+        dx = torch.empty_like(xh)
+        dres = torch.empty_like(xh) if ctx.has_res else None
+        gdst, bdst = getattr(weight, "_b200_grad", None), getattr(bias, "_b200_grad", None)
+        owned = gdst is not None and bdst is not None
+        if not owned:
+            gdst, bdst = torch.empty_like(weight), torch.empty_like(bias)
+        sc = _scratch_buf(dy.device, int(L.b200_batchnorm_scratch_bytes(Cc)))
+        nat.check(L.b200_batchnorm_bwd(
+            dyh.data_ptr(), xh.data_ptr(), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+            _f32_param(weight).data_ptr(), dx.data_ptr(), dres.data_ptr() if dres is not None else None,
+            gdst.data_ptr(), bdst.data_ptr(), int(gdst.dtype == torch.bfloat16), rows, Cc, int(ctx.relu),
+            sc.data_ptr(), nat.stream_ptr(dy.device)), "b200_batchnorm_bwd")
+        if owned:
+            weight._b200_ready()
+            bias._b200_ready()
+            gw = gb = None
+        else:
+            gw, gb = gdst, bdst
+        return (dx.permute(0, 3, 1, 2), gw, gb, None, None, None, None, None, None,
+                dres.permute(0, 3, 1, 2) if dres is not None else None)
+
+
+def batch_norm_act(x, weight, bias, running_mean, running_var, training: bool, momentum: float, eps: float,
+                   relu: bool = False, residual=None):
+    """BatchNorm2d on a logical-NCHW / channels-last tensor, optionally fused with a residual
+    add and ReLU.  Own kernels for bf16 CUDA tensors with power-of-two channels, torch otherwise."""
+    Cc = x.shape[1]
+    if (x.is_cuda and x.dtype == torch.bfloat16 and nat.available() and 8 <= Cc <= 2048
+            and (Cc & (Cc - 1)) == 0 and running_mean is not None and running_mean.dtype == torch.float32):
+        return _BatchNormAct.apply(x, weight, bias, running_mean, running_var, training, momentum, eps,
+                                   relu, residual)
+    y = F.batch_norm(x, running_mean, running_var, weight.float(), bias.float(), training, momentum, eps)
+    if residual is not None:
+        y = y + residual
+    return F.relu(y) if relu else y

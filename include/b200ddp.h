@@ -222,6 +222,26 @@ int b200_im2col(const void* x, void* col, int N, int H, int W, int C, int R, int
 int b200_col2im(const void* dcol, void* dx, int N, int H, int W, int C, int R, int S, int stride,
                 int pad, void* stream);
 
+/* ---------------------------------------------------------------- batch normalisation
+ * For BASELINE.json config 3 (ResNet-50).  ref: none in the reference; its ResNet-50
+ * baseline uses ATen batch_norm (+ separate ReLU / add kernels).  x, y, residual, dy, dx,
+ * dres: [rows, C] bf16 (NHWC activations flattened), C a power of two in [8, 2048];
+ * gamma, beta, mean, rstd, running_*: fp32 [C].
+ * fwd: training != 0 computes batch statistics (and updates running_* when non-null, unbiased
+ * variance, `momentum`), otherwise mean/rstd must already hold the inference statistics
+ * (b200_batchnorm_eval_rstd).  y = relu?((x - mean) * rstd * gamma + beta (+ residual)).
+ * bwd: g = dy * [y > 0] when relu; dgamma/dbeta [C] bf16 or fp32; dx; dres = g when non-null
+ * (gradient of the fused residual branch).  scratch: b200_batchnorm_scratch_bytes(C). */
+int64_t b200_batchnorm_scratch_bytes(int C);
+int b200_batchnorm_fwd(const void* x, const void* residual, void* y, const float* gamma, const float* beta,
+                       float* mean, float* rstd, float* running_mean, float* running_var, int64_t rows,
+                       int C, float eps, float momentum, int training, int relu, void* scratch,
+                       void* stream);
+int b200_batchnorm_bwd(const void* dy, const void* x, const void* y, const float* mean, const float* rstd,
+                       const float* gamma, void* dx, void* dres, void* dgamma, void* dbeta, int grads_bf16,
+                       int64_t rows, int C, int relu, void* scratch, void* stream);
+int b200_batchnorm_eval_rstd(const float* running_var, float* rstd, int C, float eps, void* stream);
+
 /* ---------------------------------------------------------------- peer-memory collectives
  * Symmetric allocation: every rank allocates the same size and exchanges the
  * 64-byte CUDA IPC handle through the process group (the only host-side

@@ -500,3 +500,45 @@ def test_causal_attention_own_kernels(Bs, H, T, D):
     ref.backward(dout.float())
     assert rel_err(out, ref) < 1e-2, rel_err(out, ref)
     assert rel_err(qkv.grad, ref_in.grad) < 2e-2, rel_err(qkv.grad, ref_in.grad)
+
+
+@pytest.mark.parametrize("C,H,relu,res", [(64, 28, True, False), (256, 14, True, True), (512, 7, False, False),
+                                          (2048, 7, True, True)])
+def test_batchnorm_act_kernels(C, H, relu, res):
+    from b200ddp.ops import functional as Fn
+    torch.manual_seed(19)
+    dev = torch.device("cuda")
+    N = 8
+    x = bf(torch.randn(N, C, H, H, device=dev) * 2 + 0.3).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    r = bf(torch.randn(N, C, H, H, device=dev)).contiguous(memory_format=torch.channels_last).requires_grad_(True) if res else None
+    w = bf(torch.rand(C, device=dev) + 0.5).requires_grad_(True)
+    b = bf(torch.randn(C, device=dev) * 0.1).requires_grad_(True)
+    rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    y = Fn.batch_norm_act(x, w, b, rm, rv, True, 0.1, 1e-5, relu=relu, residual=r)
+    dy = bf(torch.randn_like(y))
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_(True)
+    rr = r.detach().float().requires_grad_(True) if res else None
+    wr, br = w.detach().float().requires_grad_(True), b.detach().float().requires_grad_(True)
+    rm2, rv2 = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    yr = F.batch_norm(xr, rm2, rv2, wr, br, True, 0.1, 1e-5)
+    if res:
+        yr = yr + rr
+    if relu:
+        yr = F.relu(yr)
+    yr.backward(dy.float())
+    assert rel_err(y, yr) < 8e-3
+    assert rel_err(x.grad, xr.grad) < 2e-2
+    assert rel_err(w.grad, wr.grad) < 2e-2 and rel_err(b.grad, br.grad) < 2e-2
+    if res:
+        assert rel_err(r.grad, rr.grad) < 1e-2
+    assert torch.allclose(rm, rm2, rtol=1e-3, atol=1e-4) and torch.allclose(rv, rv2, rtol=1e-3, atol=1e-4)
+    # inference path uses the running statistics
+    ye = Fn.batch_norm_act(x.detach(), w.detach(), b.detach(), rm, rv, False, 0.1, 1e-5, relu=relu,
+                           residual=r.detach() if res else None)
+    yer = F.batch_norm(xr.detach(), rm2, rv2, wr.detach(), br.detach(), False, 0.1, 1e-5)
+    if res:
+        yer = yer + rr.detach()
+    if relu:
+        yer = F.relu(yer)
+    assert rel_err(ye, yer) < 8e-3
