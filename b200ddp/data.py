@@ -151,9 +151,9 @@ class BatchLoader:
         self._ring = [
             (
                 torch.empty(self.batch_size, *d.data.shape[1:], dtype=d.data.dtype).pin_memory(),
-                torch.empty(self.batch_size, dtype=d.labels.dtype).pin_memory(),
+                torch.empty(self.batch_size, *d.labels.shape[1:], dtype=d.labels.dtype).pin_memory(),
                 torch.empty(self.batch_size, *d.data.shape[1:], dtype=d.data.dtype, device=self.device),
-                torch.empty(self.batch_size, dtype=d.labels.dtype, device=self.device),
+                torch.empty(self.batch_size, *d.labels.shape[1:], dtype=d.labels.dtype, device=self.device),
                 torch.cuda.Event(),  # copy done
                 torch.cuda.Event(),  # consumer done with the device buffers
             )

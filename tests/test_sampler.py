@@ -46,3 +46,13 @@ def test_dataset_shapes_and_dtypes():
     assert x.shape == (784,) and x.dtype == torch.float32
     assert y.dtype == torch.int64 and 0 <= int(y) < 10
     assert len(ds) == 17
+
+
+def test_loader_handles_sequence_labels():
+    """Token datasets have [N, T] labels; batches keep that shape (CPU path)."""
+    from b200ddp.models.datasets import SyntheticTokens
+    ds = SyntheticTokens(20, seq_len=16, vocab_size=50, seed=0)
+    loader, _ = create_data_loader(ds, 8, rank=0, world_size=1)
+    shapes = [(x.shape, y.shape) for x, y in loader]
+    assert shapes[0] == (torch.Size([8, 16]), torch.Size([8, 16])) and shapes[-1][0][0] == 4
+    assert torch.equal(ds.data[:, 1:], ds.labels[:, :-1])  # labels are the inputs shifted by one
