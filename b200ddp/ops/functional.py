@@ -77,7 +77,16 @@ def _emit_param_grad(p: torch.Tensor, compute_into, signal: bool = True):
 def _wgrad_into(dy2: torch.Tensor, x2: torch.Tensor, dst: torch.Tensor) -> None:
     # dW[n_out, n_in] = dy^T @ x : both operands read MN-major, nothing is transposed
     n_out, n_in = dst.shape
-    _B().gemm(dy2, x2, dst, M=n_out, N=n_in, K=x2.shape[0], a_mn_major=True, b_mn_major=True)
+    K = x2.shape[0]
+    tiles = ((n_out + 127) // 128) * ((n_in + 255) // 256)
+    if tiles < 100 and K >= 2048:
+        # few output tiles, long reduction: split K across the idle SMs (fp32 partials combined
+        # with vector atomics), then one cast into the arena
+        tmp = torch.zeros(n_out, n_in, dtype=torch.float32, device=dst.device)
+        _B().gemm(dy2, x2, tmp, M=n_out, N=n_in, K=K, a_mn_major=True, b_mn_major=True, split_k=1)
+        dst.copy_(tmp)
+        return
+    _B().gemm(dy2, x2, dst, M=n_out, N=n_in, K=K, a_mn_major=True, b_mn_major=True)
 
 
 # ------------------------------------------------------------------ linear (+bias, +residual)

@@ -505,6 +505,175 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     }
 }
 
+// ---------------------------------------------------------------- 256 x 256 tiles
+// Large-GEMM variant.  Measured on B200 the 128x256 kernel is bound by what one SM can pull
+// from L2 (48 KB of operands per 540 MMA cycles = 89 B/clk; 128-wide tiles are slower still),
+// not by the tensor pipe.  This kernel gives each CTA TWO M=128 accumulators that share every B
+// tile — a 256x256 output tile, 64 KB per 1080 MMA cycles = 59 B/clk — without clusters: both
+// accumulators live in TMEM (2 x 256 columns = all of it), the MMA thread interleaves them per
+// k-block, and the epilogue drains the upper half while the lower half's last MMAs retire and
+// the next tile's MMAs refill the upper half.  Plain (non-batched, non-causal) problems only.
+constexpr int BM2 = 256;
+constexpr int STAGES2 = 3;
+constexpr uint32_t A2_STAGE_BYTES = BM2 * BK * 2;   // 32 KB
+constexpr uint32_t B2_STAGE_BYTES = 256 * BK * 2;   // 32 KB
+constexpr uint32_t GEMM2_SMEM = STAGES2 * (A2_STAGE_BYTES + B2_STAGE_BYTES) + 1024 + 256;
+
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_kernel_m256(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                 const GemmParams p) {
+    constexpr int BN = 256;
+    constexpr int NC = 32;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + STAGES2 * A2_STAGE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + STAGES2 * B2_STAGE_BYTES);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + STAGES2;
+    uint64_t* tmem_full = bars + 2 * STAGES2;       // [2]: upper / lower accumulator complete
+    uint64_t* tmem_empty = bars + 2 * STAGES2 + 2;  // [2]: upper / lower accumulator drained
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES2 + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < STAGES2; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], 4);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m0 = (tile % p.num_m_blocks) * BM2;
+                const int n0 = (tile / p.num_m_blocks) * BN;
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    mbar_arrive_expect_tx(&full_bar[stage], A2_STAGE_BYTES + B2_STAGE_BYTES);
+                    uint8_t* sa = smem_a + stage * A2_STAGE_BYTES;
+                    uint8_t* sb = smem_b + stage * B2_STAGE_BYTES;
+                    const int k0 = kb * BK;
+                    if (!p.a_mn) {
+                        tma_load_4d(sa, &tma_a, &full_bar[stage], k0, m0, 0, 0);  // one 256-row box
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BM2 / 64; ++j)
+                            tma_load_4d(sa + j * 8192, &tma_a, &full_bar[stage], m0 + j * 64, k0, 0, 0);
+                    }
+                    if (!p.b_mn) {
+                        tma_load_4d(sb, &tma_b, &full_bar[stage], k0, n0, 0, 0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_4d(sb + j * 8192, &tma_b, &full_bar[stage], n0 + j * 64, k0, 0, 0);
+                    }
+                    if (++stage == STAGES2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            int it = 0;
+            const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
+            const uint32_t a_kstep = p.a_mn ? 2048u : 32u, b_kstep = p.b_mn ? 2048u : 32u;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+                const uint32_t par = (uint32_t)(it & 1);
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem_a + stage * A2_STAGE_BYTES);
+                    const uint32_t sb = smem_u32(smem_b + stage * B2_STAGE_BYTES);
+                    const bool last = kb == p.num_k_blocks - 1;
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        if (kb == 0) {  // this half of TMEM must have been drained (previous tile)
+                            mbar_wait(&tmem_empty[h], par ^ 1);
+                            tc_fence_after();
+                        }
+                        // rows 128..255 of the A stage start 16 KB in (K-major: 128 rows x 128 B;
+                        // MN-major: two 8 KB chunks)
+                        const uint32_t sah = sa + h * 16384u;
+#pragma unroll
+                        for (int k = 0; k < BK / 16; ++k) {
+                            const uint64_t da = umma_smem_desc(sah + k * a_kstep, a_lbo, 1024u);
+                            const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024u);
+                            umma_bf16(tmem_base + h * BN, da, db, p.idesc, (kb | k) != 0 ? 1u : 0u);
+                        }
+                        if (last) umma_commit(&tmem_full[h]);  // upper half completes first
+                    }
+                    umma_commit(&empty_bar[stage]);
+                    if (++stage == STAGES2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else {
+        const int quarter = warp & 3;
+        uint32_t step = 0;
+        if (p.step_dev) step = (uint32_t)__ldg(p.step_dev);
+        int it = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+            const int m0 = (tile % p.num_m_blocks) * BM2;
+            const int n0 = (tile / p.num_m_blocks) * BN;
+            const uint32_t par = (uint32_t)(it & 1);
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) {
+                mbar_wait(&tmem_full[h], par);
+                tc_fence_after();
+                const int row = m0 + h * 128 + quarter * 32 + lane;
+                const bool row_ok = row < p.M;
+                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + h * BN;
+#pragma unroll 1
+                for (int c = 0; c < BN / NC; ++c) {
+                    uint32_t v[NC];
+                    tmem_ld_32x32(taddr + c * NC, v);
+                    tmem_ld_wait();
+                    float f[NC];
+#pragma unroll
+                    for (int j = 0; j < NC; ++j) f[j] = __uint_as_float(v[j]);
+                    const int n = n0 + c * NC;
+                    if (n >= p.N) continue;
+                    epilogue_chunk<NC>(p, row, row_ok, n, f, step);
+                    if (p.colsum) colsum_chunk<NC>(p, row_ok, n, f);
+                    if (row_ok) store_row<NC>(p, 0, row, n, f);
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty[h]);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
 // ---------------------------------------------------------------- host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -569,6 +738,24 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams
     return 0;
 }
 
+static int launch_m256(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int ctas, cudaStream_t s) {
+    static const bool pdl = getenv("B200DDP_NO_PDL") == nullptr;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)ctas);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = GEMM2_SMEM;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel_m256, ma, mb, p));
+    b200_count_launch(1);
+    B200_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
 static int sm_count() {
     static int n = 0;
     if (n == 0) {
@@ -592,8 +779,9 @@ static int pick_tile_n(const b200_gemm_desc* d, int sms) {
     for (int c : cands) {
         const int64_t tiles = mblk * ((d->N + c - 1) / c);
         const int64_t waves = (tiles + sms - 1) / sms;
-        // per-tile cost: MMA time ~ BN, plus a fixed per-tile overhead (~ BN=48 worth)
-        const int64_t cost = waves * (c + 48);
+        // measured: tiles are bound by operand bytes pulled from L2, (128 + BN) * 128 B per
+        // k-block, so the cost of a wave scales with 128 + BN; ties go to the wider tile
+        const int64_t cost = waves * (128 + c);
         if (cost < best_cost) { best_cost = cost; best = c; }
     }
     return best;
@@ -643,7 +831,18 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
         B200_REQUIRE(d->epilogue == B200_EPI_NONE && !d->aux && !d->bias && !d->colsum && !d->split_k,
                      "gemm: batched mode supports the plain epilogue only");
     B200_REQUIRE(d->causal >= 0 && d->causal <= 3, "gemm: causal mode %d unknown", d->causal);
-    if (!d->a_mn_major) rc = make_map(&ma, d->A, d->K, d->M, d->lda, BK, BM, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
+    // 256x256 dual-accumulator tiles for large plain GEMMs (at least ~one wave of them)
+    static const bool m256_off = getenv("B200DDP_NO_M256") != nullptr;
+    bool m256 = false;
+    if (bn == 256 && nbi * nbo == 1 && !d->causal && !d->split_k && d->epilogue != B200_EPI_SOFTMAX_CE) {
+        const int64_t t2 = (int64_t)((d->M + BM2 - 1) / BM2) * ((d->N + 255) / 256);
+        // measured: wins for long reductions (K >= 4096: 1481 vs 1288 TFLOP/s at 8192^3); with short K its
+        // single-buffered accumulators expose the epilogue and 128x256 is faster
+        m256 = d->tile_m == 256 || (d->tile_m == 0 && !m256_off && d->M >= 512 && d->K >= 4096 && t2 >= sms);
+    }
+    B200_REQUIRE(d->tile_m == 0 || d->tile_m == 128 || d->tile_m == 256, "gemm: tile_m must be 0, 128 or 256");
+    B200_REQUIRE(d->tile_m != 256 || m256, "gemm: tile_m 256 needs tile_n 256 and a plain, non-batched problem");
+    if (!d->a_mn_major) rc = make_map(&ma, d->A, d->K, d->M, d->lda, BK, m256 ? BM2 : BM, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
     else rc = make_map(&ma, d->A, d->M, d->K, d->lda, 64, BK, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
     if (rc) return rc;
     if (!d->b_mn_major) rc = make_map(&mb, d->B, d->K, d->N, d->ldb, BK, bn, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
@@ -661,7 +860,7 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
     p.seed = d->seed; p.step_dev = d->step_dev; p.layer_id = d->layer_id;
     p.targets = d->targets; p.ce_grad_scale = d->ce_grad_scale;
     p.loss_out = d->loss_out; p.loss_scale = d->loss_scale; p.ce_write_grad = d->ce_write_grad;
-    p.num_m_blocks = (d->M + BM - 1) / BM;
+    p.num_m_blocks = m256 ? (d->M + BM2 - 1) / BM2 : (d->M + BM - 1) / BM;
     p.num_n_blocks = (d->N + bn - 1) / bn;
     p.num_k_blocks = (d->K + BK - 1) / BK;
     // instruction descriptor: fp32 accumulate, bf16 A/B, majors, N>>3, M>>4
@@ -691,6 +890,7 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
     int ctas = d->max_ctas > 0 ? d->max_ctas : sms;
     if (ctas > tiles) ctas = tiles;
     cudaStream_t s = (cudaStream_t)stream;
+    if (m256) return launch_m256(ma, mb, p, ctas, s);
     switch (bn) {
         case 16: return launch<16>(ma, mb, p, ctas, s);
         case 32: return launch<32>(ma, mb, p, ctas, s);
@@ -710,5 +910,6 @@ int b200_gemm_init() {
                                       (int)gemm_smem_bytes<BN>()))
     PREP(16); PREP(32); PREP(64); PREP(128); PREP(256);
 #undef PREP
+    B200_CUDA_OK(cudaFuncSetAttribute(gemm_kernel_m256, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM2_SMEM));
     return 0;
 }

@@ -156,6 +156,8 @@ typedef struct {
     int causal;                                 /* 0 none; 1 output lower-triangular: tiles above the diagonal
                                                  * are skipped (never written); 2 reduce k < row tile end (A is
                                                  * lower-triangular); 3 reduce k >= row tile start (A^T is) */
+    int tile_m;                                 /* 0 = choose; 128; 256 = dual-accumulator 256x256 tiles
+                                                 * (needs tile_n 256, plain non-batched problem) */
     int split_k;                                /* 0 = off; 1 = choose; >1 = that many K slices.  Plain
                                                  * fp32 D only, zeroed by the caller: slices are combined
                                                  * with 16-byte vector atomics (wgrad: long K, few tiles) */

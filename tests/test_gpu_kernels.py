@@ -542,3 +542,20 @@ def test_batchnorm_act_kernels(C, H, relu, res):
     if relu:
         yer = F.relu(yer)
     assert rel_err(ye, yer) < 8e-3
+
+
+@pytest.mark.parametrize("M,N,K,a_mn,b_mn", [(512, 512, 256, False, False), (1000, 700, 328, False, False),
+                                            (768, 512, 1024, True, True), (2048, 1024, 192, False, True)])
+def test_gemm_256x256_dual_accumulator_tiles(B, M, N, K, a_mn, b_mn):
+    torch.manual_seed(20)
+    dev = torch.device("cuda")
+    a = bf(torch.randn((K, M) if a_mn else (M, K), device=dev))
+    b = bf(torch.randn((K, N) if b_mn else (N, K), device=dev))
+    want = _ref_gemm(a, b, a_mn, b_mn)
+    bias = torch.randn(N, device=dev)
+    out = torch.full((M, N), 7.0, dtype=torch.bfloat16, device=dev)
+    B.gemm(a, b, out, M=M, N=N, K=K, a_mn_major=a_mn, b_mn_major=b_mn, tile_n=256, tile_m=256, bias=bias)
+    assert rel_err(out, want + bias) < 6e-3, rel_err(out, want + bias)
+    out32 = torch.empty(M, N, dtype=torch.float32, device=dev)
+    B.gemm(a, b, out32, M=M, N=N, K=K, a_mn_major=a_mn, b_mn_major=b_mn, tile_n=256, tile_m=256)
+    assert rel_err(out32, want) < 2e-5
