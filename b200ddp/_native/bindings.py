@@ -76,6 +76,12 @@ def declare(L: C.CDLL) -> None:
     for name in ("b200_layernorm_bwd_scratch_bytes", "b200_colsum_scratch_bytes"):
         getattr(L, name).argtypes = [C.c_int64, C.c_int]
         getattr(L, name).restype = C.c_int64
+    L.b200_flash_attn_fwd.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                      C.c_void_p]
+    L.b200_flash_attn_fwd.restype = C.c_int
+    if hasattr(L, "b200_flash_attn_bwd"):
+        L.b200_flash_attn_bwd.argtypes = [C.c_void_p] * 7 + [C.c_int] * 4 + [C.c_void_p]
+        L.b200_flash_attn_bwd.restype = C.c_int
     L.b200_causal_softmax_fwd.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p]
     L.b200_causal_softmax_bwd.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_void_p]
     L.b200_causal_softmax_fwd.restype = L.b200_causal_softmax_bwd.restype = C.c_int

@@ -417,6 +417,19 @@ class _CausalAttention(torch.autograd.Function):
         return dqkv, None
 
 
+def flash_attention_forward(qkv: torch.Tensor, n_head: int):
+    """Fused causal attention forward (csrc/flash_attention.cu): returns (out [B,T,C], lse [B,H,T])."""
+    Bs, T, C3 = qkv.shape
+    Cc = C3 // 3
+    if not qkv.is_contiguous():
+        qkv = qkv.contiguous()
+    out = torch.empty(Bs, T, Cc, dtype=torch.bfloat16, device=qkv.device)
+    lse = torch.empty(Bs, n_head, T, dtype=torch.float32, device=qkv.device)
+    nat.check(nat.lib().b200_flash_attn_fwd(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), Bs, T, n_head,
+                                            Cc // n_head, nat.stream_ptr(qkv.device)), "b200_flash_attn_fwd")
+    return out, lse
+
+
 def causal_attention(qkv: torch.Tensor, n_head: int) -> torch.Tensor:
     """qkv [B, T, 3C] -> [B, T, C].  Own kernels on a B200 (B200DDP_ATTENTION=sdpa selects torch's
     fused SDPA library kernel instead, for comparison); torch SDPA elsewhere."""
@@ -425,6 +438,8 @@ def causal_attention(qkv: torch.Tensor, n_head: int) -> torch.Tensor:
     D = Cc // n_head
     if (native_ok(qkv) and D % 64 == 0 and T % 128 == 0
             and os.environ.get("B200DDP_ATTENTION", "native") != "sdpa"):
+        if D == 64 and not (torch.is_grad_enabled() and qkv.requires_grad):
+            return flash_attention_forward(qkv, n_head)[0]   # inference: scores stay on chip
         return _CausalAttention.apply(qkv, n_head)
     q, k, v = qkv.view(Bsz, T, 3, n_head, D).permute(2, 0, 3, 1, 4)
     y = F.scaled_dot_product_attention(q, k, v, is_causal=True)

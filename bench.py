@@ -26,6 +26,9 @@ import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# rank 0 prints exactly one line: keep NCCL's own banner ("NCCL version ...") off stdout
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+    os.environ["NCCL_DEBUG"] = "WARN"
 
 L2_BYTES = 126 * 1024 * 1024
 IN_FEATURES, CLASSES = 784, 10

@@ -212,6 +212,15 @@ int b200_causal_softmax_fwd(void* scores, int64_t batch_heads, int T, float scal
 int b200_causal_softmax_bwd(const void* probs, void* dprobs, int64_t batch_heads, int T, float scale,
                             void* stream);
 
+/* Fused causal attention (flash-style): scores never leave the chip.  qkv: packed
+ * [B, T, 3, H, D] bf16 (the qkv linear's output), D = 64, T a multiple of 128.
+ * fwd: out [B, T, H*D] bf16, lse [B, H, T] fp32 (natural-log sum-exp of the scaled scores).
+ * bwd: dqkv [B, T, 3, H, D] bf16 from dout [B, T, H*D]; `dq_acc` is an fp32 [B, H, T, D]
+ * workspace (zeroed by the call), `delta` an fp32 [B, H, T] workspace. */
+int b200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D, void* stream);
+int b200_flash_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                        float* dq_acc, float* delta, int B, int T, int H, int D, void* stream);
+
 /* ---------------------------------------------------------------- convolution as GEMM
  * For BASELINE.json config 3 (ResNet-50).  ref: none in the reference itself; its
  * ResNet-50 baseline calls cuDNN.  NHWC bf16 tensors, C a multiple of 8.

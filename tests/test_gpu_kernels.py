@@ -559,3 +559,23 @@ def test_gemm_256x256_dual_accumulator_tiles(B, M, N, K, a_mn, b_mn):
     out32 = torch.empty(M, N, dtype=torch.float32, device=dev)
     B.gemm(a, b, out32, M=M, N=N, K=K, a_mn_major=a_mn, b_mn_major=b_mn, tile_n=256, tile_m=256)
     assert rel_err(out32, want) < 2e-5
+
+
+@pytest.mark.parametrize("Bs,H,T", [(1, 1, 128), (2, 4, 384), (2, 12, 1024)])
+def test_flash_attention_forward(Bs, H, T):
+    """Fused tcgen05 attention forward (scores stay in TMEM/smem) vs fp32 SDPA, plus its LSE."""
+    from b200ddp.ops import functional as Fn
+    torch.manual_seed(21)
+    dev = torch.device("cuda")
+    D, C = 64, H * 64
+    qkv = bf(torch.randn(Bs, T, 3 * C, device=dev))
+    out, lse = Fn.flash_attention_forward(qkv, H)
+    q, k, v = qkv.float().view(Bs, T, 3, H, D).permute(2, 0, 3, 1, 4)
+    ref = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(Bs, T, C)
+    s = (q @ k.transpose(-1, -2)) / D ** 0.5
+    mask = torch.ones(T, T, device=dev, dtype=torch.bool).tril()
+    lse_ref = torch.logsumexp(s.masked_fill(~mask, float("-inf")), dim=-1)
+    assert rel_err(out, ref) < 6e-3
+    assert (lse - lse_ref).abs().max().item() < 1e-3
+    with torch.no_grad():  # the no-grad path of causal_attention uses this kernel
+        assert torch.equal(Fn.causal_attention(qkv, H), out)
