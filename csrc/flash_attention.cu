@@ -26,7 +26,8 @@ constexpr int FA_BLOCK = 128;   // queries per CTA and keys per step
 constexpr int FA_D = 64;        // head dimension
 constexpr int FA_THREADS = 160; // warps 0-3 softmax (one row per thread), warp 4 TMA + MMA
 constexpr uint32_t FA_TILE_BYTES = FA_BLOCK * FA_D * 2;  // 16 KB
-constexpr uint32_t FA_SMEM = FA_TILE_BYTES * (1 + 2 + 2) + 2 * FA_TILE_BYTES /*P*/ + 1024 + 256;
+// 7 tiles + barriers = 114,944 B: with the 1 KB per-block reserve, two CTAs fit in 227 KB.
+constexpr uint32_t FA_SMEM = FA_TILE_BYTES * (1 + 2 + 2) + 2 * FA_TILE_BYTES /*P*/ + 256;
 
 struct FaParams {
     int B, T, H;
@@ -50,8 +51,8 @@ __device__ __forceinline__ uint32_t fa_idesc(int n, bool b_mn) {
 // softmax overlaps the other's MMAs and loads.
 __global__ void __launch_bounds__(FA_THREADS, 2)
 flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaParams p) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    extern __shared__ __align__(1024) uint8_t smem[];   // swizzled tiles need 1 KB alignment
+    if (threadIdx.x == 0 && (smem_u32(smem) & 1023u) != 0) __trap();
     uint8_t* s_q = smem;
     uint8_t* s_k = s_q + FA_TILE_BYTES;            // 2 stages
     uint8_t* s_v = s_k + 2 * FA_TILE_BYTES;        // 2 stages
