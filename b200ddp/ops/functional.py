@@ -430,17 +430,51 @@ def flash_attention_forward(qkv: torch.Tensor, n_head: int):
     return out, lse
 
 
+class _FlashAttention(torch.autograd.Function):
+    """Fused causal attention, forward and backward (csrc/flash_attention.cu): scores and
+    probabilities never leave TMEM / shared memory; only O and the per-row log-sum-exp are kept."""
+
+    @staticmethod
+    def forward(ctx, qkv, n_head):
+        if not qkv.is_contiguous():
+            qkv = qkv.contiguous()
+        out, lse = flash_attention_forward(qkv, n_head)
+        ctx.save_for_backward(qkv, out, lse)
+        ctx.n_head = n_head
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, out, lse = ctx.saved_tensors
+        H = ctx.n_head
+        Bs, T, C3 = qkv.shape
+        D = C3 // 3 // H
+        if not dout.is_contiguous():
+            dout = dout.contiguous()
+        dqkv = torch.empty_like(qkv)
+        dq_acc = torch.empty(Bs, H, T, D, dtype=torch.float32, device=qkv.device)
+        delta = torch.empty(Bs, H, T, dtype=torch.float32, device=qkv.device)
+        nat.check(nat.lib().b200_flash_attn_bwd(
+            qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(),
+            dq_acc.data_ptr(), delta.data_ptr(), Bs, T, H, D, nat.stream_ptr(qkv.device)),
+            "b200_flash_attn_bwd")
+        return dqkv, None
+
+
 def causal_attention(qkv: torch.Tensor, n_head: int) -> torch.Tensor:
-    """qkv [B, T, 3C] -> [B, T, C].  Own kernels on a B200 (B200DDP_ATTENTION=sdpa selects torch's
-    fused SDPA library kernel instead, for comparison); torch SDPA elsewhere."""
+    """qkv [B, T, 3C] -> [B, T, C].  On a B200: the fused flash-style tcgen05 kernels (head dim 64),
+    or the batched-GEMM + row-softmax path (B200DDP_ATTENTION=gemm, other head dims); both are
+    ours.  B200DDP_ATTENTION=sdpa selects torch's library kernel for comparison; torch SDPA on CPU."""
     Bsz, T, C3 = qkv.shape
     Cc = C3 // 3
     D = Cc // n_head
-    if (native_ok(qkv) and D % 64 == 0 and T % 128 == 0
-            and os.environ.get("B200DDP_ATTENTION", "native") != "sdpa"):
-        if D == 64 and not (torch.is_grad_enabled() and qkv.requires_grad):
-            return flash_attention_forward(qkv, n_head)[0]   # inference: scores stay on chip
-        return _CausalAttention.apply(qkv, n_head)
+    mode = os.environ.get("B200DDP_ATTENTION", "flash")   # flash | gemm | sdpa
+    if native_ok(qkv) and D % 64 == 0 and T % 128 == 0 and mode != "sdpa":
+        if D == 64 and mode == "flash":
+            if not (torch.is_grad_enabled() and qkv.requires_grad):
+                return flash_attention_forward(qkv, n_head)[0]
+            return _FlashAttention.apply(qkv, n_head)
+        return _CausalAttention.apply(qkv, n_head)   # batched causal GEMMs + row softmax kernels
     q, k, v = qkv.view(Bsz, T, 3, n_head, D).permute(2, 0, 3, 1, 4)
     y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
     return y.transpose(1, 2).reshape(Bsz, T, Cc)

@@ -1,4 +1,4 @@
-// Fused causal attention (flash-style) on tcgen05: forward.
+// Fused causal attention (flash-style) on tcgen05: forward and backward.
 //
 // For BASELINE.json config 4 (GPT-2 small, seq 1024, head dim 64).  ref: none in the
 // reference; its GPT-2 baseline reaches a library flash-attention kernel through torch SDPA.
@@ -238,6 +238,275 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaParam
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// Backward.  One CTA per (sequence, head, 128-key block j); it keeps K_j, V_j resident and
+// walks the query blocks i >= j (causal).  Five tensor-core products per step, all from the same
+// swizzled tiles read through K-major or MN-major descriptors (nothing is transposed):
+//     S  = Q_i K_j^T          dP = dO_i V_j^T                      -> TMEM (fresh)
+//     P = exp2(S*c - lse),  dS = P * (dP - delta) * scale          4 warps, one query row each,
+//                                                                  bf16 P and dS into smem
+//     dV_j += P^T dO_i        dK_j += dS^T Q_i                     -> TMEM (accumulate over i)
+//     dQ_i partial = dS K_j                                        -> TMEM -> fp32 vector atomics
+// TMEM: S 128 + dP 128 + dV 64 + dK 64 + dQ 64 = 448 of 512 columns.
+constexpr uint32_t FAB_SMEM = FA_TILE_BYTES * (2 + 4) + 4 * FA_TILE_BYTES /*P, dS*/ + 256;
+
+struct FaBwdParams {
+    int B, T, H;
+    const float* lse;     // [B, H, T]
+    const float* delta;   // [B, H, T]
+    float* dq_acc;        // [B, H, T, D] fp32, zeroed
+    __nv_bfloat16* dqkv;  // [B, T, 3, H, D]
+    float scale, scale_log2e;
+};
+
+__device__ __forceinline__ uint32_t fab_idesc(int n, bool a_mn, bool b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(a_mn ? 1 : 0) << 15) | ((uint32_t)(b_mn ? 1 : 0) << 16) |
+           ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+}
+
+__global__ void __launch_bounds__(FA_THREADS, 1)
+flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_constant__ CUtensorMap tma_do,
+                      const FaBwdParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if (threadIdx.x == 0 && (smem_u32(smem) & 1023u) != 0) __trap();
+    uint8_t* s_k = smem;                          // K_j
+    uint8_t* s_v = s_k + FA_TILE_BYTES;           // V_j
+    uint8_t* s_q = s_v + FA_TILE_BYTES;           // Q_i, 2 stages
+    uint8_t* s_do = s_q + 2 * FA_TILE_BYTES;      // dO_i, 2 stages
+    uint8_t* s_p = s_do + 2 * FA_TILE_BYTES;      // P   [128 q x 128 keys] as two swizzled blocks
+    uint8_t* s_ds = s_p + 2 * FA_TILE_BYTES;      // dS  same layout
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_ds + 2 * FA_TILE_BYTES);
+    uint64_t* kv_full = bars;         // 1
+    uint64_t* qdo_full = bars + 1;    // 2
+    uint64_t* qdo_empty = bars + 3;   // 2
+    uint64_t* sdp_full = bars + 5;    // 1
+    uint64_t* pds_full = bars + 6;    // 1 (128 arrivals)
+    uint64_t* dq_full = bars + 7;     // 1
+    uint64_t* dkv_full = bars + 8;    // 1
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nq = p.T / FA_BLOCK;
+    const int kj = blockIdx.x;                 // key block; block 0 has the most query blocks
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int niter = nq - kj;
+    const int k0 = kj * FA_BLOCK;
+
+    if (warp == 4 && lane == 0) {
+        tma_prefetch_desc(&tma_qkv);
+        tma_prefetch_desc(&tma_do);
+        mbar_init(kv_full, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
+        mbar_init(sdp_full, 1);
+        mbar_init(pds_full, FA_BLOCK);
+        mbar_init(dq_full, 1);
+        mbar_init(dkv_full, 1);
+        fence_mbar_init();
+    }
+    if (warp == 4) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t t_s = tmem_base, t_dp = tmem_base + 128, t_dv = tmem_base + 256, t_dk = tmem_base + 320,
+                   t_dq = tmem_base + 384;
+
+    if (warp == 4) {
+        if (lane == 0) {
+            auto load_qdo = [&](int it) {
+                const int st = it & 1, i = kj + it;
+                mbar_arrive_expect_tx(&qdo_full[st], 2 * FA_TILE_BYTES);
+                tma_load_4d(s_q + st * FA_TILE_BYTES, &tma_qkv, &qdo_full[st], 0, 0 * p.H + h, i * FA_BLOCK, b);
+                tma_load_4d(s_do + st * FA_TILE_BYTES, &tma_do, &qdo_full[st], 0, h, i * FA_BLOCK, b);
+            };
+            mbar_arrive_expect_tx(kv_full, 2 * FA_TILE_BYTES);
+            tma_load_4d(s_k, &tma_qkv, kv_full, 0, 1 * p.H + h, k0, b);
+            tma_load_4d(s_v, &tma_qkv, kv_full, 0, 2 * p.H + h, k0, b);
+            load_qdo(0);
+            if (niter > 1) load_qdo(1);
+            const uint32_t id_s = fab_idesc(128, false, false);   // S, dP: both operands K-major
+            const uint32_t id_kv = fab_idesc(64, true, true);     // dV, dK: both MN-major
+            const uint32_t id_dq = fab_idesc(64, false, true);    // dQ: dS K-major, K_j MN-major
+            const uint32_t ak = smem_u32(s_k), av = smem_u32(s_v), ap = smem_u32(s_p), ads = smem_u32(s_ds);
+            mbar_wait(kv_full, 0);
+            for (int it = 0; it < niter; ++it) {
+                const int st = it & 1;
+                const uint32_t par2 = (uint32_t)((it >> 1) & 1);
+                mbar_wait(&qdo_full[st], par2);
+                tc_fence_after();
+                const uint32_t aq = smem_u32(s_q + st * FA_TILE_BYTES), ado = smem_u32(s_do + st * FA_TILE_BYTES);
+#pragma unroll
+                for (int k = 0; k < FA_D / 16; ++k)
+                    umma_bf16(t_s, umma_smem_desc(aq + k * 32, 16, 1024), umma_smem_desc(ak + k * 32, 16, 1024), id_s,
+                              k != 0 ? 1u : 0u);
+#pragma unroll
+                for (int k = 0; k < FA_D / 16; ++k)
+                    umma_bf16(t_dp, umma_smem_desc(ado + k * 32, 16, 1024), umma_smem_desc(av + k * 32, 16, 1024), id_s,
+                              k != 0 ? 1u : 0u);
+                umma_commit(sdp_full);
+                mbar_wait(pds_full, (uint32_t)(it & 1));   // P and dS are in smem, S/dP consumed
+                tc_fence_after();
+#pragma unroll
+                for (int kk = 0; kk < FA_BLOCK / 16; ++kk) {   // reduce over the 128 query rows
+                    // A^T views of P / dS: [q rows, keys] read MN-major (64-key chunks 16 KB apart)
+                    umma_bf16(t_dv, umma_smem_desc(ap + kk * 2048, 16384, 1024), umma_smem_desc(ado + kk * 2048, 8192, 1024),
+                              id_kv, (it | kk) != 0 ? 1u : 0u);
+                    umma_bf16(t_dk, umma_smem_desc(ads + kk * 2048, 16384, 1024), umma_smem_desc(aq + kk * 2048, 8192, 1024),
+                              id_kv, (it | kk) != 0 ? 1u : 0u);
+                }
+#pragma unroll
+                for (int kk = 0; kk < FA_BLOCK / 16; ++kk)     // reduce over the 128 keys
+                    umma_bf16(t_dq, umma_smem_desc(ads + (kk >> 2) * FA_TILE_BYTES + (kk & 3) * 32, 16, 1024),
+                              umma_smem_desc(ak + kk * 2048, 8192, 1024), id_dq, kk != 0 ? 1u : 0u);
+                umma_commit(dq_full);
+                umma_commit(&qdo_empty[st]);
+                if (it + 2 < niter) {
+                    mbar_wait(&qdo_empty[st], par2);
+                    load_qdo(it + 2);
+                }
+            }
+            umma_commit(dkv_full);
+        }
+    } else {
+        const int r = threadIdx.x;
+        const uint32_t lane_addr = ((uint32_t)(warp * 32)) << 16;
+        const int64_t bh = (int64_t)b * p.H + h;
+        for (int it = 0; it < niter; ++it) {
+            const int i = kj + it;
+            const bool diag = (it == 0);
+            const int64_t qrow = bh * p.T + (int64_t)i * FA_BLOCK + r;
+            const float lse2 = p.lse[qrow] * 1.4426950408889634f;
+            const float dlt = p.delta[qrow];
+            mbar_wait(sdp_full, (uint32_t)(it & 1));
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < FA_BLOCK / 32; ++c) {
+                uint32_t vs[32], vd[32];
+                tmem_ld_32x32(t_s + lane_addr + c * 32, vs);
+                tmem_ld_32x32(t_dp + lane_addr + c * 32, vd);
+                tmem_ld_wait();
+                float pv[32], dv[32];
+#pragma unroll
+                for (int e = 0; e < 32; ++e) {
+                    const float pe = fa_exp2(__uint_as_float(vs[e]) * p.scale_log2e - lse2);
+                    const bool ok = !diag || c * 32 + e <= r;   // key column <= query row
+                    pv[e] = ok ? pe : 0.f;
+                    dv[e] = ok ? pe * (__uint_as_float(vd[e]) - dlt) * p.scale : 0.f;
+                }
+                uint8_t* bp = s_p + (c >> 1) * FA_TILE_BYTES + r * 128;
+                uint8_t* bd = s_ds + (c >> 1) * FA_TILE_BYTES + r * 128;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int off = (((c & 1) * 4 + t) ^ (r & 7)) << 4;
+                    *reinterpret_cast<uint4*>(bp + off) =
+                        make_uint4(pack_bf16(pv[8 * t], pv[8 * t + 1]), pack_bf16(pv[8 * t + 2], pv[8 * t + 3]),
+                                   pack_bf16(pv[8 * t + 4], pv[8 * t + 5]), pack_bf16(pv[8 * t + 6], pv[8 * t + 7]));
+                    *reinterpret_cast<uint4*>(bd + off) =
+                        make_uint4(pack_bf16(dv[8 * t], dv[8 * t + 1]), pack_bf16(dv[8 * t + 2], dv[8 * t + 3]),
+                                   pack_bf16(dv[8 * t + 4], dv[8 * t + 5]), pack_bf16(dv[8 * t + 6], dv[8 * t + 7]));
+                }
+            }
+            fence_proxy_async();
+            tc_fence_before();
+            mbar_arrive(pds_full);
+            // dQ_i partial -> fp32 accumulator (other key blocks add to the same rows)
+            mbar_wait(dq_full, (uint32_t)(it & 1));
+            tc_fence_after();
+            float* dq = p.dq_acc + qrow * FA_D;
+#pragma unroll
+            for (int c = 0; c < FA_D / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32(t_dq + lane_addr + c * 32, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 32; e += 4)
+                    atomicAdd(reinterpret_cast<float4*>(dq + c * 32 + e),
+                              make_float4(__uint_as_float(v[e]), __uint_as_float(v[e + 1]), __uint_as_float(v[e + 2]),
+                                          __uint_as_float(v[e + 3])));
+            }
+            tc_fence_before();
+        }
+        // dV_j, dK_j: thread r owns key row k0 + r
+        mbar_wait(dkv_full, 0);
+        tc_fence_after();
+        const int64_t row3 = ((int64_t)b * p.T + k0 + r) * 3;
+        __nv_bfloat16* dk_dst = p.dqkv + (row3 + 1) * ((int64_t)p.H * FA_D) + (int64_t)h * FA_D;
+        __nv_bfloat16* dv_dst = p.dqkv + (row3 + 2) * ((int64_t)p.H * FA_D) + (int64_t)h * FA_D;
+#pragma unroll
+        for (int which = 0; which < 2; ++which) {
+            const uint32_t taddr = (which == 0 ? t_dk : t_dv) + lane_addr;
+            __nv_bfloat16* dst = which == 0 ? dk_dst : dv_dst;
+#pragma unroll
+            for (int c = 0; c < FA_D / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32(taddr + c * 32, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 32; e += 8)
+                    *reinterpret_cast<uint4*>(dst + c * 32 + e) = make_uint4(
+                        pack_bf16(__uint_as_float(v[e]), __uint_as_float(v[e + 1])),
+                        pack_bf16(__uint_as_float(v[e + 2]), __uint_as_float(v[e + 3])),
+                        pack_bf16(__uint_as_float(v[e + 4]), __uint_as_float(v[e + 5])),
+                        pack_bf16(__uint_as_float(v[e + 6]), __uint_as_float(v[e + 7])));
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]   (one thread per (b,t,h) row of 64)
+__global__ void __launch_bounds__(256) fa_delta_kernel(const __nv_bfloat16* __restrict__ out,
+                                                       const __nv_bfloat16* __restrict__ dout,
+                                                       float* __restrict__ delta, int B, int T, int H) {
+    const int64_t n = (int64_t)B * T * H;
+    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (int64_t)gridDim.x * blockDim.x) {
+        const int hh = (int)(idx % H);
+        const int64_t bt = idx / H;
+        const int t = (int)(bt % T);
+        const int bb = (int)(bt / T);
+        const uint4* po = reinterpret_cast<const uint4*>(out + idx * FA_D);
+        const uint4* pd = reinterpret_cast<const uint4*>(dout + idx * FA_D);
+        float acc = 0.f;
+#pragma unroll
+        for (int v = 0; v < FA_D / 8; ++v) {
+            const uint4 a = po[v], d = pd[v];
+            const uint32_t wa[4] = {a.x, a.y, a.z, a.w}, wd[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 fa = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wa[q]));
+                const float2 fd = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wd[q]));
+                acc += fa.x * fd.x + fa.y * fd.y;
+            }
+        }
+        delta[((int64_t)bb * H + hh) * T + t] = acc;
+    }
+}
+
+// dq_acc [B,H,T,D] fp32 -> dqkv[b,t,0,h,:] bf16
+__global__ void __launch_bounds__(256) fa_dq_convert_kernel(const float* __restrict__ dq_acc,
+                                                            __nv_bfloat16* __restrict__ dqkv, int B, int T, int H) {
+    const int64_t nvec = (int64_t)B * H * T * (FA_D / 8);
+    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < nvec; idx += (int64_t)gridDim.x * blockDim.x) {
+        const int v = (int)(idx % (FA_D / 8));
+        int64_t r = idx / (FA_D / 8);
+        const int t = (int)(r % T); r /= T;
+        const int hh = (int)(r % H);
+        const int bb = (int)(r / H);
+        const float4 a = reinterpret_cast<const float4*>(dq_acc)[idx * 2], c = reinterpret_cast<const float4*>(dq_acc)[idx * 2 + 1];
+        __nv_bfloat16* dst = dqkv + (((int64_t)bb * T + t) * 3 + 0) * ((int64_t)H * FA_D) + (int64_t)hh * FA_D + v * 8;
+        *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(c.x, c.y), pack_bf16(c.z, c.w));
+    }
+}
+
 typedef CUresult (*FaEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -282,6 +551,8 @@ static int fa_bind_ctx() {
 int b200_flash_init() {
     B200_CUDA_OK(cudaFuncSetAttribute(b200::flash_attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)b200::FA_SMEM));
+    B200_CUDA_OK(cudaFuncSetAttribute(b200::flash_attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)b200::FAB_SMEM));
     return 0;
 }
 
@@ -301,6 +572,35 @@ extern "C" int b200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B
     dim3 grid((unsigned)(T / FA_BLOCK), (unsigned)H, (unsigned)B);
     flash_attn_fwd_kernel<<<grid, FA_THREADS, FA_SMEM, (cudaStream_t)stream>>>(map, p);
     b200_count_launch(1);
+    B200_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int b200_flash_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                                   float* dq_acc, float* delta, int B, int T, int H, int D, void* stream) {
+    using namespace b200;
+    B200_REQUIRE(qkv && out && dout && lse && dqkv && dq_acc && delta, "flash_attn_bwd: null pointer");
+    B200_REQUIRE(D == FA_D, "flash_attn_bwd: head dimension must be %d (got %d)", FA_D, D);
+    B200_REQUIRE(T > 0 && T % FA_BLOCK == 0, "flash_attn_bwd: T must be a multiple of %d", FA_BLOCK);
+    B200_REQUIRE(B > 0 && H > 0 && H <= 65535 && B <= 65535, "flash_attn_bwd: bad batch/heads");
+    if (int rc = fa_bind_ctx()) return rc;
+    static int inited = b200_flash_init();
+    if (inited) return inited;
+    CUtensorMap map_qkv, map_do;
+    if (int rc = fa_make_map(&map_qkv, qkv, B, T, H, 3)) return rc;
+    if (int rc = fa_make_map(&map_do, dout, B, T, H, 1)) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t rows = (int64_t)B * T * H;
+    B200_CUDA_OK(cudaMemsetAsync(dq_acc, 0, (size_t)rows * FA_D * sizeof(float), s));
+    int blocks = (int)((rows + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    fa_delta_kernel<<<blocks, 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, B, T, H);
+    const float scale = 1.f / sqrtf((float)D);
+    FaBwdParams p{B, T, H, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, scale, scale * 1.4426950408889634f};
+    dim3 grid((unsigned)(T / FA_BLOCK), (unsigned)H, (unsigned)B);
+    flash_attn_bwd_kernel<<<grid, FA_THREADS, FAB_SMEM, s>>>(map_qkv, map_do, p);
+    fa_dq_convert_kernel<<<148 * 8, 256, 0, s>>>(dq_acc, (__nv_bfloat16*)dqkv, B, T, H);
+    b200_count_launch(3);
     B200_CUDA_OK(cudaGetLastError());
     return 0;
 }

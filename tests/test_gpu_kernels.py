@@ -483,10 +483,13 @@ def test_gemm_split_k(B):
         assert rel_err(out, want) < 1e-4, (M, N, K, rel_err(out, want))
 
 
-@pytest.mark.parametrize("Bs,H,T,D", [(2, 4, 256, 64), (1, 12, 1024, 64), (3, 2, 128, 128)])
-def test_causal_attention_own_kernels(Bs, H, T, D):
-    """Batched causal tcgen05 GEMMs + row softmax kernels vs fp32 SDPA, forward and backward."""
+@pytest.mark.parametrize("mode", ["flash", "gemm"])
+@pytest.mark.parametrize("Bs,H,T,D", [(2, 4, 256, 64), (1, 12, 1024, 64), (3, 2, 128, 128), (1, 1, 128, 64)])
+def test_causal_attention_own_kernels(Bs, H, T, D, mode, monkeypatch):
+    """Both own attention paths vs fp32 SDPA, forward and backward: the fused flash-style tcgen05
+    kernels (head dim 64) and the batched causal GEMMs + row softmax kernels."""
     from b200ddp.ops import functional as Fn
+    monkeypatch.setenv("B200DDP_ATTENTION", mode)
     torch.manual_seed(18)
     dev = torch.device("cuda")
     C = H * D
