@@ -60,6 +60,47 @@ def _colsum_into(x2: torch.Tensor, out: torch.Tensor) -> None:
                             nat.stream_ptr(x2.device)), "b200_colsum")
 
 
+_side_streams = {}
+
+
+class _AsyncBiasGrad:
+    """Bias gradient (column sum of dy) on a side stream, so this DRAM-bound reduction overlaps
+    the tensor-core-bound dgrad/wgrad GEMMs of the same layer.  `join()` re-joins the streams,
+    signals the bucket and returns what autograd should see."""
+
+    def __init__(self, b: torch.Tensor, dy2: torch.Tensor):
+        dev = dy2.device
+        key = dev.index
+        if key not in _side_streams:
+            _side_streams[key] = (torch.cuda.Stream(dev), {})
+        self.side, scratch = _side_streams[key]
+        self.b = b
+        self.dst = getattr(b, "_b200_grad", None)
+        self.owned = self.dst is not None
+        if not self.owned:
+            self.dst = torch.empty_like(b)
+        L = nat.lib()
+        rows, cols = dy2.shape
+        need = int(L.b200_colsum_scratch_bytes(rows, cols))
+        slot = scratch.get("buf")
+        if slot is None or slot.numel() < need:
+            slot = scratch["buf"] = torch.empty(max(need, 4 << 20), dtype=torch.uint8, device=dev)
+        cur = torch.cuda.current_stream(dev)
+        self.side.wait_stream(cur)
+        dy2.record_stream(self.side)
+        with torch.cuda.stream(self.side):
+            nat.check(L.b200_colsum(dy2.data_ptr(), dy2.stride(0), rows, cols, self.dst.data_ptr(),
+                                    int(self.dst.dtype == torch.bfloat16), slot.data_ptr(),
+                                    nat.stream_ptr(dev)), "b200_colsum")
+
+    def join(self):
+        torch.cuda.current_stream(self.dst.device).wait_stream(self.side)
+        if self.owned:
+            self.b._b200_ready()
+            return None
+        return self.dst
+
+
 def _emit_param_grad(p: torch.Tensor, compute_into, signal: bool = True):
     """Runs compute_into(dst) with dst = the arena view when the engine owns p (returns None so
     autograd does not accumulate), else into a fresh tensor that is returned to autograd."""
@@ -117,13 +158,14 @@ class _Linear(torch.autograd.Function):
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         M = dy2.shape[0]
+        bias_job = _AsyncBiasGrad(b, dy2) if b is not None else None   # overlaps the GEMMs below
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty(M, K, dtype=torch.bfloat16, device=dy.device)
             B.gemm(dy2, w, dx, M=M, N=K, K=N, b_mn_major=True)  # W stored [N_out, K_in] = [K, N]
             dx = dx.view(ctx.x_shape)
         gw = _emit_param_grad(w, lambda dst: _wgrad_into(dy2, x2, dst))
-        gb = _emit_param_grad(b, lambda dst: _colsum_into(dy2, dst)) if b is not None else None
+        gb = bias_job.join() if bias_job is not None else None
         return dx, gw, gb, (dy if ctx.has_res else None)
 
 
@@ -175,18 +217,20 @@ class _MLP(torch.autograd.Function):
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         M = dy2.shape[0]
+        bp_job = _AsyncBiasGrad(b_proj, dy2)   # side stream: overlaps the GEMMs below
         # dz = (dy @ Wproj) * gelu'(z): dgrad GEMM with the gate in its epilogue
         dz = torch.empty(M, H, dtype=torch.bfloat16, device=dy.device)
         B.gemm(dy2, w_proj, dz, M=M, N=H, K=C_out, b_mn_major=True, epilogue=B.EPI_GELU_BWD, aux=z)
+        bf_job = _AsyncBiasGrad(b_fc, dz)
         g_wp = _emit_param_grad(w_proj, lambda dst: _wgrad_into(dy2, h, dst))
-        g_bp = _emit_param_grad(b_proj, lambda dst: _colsum_into(dy2, dst))
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty(M, C_in, dtype=torch.bfloat16, device=dy.device)
             B.gemm(dz, w_fc, dx, M=M, N=C_in, K=H, b_mn_major=True)
             dx = dx.view(ctx.x_shape)
         g_wf = _emit_param_grad(w_fc, lambda dst: _wgrad_into(dz, x2, dst))
-        g_bf = _emit_param_grad(b_fc, lambda dst: _colsum_into(dz, dst))
+        g_bp = bp_job.join()
+        g_bf = bf_job.join()
         return dx, g_wf, g_bf, g_wp, g_bp, (dy if ctx.has_res else None)
 
 
