@@ -40,7 +40,7 @@ dev = torch.device("cuda", local)
 eng = DataParallel(SimpleNet().to(dev), backend="b200", compute_dtype=torch.bfloat16)
 x = torch.randn(64, 784, device=dev); y = torch.randint(0, 10, (64,), device=dev)
 eng.train_step(x, y); torch.cuda.synchronize()
-print("STEP_OK", rank, flush=True)
+print(f"STEP_OK {rank}", flush=True)
 if rank == 1:
     os._exit(3)                       # dies between steps
 t0 = time.time()

@@ -102,7 +102,7 @@ def test_supervisor_propagates_first_failure(tmp_path):
 
 def test_supervisor_success(tmp_path):
     script = tmp_path / "ok.py"
-    script.write_text("import os; print('hello', os.environ['RANK'], os.environ['WORLD_SIZE'])\n")
+    script.write_text("import os; print('hello %s %s' % (os.environ['RANK'], os.environ['WORLD_SIZE']), flush=True)\n")
     r = subprocess.run([sys.executable, "-m", "b200ddp.launch", "--nproc-per-node=2", str(script)],
                        cwd=ROOT, capture_output=True, text=True, timeout=60)
     assert r.returncode == 0

@@ -88,7 +88,7 @@ for _ in range(4):
 got = [torch.empty_like(eng.master) for _ in range(world)]
 dist.all_gather(got, eng.master)
 assert all(torch.equal(got[0], g) for g in got), "replicas diverged"
-print("IDENTICAL", rank)
+print(f"IDENTICAL {rank}", flush=True)
 """)
     cmd = [sys.executable, "-m", "b200ddp.launch", "--nproc-per-node=2",
            f"--master-port={free_port()}", str(script)]
@@ -128,7 +128,7 @@ got = [torch.empty_like(eng._buffer_arenas[0]) for _ in range(world)]
 # batch mean on top of 0.9 * 10.0 on every rank
 rm = net[1].running_mean
 assert torch.all((rm - 9.0).abs() < 1.0), rm
-print("K4_OK", rank)
+print(f"K4_OK {rank}", flush=True)
 """)
     cmd = [sys.executable, "-m", "b200ddp.launch", "--nproc-per-node=2",
            f"--master-port={free_port()}", str(script)]
