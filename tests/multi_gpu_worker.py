@@ -63,14 +63,23 @@ def check_fused_optimizer(rank, world, dev, compute_dtype, two_shot, kind):
     ref = DataParallel(copy.deepcopy(net), optimizer=kind, lr=1e-2, backend="nccl",
                        compute_dtype=compute_dtype, use_program=False)
     assert torch.equal(eng.master, ref.master)
-    nvls_bf16 = bool(two_shot and compute_dtype == torch.bfloat16 and eng.symm.nvls)
-    rtol, atol = (2e-3, 3e-4) if nvls_bf16 else (3e-6, 2e-6)
+    nvls = bool(two_shot and eng.symm.nvls and world > 2)
+    nvls_bf16 = nvls and compute_dtype == torch.bfloat16
+    # in-switch reduction order is the hardware's: fp32 differs in the last bits (amplified by
+    # Adam's normalisation), bf16 additionally rounds the sum
+    rtol, atol = (5e-3, 2e-3) if nvls_bf16 else ((1e-4, 1e-5) if nvls else (3e-6, 2e-6))
     for step in range(3):
         torch.manual_seed(77 * rank + step)
         g = torch.randn(eng.layout.total, device=dev)
         eng.grad.copy_(g); ref.grad.copy_(g)
         # reference: NCCL sum, then the torch-op update
-        gsum = ref.grad.float().clone(); dist.all_reduce(gsum)
+        # reference sum in the kernels' order (rank 0..W-1, fp32): gather then add, so the P2P
+        # paths can be held to a tight tolerance whatever algorithm NCCL would pick
+        parts = [torch.empty_like(ref.grad) for _ in range(world)]
+        dist.all_gather(parts, ref.grad)
+        gsum = parts[0].float().clone()
+        for part in parts[1:]:
+            gsum += part.float()
         if nvls_bf16:  # the switch returns the fp32-accumulated sum rounded to bf16
             gsum = gsum.to(torch.bfloat16).float()
         ref.grad.copy_(gsum) if ref.grad.dtype == torch.float32 else None
@@ -90,8 +99,9 @@ def check_fused_optimizer(rank, world, dev, compute_dtype, two_shot, kind):
     assert torch.allclose(eng.master, ref.master, rtol=rtol, atol=atol), rel(eng.master, ref.master)
     # in-switch bf16 reduction rounds more than one fp32 accumulation would (hardware property,
     # same class of error as an NCCL bf16 all-reduce): the moments get a looser bound
-    assert torch.allclose(eng.optimizer.exp_avg, ref.optimizer.exp_avg, rtol=2e-2 if nvls_bf16 else rtol,
-                          atol=5e-3 if nvls_bf16 else atol)
+    # (the SGD momentum buffer holds raw gradient sums, so it sees the full in-switch rounding)
+    assert torch.allclose(eng.optimizer.exp_avg, ref.optimizer.exp_avg, rtol=3e-2 if nvls_bf16 else rtol,
+                          atol=3e-2 if nvls_bf16 else atol)
     if eng.shadow is not None:
         assert torch.equal(eng.shadow, eng.master.to(torch.bfloat16))
     got = [torch.empty_like(eng.master) for _ in range(world)]
@@ -104,7 +114,7 @@ def check_fused_optimizer(rank, world, dev, compute_dtype, two_shot, kind):
     sd = eng.optimizer.state_dict()
     if kind != "sgd":
         assert float(sd["state"][0]["step"]) == 3.0
-    algo = ("NVLS" if eng.symm.nvls else "two-shot") if two_shot else "one-shot"
+    algo = ("NVLS" if nvls else "two-shot") if two_shot else "one-shot"
     log(f"fused all-reduce+{kind}: {algo} "
         f"{str(compute_dtype).split('.')[-1]} matches NCCL + torch-op update; replicas identical")
 
