@@ -17,7 +17,7 @@ void b200_count_launch(int n);
 namespace b200 {
 
 constexpr int BN_THREADS = 256;
-constexpr int BN_MAX_BLOCKS = 296;
+constexpr int BN_MAX_BLOCKS = 592;   // 4 resident blocks per SM
 
 __device__ __forceinline__ void bn_unpack8(const uint4& raw, float (&f)[8]) {
     const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
@@ -52,6 +52,7 @@ __global__ void __launch_bounds__(BN_THREADS) bn_reduce_kernel(
         for (int k = 0; k < 8; ++k) { mu[k] = mean[v * 8 + k]; rs[k] = rstd[v * 8 + k]; }
     }
     if (rl < lanes_r) {
+#pragma unroll 4
         for (int64_t row = (int64_t)blockIdx.x * lanes_r + rl; row < rows; row += (int64_t)gridDim.x * lanes_r) {
             const int64_t idx = row * cv + v;
             float f[8];
@@ -149,6 +150,8 @@ __global__ void __launch_bounds__(256) bn_finalize_bwd_kernel(const float* __res
 
 // y = relu?( (x - mean) * rstd * gamma + beta (+ residual) ).  In inference `rstd` already holds
 // rsqrt(running_var + eps) and `mean` the running mean.
+// The grid stride is a multiple of C/8 (C is a power of two <= 2048, the stride a multiple of
+// 256), so every thread stays on the same 8 channels: their scale/shift live in registers.
 __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ x,
                                                        const __nv_bfloat16* __restrict__ residual,
                                                        __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
@@ -156,15 +159,19 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
                                                        const float* __restrict__ beta, int64_t total_vecs, int C, int relu) {
     const int cv = C >> 3;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_vecs; i += stride) {
-        const int c0 = (int)(i % cv) * 8;
+    const int64_t first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int c0 = (int)(first % cv) * 8;
+    float sc[8], sh[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        sc[k] = rstd[c0 + k] * gamma[c0 + k];
+        sh[k] = beta[c0 + k] - mean[c0 + k] * sc[k];
+    }
+    for (int64_t i = first; i < total_vecs; i += stride) {
         float f[8];
         bn_unpack8(reinterpret_cast<const uint4*>(x)[i], f);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const float sc = __ldg(rstd + c0 + k) * __ldg(gamma + c0 + k);
-            f[k] = (f[k] - __ldg(mean + c0 + k)) * sc + __ldg(beta + c0 + k);
-        }
+        for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], sc[k], sh[k]);
         if (residual) {
             float r[8];
             bn_unpack8(reinterpret_cast<const uint4*>(residual)[i], r);
@@ -180,7 +187,10 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __re
 }
 
 // dx = gamma * rstd * (g - sum_g/rows - xhat * sum_gxhat/rows), g = dy * [y > 0] when relu;
-// dres (optional) = g: the gradient of the fused residual branch.
+// dres (optional) = g: the gradient of the fused residual branch.  Per-channel terms are
+// folded into three register constants per channel (same channel-invariance as above):
+//   dx = a * g + b2 * x + c,  a = gamma*rstd,  b2 = -a*rstd*q,  c = a*(rstd*mean*q - s)
+// with s = sum_g/rows, q = sum_gxhat/rows.
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
     const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
     const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
@@ -188,8 +198,18 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
     int64_t total_vecs, int C, float inv_rows, int relu) {
     const int cv = C >> 3;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_vecs; i += stride) {
-        const int c0 = (int)(i % cv) * 8;
+    const int64_t first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int c0 = (int)(first % cv) * 8;
+    float ka[8], kb[8], kc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const float rs = rstd[c0 + k], mu = mean[c0 + k];
+        const float sg = sums[c0 + k] * inv_rows, sq = sums[C + c0 + k] * inv_rows;
+        ka[k] = gamma[c0 + k] * rs;
+        kb[k] = -ka[k] * rs * sq;
+        kc[k] = ka[k] * (rs * mu * sq - sg);
+    }
+    for (int64_t i = first; i < total_vecs; i += stride) {
         float g[8], xv[8], o[8];
         bn_unpack8(reinterpret_cast<const uint4*>(dy)[i], g);
         bn_unpack8(reinterpret_cast<const uint4*>(x)[i], xv);
@@ -200,12 +220,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
             for (int k = 0; k < 8; ++k) g[k] = yv[k] > 0.f ? g[k] : 0.f;
         }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const float rs = __ldg(rstd + c0 + k);
-            const float xh = (xv[k] - __ldg(mean + c0 + k)) * rs;
-            o[k] = __ldg(gamma + c0 + k) * rs *
-                   (g[k] - __ldg(sums + c0 + k) * inv_rows - xh * __ldg(sums + C + c0 + k) * inv_rows);
-        }
+        for (int k = 0; k < 8; ++k) o[k] = fmaf(ka[k], g[k], fmaf(kb[k], xv[k], kc[k]));
         reinterpret_cast<uint4*>(dx)[i] = bn_pack8(o);
         if (dres) reinterpret_cast<uint4*>(dres)[i] = bn_pack8(g);
     }

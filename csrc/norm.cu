@@ -190,6 +190,7 @@ __global__ void __launch_bounds__(256) colsum_stage1_kernel(const __nv_bfloat16*
     const int64_t r1 = r0 + rows_per < rows ? r0 + rows_per : rows;
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (c0 + 8 <= cols && (ld & 7) == 0) {
+#pragma unroll 4
         for (int64_t r = r0; r < r1; ++r) {
             float v[8];
             unpack8(*reinterpret_cast<const uint4*>(x + r * ld + c0), v);
@@ -273,7 +274,7 @@ extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gam
 
 extern "C" int64_t b200_colsum_scratch_bytes(int64_t rows, int cols) {
     (void)rows;
-    return 64 * (int64_t)((cols + 7) / 8 * 8) * (int64_t)sizeof(float);
+    return 512 * (int64_t)((cols + 7) / 8 * 8) * (int64_t)sizeof(float);
 }
 
 extern "C" int b200_colsum(const void* x, int64_t ld, int64_t rows, int cols, void* out, int out_bf16,
@@ -281,8 +282,13 @@ extern "C" int b200_colsum(const void* x, int64_t ld, int64_t rows, int cols, vo
     using namespace b200;
     B200_REQUIRE(x && out && scratch && rows > 0 && cols > 0 && ld >= cols, "colsum: bad arguments");
     const int64_t pstride = (cols + 7) / 8 * 8;
-    int chunks = (int)((rows + 127) / 128);
-    if (chunks > 64) chunks = 64;
+    // enough row chunks to put ~4 blocks on every SM (the stage is latency-bound otherwise)
+    const int col_blocks = (int)((pstride / 8 + 255) / 256);
+    int chunks = (int)((rows + 31) / 32);
+    const int want = (148 * 4 + col_blocks - 1) / col_blocks;
+    if (chunks > want) chunks = want;
+    if (chunks > 512) chunks = 512;
+    if (chunks < 1) chunks = 1;
     const int64_t rows_per = (rows + chunks - 1) / chunks;
     dim3 grid((unsigned)((pstride / 8 + 255) / 256), (unsigned)chunks);
     cudaStream_t s = (cudaStream_t)stream;
