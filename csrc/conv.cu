@@ -24,26 +24,36 @@ struct ConvGeom {
     int stride, pad;
 };
 
-// col[(n,p,q), (r,s,c)]; one thread moves 8 channels (16 B).
+// col[(n,p,q), (r,s,c)].  One thread owns 8 channels (16 B) of one output pixel and walks the
+// R*S taps: the pixel decomposition (three integer divisions) is paid once per R*S vectors, and
+// the taps' loads are independent, so several are in flight per thread.
 __global__ void __launch_bounds__(256) im2col_kernel(const __nv_bfloat16* __restrict__ x,
                                                      __nv_bfloat16* __restrict__ col, ConvGeom g,
-                                                     int64_t total_vecs) {
+                                                     int64_t total_items) {
     const int cv = g.C >> 3;  // vectors per pixel
+    const int taps = g.R * g.S;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_vecs; i += stride) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_items; i += stride) {
         int64_t t = i;
         const int c8 = (int)(t % cv); t /= cv;
-        const int s = (int)(t % g.S); t /= g.S;
-        const int r = (int)(t % g.R); t /= g.R;
+        const int64_t pix = t;
         const int q = (int)(t % g.Q); t /= g.Q;
         const int p = (int)(t % g.P); t /= g.P;
         const int n = (int)t;
-        const int h = p * g.stride + r - g.pad;
-        const int w = q * g.stride + s - g.pad;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (h >= 0 && h < g.H && w >= 0 && w < g.W)
-            v = reinterpret_cast<const uint4*>(x)[(((int64_t)n * g.H + h) * g.W + w) * cv + c8];
-        reinterpret_cast<uint4*>(col)[i] = v;  // i enumerates col in exactly this order
+        const int h0 = p * g.stride - g.pad, w0 = q * g.stride - g.pad;
+        uint4* dst = reinterpret_cast<uint4*>(col) + (pix * taps) * cv + c8;
+        const uint4* src = reinterpret_cast<const uint4*>(x) + ((int64_t)n * g.H * g.W) * cv + c8;
+        for (int r = 0; r < g.R; ++r) {
+            const int h = h0 + r;
+            const bool hok = h >= 0 && h < g.H;
+#pragma unroll 4
+            for (int s2 = 0; s2 < g.S; ++s2) {
+                const int w = w0 + s2;
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (hok && w >= 0 && w < g.W) v = src[((int64_t)h * g.W + w) * cv];
+                dst[(int64_t)(r * g.S + s2) * cv] = v;
+            }
+        }
     }
 }
 
@@ -119,7 +129,7 @@ extern "C" int b200_im2col(const void* x, void* col, int N, int H, int W, int C,
     B200_REQUIRE(x && col, "im2col: null pointer");
     ConvGeom g;
     if (int rc = make_geom(&g, N, H, W, C, R, S, stride, pad)) return rc;
-    const int64_t vecs = (int64_t)N * g.P * g.Q * R * S * (C / 8);
+    const int64_t vecs = (int64_t)N * g.P * g.Q * (C / 8);   // one thread item = 8 channels of a pixel
     im2col_kernel<<<conv_grid(vecs), 256, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)x, (__nv_bfloat16*)col, g, vecs);
     b200_count_launch(1);
