@@ -46,6 +46,7 @@ class GemmDesc(C.Structure):
         ("causal", C.c_int),
         ("tile_m", C.c_int),
         ("split_k", C.c_int),
+        ("cta_pair", C.c_int),
     ]
 
 
@@ -173,7 +174,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, M: int, N: int,
          targets: Optional[torch.Tensor] = None, ce_grad_scale: float = 1.0,
          loss_out: Optional[torch.Tensor] = None, loss_scale: float = 1.0,
          ce_write_grad: bool = True, tile_n: int = 0, max_ctas: int = 0, split_k: int = 0,
-         batch=None, causal: int = 0, lda=None, ldb=None, ldd=None, tile_m: int = 0) -> None:
+         batch=None, causal: int = 0, lda=None, ldb=None, ldd=None, tile_m: int = 0,
+         cta_pair: int = 0) -> None:
     """out[M,N] = epilogue(A @ B^T).  A is [M,K] (K-major) or stored [K,M] (a_mn_major);
     B is [N,K] or stored [K,N] (b_mn_major).  Strides are taken from the tensors."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
@@ -195,6 +197,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, M: int, N: int,
             (d.d_stride_inner, d.d_stride_outer) = batch[2], batch[3], batch[4]
     d.causal = causal
     d.tile_m = tile_m
+    d.cta_pair = cta_pair
     d.bias = _ptr(bias)
     d.epilogue = epilogue
     d.aux, d.ldaux = _ptr(aux), (aux.stride(0) if aux is not None else 0)

@@ -8,15 +8,19 @@
 // GELU fwd/bwd, residual add, bias-gradient column sums and, for the classifier
 // layer, the whole softmax cross-entropy forward+backward.
 //
-// Structure (persistent, one CTA per SM, 192 threads):
+// Structure (persistent, one CTA per SM, 320 threads):
 //   warp 0      TMA producer: cp.async.bulk.tensor tiles of A and B into a
 //               STAGES-deep ring of 128B-swizzled shared memory, mbarrier tx-count.
 //   warp 1      MMA issuer: one thread issues tcgen05.mma (M=128, N=BN, K=16) from
 //               shared-memory descriptors into a TMEM accumulator; tcgen05.commit
 //               frees ring slots and publishes finished accumulators.
-//   warps 2..5  epilogue: tcgen05.ld the accumulator (one row per thread), apply
-//               the fused epilogue, store.  TMEM holds two accumulators so the
-//               epilogue of tile i overlaps the MMAs of tile i+1.
+//   warps 2..9  epilogue: tcgen05.ld the accumulator (one row per thread, two warps per
+//               TMEM lane quarter splitting the columns), apply the fused epilogue,
+//               store.  TMEM holds two accumulators so the epilogue of tile i overlaps
+//               the MMAs of tile i+1.  The tile's bias slice is staged in shared memory
+//               and the aux operand is fetched one chunk ahead: with one warp per
+//               scheduler every exposed load latency is paid in full (ncu: the bias
+//               loads were 38 % of all stall samples at K = 768).
 //
 // Operand layouts: K-major (reduction index contiguous: activations [M,K],
 // nn.Linear weights [N,K]) and MN-major (stored [K,M] / [K,N]) are both native —
@@ -35,7 +39,12 @@ namespace b200 {
 
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 B = one swizzle row
-constexpr int GEMM_THREADS = 192;
+// TMA warp + MMA warp + epilogue warps.  The general kernels run 4 epilogue warps (one per TMEM
+// lane quarter, up to 255 registers each for the dropout / cross-entropy / column-sum paths); the
+// FAST kernels (plain, bias, residual, GELU forward/backward with bf16 output) run 8 lean ones.
+template <bool FAST> struct EpiWarps { static constexpr int value = FAST ? 8 : 4; };
+template <bool FAST> constexpr int gemm_threads() { return 64 + 32 * EpiWarps<FAST>::value; }
+constexpr int BIAS_SMEM_BYTES = 2 * 256 * 4;  // per-tile bias slice, double buffered
 constexpr uint32_t A_STAGE_BYTES = BM * BK * 2;  // 16 KB
 
 struct GemmParams {
@@ -69,7 +78,7 @@ template <int BN> struct StagesFor { static constexpr int value = BN >= 256 ? 4 
 
 template <int BN>
 constexpr uint32_t gemm_smem_bytes() {
-    return StagesFor<BN>::value * (A_STAGE_BYTES + BN * BK * 2) + 1024 /*align*/ + 256 /*barriers*/;
+    return StagesFor<BN>::value * (A_STAGE_BYTES + BN * BK * 2) + 1024 /*align*/ + 256 /*barriers*/ + BIAS_SMEM_BYTES;
 }
 
 // MUFU tanh (one instruction, ~2^-11 relative error: below bf16 resolution).  tanhf() costs
@@ -162,19 +171,52 @@ __device__ __forceinline__ void load_aux_row(const __nv_bfloat16* aux, int64_t l
 }
 
 // One NC-column chunk of one accumulator row through the fused epilogue.
+// The aux operand (residual / pre-activation) of one chunk: issued one chunk ahead of its use so
+// the row-strided global loads are in flight while the previous chunk is processed.
+template <int NC>
+__device__ __forceinline__ void prefetch_aux(const GemmParams& p, bool vec_ok, int row, int n, uint4 (&raw)[NC / 8]) {
+    if (vec_ok && n + NC <= p.N) {
+        const uint4* src = reinterpret_cast<const uint4*>(p.aux + (int64_t)row * p.ldaux + n);
+#pragma unroll
+        for (int j = 0; j < NC / 8; ++j) raw[j] = src[j];
+    }
+}
+template <int NC>
+__device__ __forceinline__ void aux_values(const GemmParams& p, bool vec_ok, int row, int n,
+                                           const uint4 (&raw)[NC / 8], float (&a)[NC]) {
+    if (vec_ok && n + NC <= p.N) {
+#pragma unroll
+        for (int j = 0; j < NC / 8; ++j) {
+            const uint32_t w[4] = {raw[j].x, raw[j].y, raw[j].z, raw[j].w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[q]));
+                a[8 * j + 2 * q] = t.x;
+                a[8 * j + 2 * q + 1] = t.y;
+            }
+        }
+    } else {
+        load_aux_row<NC>(p.aux, p.ldaux, p.N, row, n, a);
+    }
+}
+
+// `sbias` points at this chunk's slice of the tile's bias staged in shared memory (zero beyond N).
 template <int NC>
 __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, bool row_ok, int n,
-                                               float (&f)[NC], uint32_t step) {
-    if (p.bias) {
+                                               float (&f)[NC], uint32_t step, const float* sbias,
+                                               bool aux_vec, const uint4 (&araw)[NC / 8]) {
+    if (sbias) {
 #pragma unroll
-        for (int j = 0; j < NC; ++j)
-            if (n + j < p.N) f[j] += __ldg(p.bias + n + j);
+        for (int j = 0; j < NC; j += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(sbias + j);
+            f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+        }
     }
     switch (p.epilogue) {
         case B200_EPI_NONE:
             if (p.aux && row_ok) {  // residual add
                 float a[NC];
-                load_aux_row<NC>(p.aux, p.ldaux, p.N, row, n, a);
+                aux_values<NC>(p, aux_vec, row, n, araw, a);
 #pragma unroll
                 for (int j = 0; j < NC; ++j) f[j] += a[j];
             }
@@ -202,7 +244,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, boo
         }
         case B200_EPI_GATE_POSITIVE: {
             float a[NC];
-            if (row_ok) load_aux_row<NC>(p.aux, p.ldaux, p.N, row, n, a);
+            if (row_ok) aux_values<NC>(p, aux_vec, row, n, araw, a);
 #pragma unroll
             for (int j = 0; j < NC; ++j) f[j] = (row_ok && a[j] > 0.f) ? f[j] * p.gate_scale : 0.f;
             break;
@@ -232,7 +274,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, boo
         }
         case B200_EPI_GELU_BWD: {
             float a[NC];
-            if (row_ok) load_aux_row<NC>(p.aux, p.ldaux, p.N, row, n, a);
+            if (row_ok) aux_values<NC>(p, aux_vec, row, n, araw, a);
 #pragma unroll
             for (int j = 0; j < NC; ++j) f[j] = row_ok ? f[j] * gelu_tanh_grad(a[j]) : 0.f;
             break;
@@ -307,6 +349,186 @@ __device__ __forceinline__ void colsum_chunk(const GemmParams& p, bool row_ok, i
     if (lane < NC && n + col < p.N) atomicAdd(p.colsum + n + col, v[0]);
 }
 
+// Epilogue of columns [c0, c1) x NC of one 128-row accumulator: TMEM -> registers -> fused
+// epilogue -> global.  One thread owns one row.
+template <int NC>
+__device__ __forceinline__ void drain_columns(const GemmParams& p, uint32_t taddr, int row, bool row_ok, int n0,
+                                              int c0, int c1, int64_t d_off, uint32_t step, const float* sbias) {
+    const bool aux_vec = p.aux && row_ok && (p.ldaux & 7) == 0 && ((uintptr_t)p.aux & 15) == 0;
+    uint4 araw[NC / 8], anext[NC / 8];
+#pragma unroll
+    for (int j = 0; j < NC / 8; ++j) araw[j] = anext[j] = make_uint4(0, 0, 0, 0);
+    if (c0 < c1) prefetch_aux<NC>(p, aux_vec, row, n0 + c0 * NC, araw);
+#pragma unroll 1
+    for (int c = c0; c < c1; ++c) {
+        uint32_t v[NC];
+        tmem_ld_chunk(taddr + c * NC, v);
+        if (c + 1 < c1) prefetch_aux<NC>(p, aux_vec, row, n0 + (c + 1) * NC, anext);
+        tmem_ld_wait();
+        float f[NC];
+#pragma unroll
+        for (int j = 0; j < NC; ++j) f[j] = __uint_as_float(v[j]);
+        const int n = n0 + c * NC;
+        if (n < p.N) {
+            if (p.k_splits > 1) {  // partial sum of one K slice
+                if (row_ok) add_row<NC>(p, d_off, row, n, f);
+            } else {
+                if (p.epilogue == B200_EPI_SOFTMAX_CE) epilogue_ce<NC>(p, row, row_ok, f);
+                else epilogue_chunk<NC>(p, row, row_ok, n, f, step, sbias ? sbias + c * NC : nullptr, aux_vec, araw);
+                if (p.colsum) colsum_chunk<NC>(p, row_ok, n, f);
+                if (row_ok) store_row<NC>(p, d_off, row, n, f);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < NC / 8; ++j) araw[j] = anext[j];
+    }
+}
+
+// The 256 epilogue threads stage the tile's bias slice (zero beyond N) and meet on a named
+// barrier.  Done before they wait for the accumulator, so the loads hide behind the tile's MMAs.
+template <int BN, int EPI_THREADS>
+__device__ __forceinline__ void stage_bias(const GemmParams& p, float* sb, int n0, int et) {
+    for (int j = et; j < BN; j += EPI_THREADS) sb[j] = (n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
+    asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
+}
+
+// ---- FAST epilogue: everything per-tile is hoisted into registers by the caller (row pointers,
+// mode), the chunk loop touches only TMEM, the staged bias and the row's own global addresses.
+__device__ __forceinline__ void unpack8(const uint4& raw, float* a) {
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[q]));
+        a[2 * q] = t.x;
+        a[2 * q + 1] = t.y;
+    }
+}
+// 32 columns of one row as bf16; N is a multiple of 8 or the tail is written element-wise.
+__device__ __forceinline__ void store32_bf16(__nv_bfloat16* dst, int n, int N, const float (&f)[32]) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) {
+        if (n + j + 8 <= N) {
+            uint4 o;
+            o.x = pack_bf16(f[j], f[j + 1]);
+            o.y = pack_bf16(f[j + 2], f[j + 3]);
+            o.z = pack_bf16(f[j + 4], f[j + 5]);
+            o.w = pack_bf16(f[j + 6], f[j + 7]);
+            *reinterpret_cast<uint4*>(dst + n + j) = o;
+        } else {
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                if (n + j + q < N) dst[n + j + q] = __float2bfloat16_rn(f[j + q]);
+        }
+    }
+}
+// The same 32 columns, written so that every instruction covers whole 32-byte sectors: a thread's
+// row segment is four 16-byte pieces, and one piece per lane per instruction leaves each sector
+// half-written (measured: output-heavy GEMMs capped near 1.3 TB/s of stores).  Lanes 2i and 2i+1
+// swap two pieces each, then write the two halves of one sector of row 2i, then of row 2i+1.
+// `prow` is the partner lane's row pointer.  Whole chunk in range only (n + 32 <= N).
+__device__ __forceinline__ uint4 shfl_xor1(const uint4& v) {
+    uint4 r;
+    r.x = __shfl_xor_sync(0xffffffffu, v.x, 1);
+    r.y = __shfl_xor_sync(0xffffffffu, v.y, 1);
+    r.z = __shfl_xor_sync(0xffffffffu, v.z, 1);
+    r.w = __shfl_xor_sync(0xffffffffu, v.w, 1);
+    return r;
+}
+__device__ __forceinline__ void store32_pair(__nv_bfloat16* drow, __nv_bfloat16* prow, int n, bool odd,
+                                             const float (&f)[32]) {
+    uint4 c[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        c[j].x = pack_bf16(f[8 * j], f[8 * j + 1]);
+        c[j].y = pack_bf16(f[8 * j + 2], f[8 * j + 3]);
+        c[j].z = pack_bf16(f[8 * j + 4], f[8 * j + 5]);
+        c[j].w = pack_bf16(f[8 * j + 6], f[8 * j + 7]);
+    }
+    // even lane keeps pieces 0,2 of its row and receives 0,2 of the odd row;
+    // odd lane keeps pieces 1,3 of its row and receives 1,3 of the even row
+    const uint4 ra = shfl_xor1(odd ? c[0] : c[1]);
+    const uint4 rb = shfl_xor1(odd ? c[2] : c[3]);
+    __nv_bfloat16* row_lo = odd ? prow : drow;   // row 2i
+    __nv_bfloat16* row_hi = odd ? drow : prow;   // row 2i+1
+    const int off = n + (odd ? 8 : 0);
+    const uint4 lo_a = odd ? ra : c[0], lo_b = odd ? rb : c[2];
+    const uint4 hi_a = odd ? c[1] : ra, hi_b = odd ? c[3] : rb;
+    if (row_lo) {
+        *reinterpret_cast<uint4*>(row_lo + off) = lo_a;
+        *reinterpret_cast<uint4*>(row_lo + off + 16) = lo_b;
+    }
+    if (row_hi) {
+        *reinterpret_cast<uint4*>(row_hi + off) = hi_a;
+        *reinterpret_cast<uint4*>(row_hi + off + 16) = hi_b;
+    }
+}
+__device__ __forceinline__ __nv_bfloat16* partner_ptr(__nv_bfloat16* ptr) {
+    const unsigned long long v = __shfl_xor_sync(0xffffffffu, (unsigned long long)ptr, 1);
+    return reinterpret_cast<__nv_bfloat16*>(v);
+}
+__device__ __forceinline__ void fetch32(const __nv_bfloat16* arow, int n, int N, uint4 (&r)[4]) {
+    if (arow) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (n + 8 * j + 8 <= N) r[j] = *reinterpret_cast<const uint4*>(arow + n + 8 * j);
+    }
+}
+// drow / arow / zrow: this thread's row of D, aux and aux_out (null when the row is out of range or
+// the operand is absent).  mode: B200_EPI_NONE (+ residual when arow), _GELU, _GELU_BWD.
+__device__ __forceinline__ void fast_drain(uint32_t taddr, int n0, int N, int c0, int c1, int mode,
+                                           __nv_bfloat16* drow, const __nv_bfloat16* arow,
+                                           __nv_bfloat16* zrow, const float* sbias) {
+    const bool odd = (threadIdx.x & 1) != 0;
+    __nv_bfloat16* dprow = partner_ptr(drow);
+    __nv_bfloat16* zprow = partner_ptr(zrow);
+    uint4 araw[4], anext[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) araw[j] = anext[j] = make_uint4(0, 0, 0, 0);
+    if (c0 < c1) fetch32(arow, n0 + c0 * 32, N, araw);
+#pragma unroll 1
+    for (int c = c0; c < c1; ++c) {
+        const int n = n0 + c * 32;
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + c * 32, v);
+        if (c + 1 < c1) fetch32(arow, n + 32, N, anext);
+        tmem_ld_wait();
+        if (n < N) {
+            float f[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+            if (sbias) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                    const float4 b4 = *reinterpret_cast<const float4*>(sbias + c * 32 + j);
+                    f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+                }
+            }
+            if (mode == B200_EPI_GELU) {
+                // pre-activation, for the backward gate
+                if (n + 32 <= N) store32_pair(zrow, zprow, n, odd, f);
+                else if (zrow) store32_bf16(zrow, n, N, f);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) f[j] = gelu_tanh(f[j]);
+            } else if (arow) {
+                float a[32];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) unpack8(araw[j], a + 8 * j);
+                if (mode == B200_EPI_GELU_BWD) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) f[j] *= gelu_tanh_grad(a[j]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) f[j] += a[j];
+                }
+            }
+            if (n + 32 <= N) store32_pair(drow, dprow, n, odd, f);
+            else if (drow) store32_bf16(drow, n, N, f);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) araw[j] = anext[j];
+    }
+}
+
 struct TileInfo {
     int m0, n0, kb0, kb1, hb, bb;
     bool skip;
@@ -335,8 +557,8 @@ __device__ __forceinline__ TileInfo decode_tile(const GemmParams& p, int tile) {
     return t;
 }
 
-template <int BN>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+template <int BN, bool FAST>
+__global__ void __launch_bounds__(gemm_threads<FAST>(), 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
             const GemmParams p) {
     constexpr int STAGES = StagesFor<BN>::value;
@@ -354,6 +576,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     uint64_t* tmem_full = bars + 2 * STAGES;
     uint64_t* tmem_empty = bars + 2 * STAGES + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+    float* sbias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -369,7 +592,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tmem_full[s], 1);
-            mbar_init(&tmem_empty[s], 4);
+            mbar_init(&tmem_empty[s], EpiWarps<FAST>::value);
         }
         fence_mbar_init();
     }
@@ -454,8 +677,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
             }
         }
     } else {
-        // ===================== epilogue (warps 2..5) =====================
+        // ===================== epilogue =====================
+        // General kernels: warps 2..5, one per TMEM lane quarter.  FAST kernels: warps 2..9, two
+        // per quarter, each draining half of the accumulator's columns.
+        constexpr int EPI_THREADS = 32 * EpiWarps<FAST>::value;
         const int quarter = warp & 3;  // TMEM lanes this warp may read
+        const int half = (warp - 2) >> 2;
+        const int et = threadIdx.x - 64;
+        constexpr int CH = BN / NC;
+        const int c0 = FAST ? half * (CH / 2) : 0;
+        const int c1 = FAST ? c0 + CH / 2 : CH;
+        const bool use_sbias = p.bias && p.epilogue != B200_EPI_SOFTMAX_CE;
+        const int mode = p.epilogue, N = p.N;
         uint32_t step = 0;
         if (p.step_dev) step = (uint32_t)__ldg(p.step_dev);
         int it = 0;
@@ -465,30 +698,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
             const int m0 = t.m0, n0 = t.n0;
             const int64_t d_off = t.hb * p.d_stride_inner + t.bb * p.d_stride_outer;
             const uint32_t as = it & 1;
-            mbar_wait(&tmem_full[as], (it >> 1) & 1);
-            tc_fence_after();
+            float* sb = sbias + as * 256;
+            if (use_sbias) stage_bias<BN, EPI_THREADS>(p, sb, n0, et);
             const int row = m0 + quarter * 32 + lane;
             const bool row_ok = row < p.M;
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
-#pragma unroll 1
-            for (int c = 0; c < BN / NC; ++c) {
-                uint32_t v[NC];
-                if constexpr (NC == 32) tmem_ld_32x32(taddr + c * NC, v);
-                else tmem_ld_32x16(taddr + c * NC, v);
-                tmem_ld_wait();
-                float f[NC];
-#pragma unroll
-                for (int j = 0; j < NC; ++j) f[j] = __uint_as_float(v[j]);
-                const int n = n0 + c * NC;
-                if (n >= p.N) continue;
-                if (p.k_splits > 1) {  // partial sum of one K slice
-                    if (row_ok) add_row<NC>(p, d_off, row, n, f);
-                    continue;
-                }
-                if (p.epilogue == B200_EPI_SOFTMAX_CE) epilogue_ce<NC>(p, row, row_ok, f);
-                else epilogue_chunk<NC>(p, row, row_ok, n, f, step);
-                if (p.colsum) colsum_chunk<NC>(p, row_ok, n, f);
-                if (row_ok) store_row<NC>(p, d_off, row, n, f);
+            if constexpr (FAST) {
+                __nv_bfloat16* drow = row_ok ? reinterpret_cast<__nv_bfloat16*>(p.D) + d_off + (int64_t)row * p.ldd : nullptr;
+                const __nv_bfloat16* arow = (row_ok && p.aux) ? p.aux + (int64_t)row * p.ldaux : nullptr;
+                __nv_bfloat16* zrow = (row_ok && p.aux_out) ? p.aux_out + (int64_t)row * p.ldd : nullptr;
+                mbar_wait(&tmem_full[as], (it >> 1) & 1);
+                tc_fence_after();
+                fast_drain(taddr, n0, N, c0, c1, mode, drow, arow, zrow, use_sbias ? sb : nullptr);
+            } else {
+                mbar_wait(&tmem_full[as], (it >> 1) & 1);
+                tc_fence_after();
+                drain_columns<NC>(p, taddr, row, row_ok, n0, c0, c1, d_off, step, use_sbias ? sb : nullptr);
             }
             tc_fence_before();
             __syncwarp();
@@ -517,9 +742,9 @@ constexpr int BM2 = 256;
 constexpr int STAGES2 = 3;
 constexpr uint32_t A2_STAGE_BYTES = BM2 * BK * 2;   // 32 KB
 constexpr uint32_t B2_STAGE_BYTES = 256 * BK * 2;   // 32 KB
-constexpr uint32_t GEMM2_SMEM = STAGES2 * (A2_STAGE_BYTES + B2_STAGE_BYTES) + 1024 + 256;
+constexpr uint32_t GEMM2_SMEM = STAGES2 * (A2_STAGE_BYTES + B2_STAGE_BYTES) + 1024 + 256 + BIAS_SMEM_BYTES;
 
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(gemm_threads<true>(), 1)
 gemm_kernel_m256(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  const GemmParams p) {
     constexpr int BN = 256;
@@ -534,6 +759,7 @@ gemm_kernel_m256(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     uint64_t* tmem_full = bars + 2 * STAGES2;       // [2]: upper / lower accumulator complete
     uint64_t* tmem_empty = bars + 2 * STAGES2 + 2;  // [2]: upper / lower accumulator drained
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES2 + 4);
+    float* sbias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -549,7 +775,7 @@ gemm_kernel_m256(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tmem_full[s], 1);
-            mbar_init(&tmem_empty[s], 4);
+            mbar_init(&tmem_empty[s], 8);
         }
         fence_mbar_init();
     }
@@ -630,35 +856,31 @@ gemm_kernel_m256(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
             }
         }
     } else {
+        // FAST epilogue only (the host routes everything else to the 128-row kernel)
         const int quarter = warp & 3;
-        uint32_t step = 0;
-        if (p.step_dev) step = (uint32_t)__ldg(p.step_dev);
+        const int half = (warp - 2) >> 2;   // which 128 columns of each accumulator this warp drains
+        const int et = threadIdx.x - 64;
+        constexpr int CH = BN / NC;
+        const int mode = p.epilogue, N = p.N;
         int it = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
             const int m0 = (tile % p.num_m_blocks) * BM2;
             const int n0 = (tile / p.num_m_blocks) * BN;
             const uint32_t par = (uint32_t)(it & 1);
+            float* sb = sbias + par * 256;
+            if (p.bias) stage_bias<BN, 256>(p, sb, n0, et);
 #pragma unroll 1
             for (int h = 0; h < 2; ++h) {
-                mbar_wait(&tmem_full[h], par);
-                tc_fence_after();
                 const int row = m0 + h * 128 + quarter * 32 + lane;
                 const bool row_ok = row < p.M;
+                __nv_bfloat16* drow = row_ok ? reinterpret_cast<__nv_bfloat16*>(p.D) + (int64_t)row * p.ldd : nullptr;
+                const __nv_bfloat16* arow = (row_ok && p.aux) ? p.aux + (int64_t)row * p.ldaux : nullptr;
+                __nv_bfloat16* zrow = (row_ok && p.aux_out) ? p.aux_out + (int64_t)row * p.ldd : nullptr;
+                mbar_wait(&tmem_full[h], par);
+                tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + h * BN;
-#pragma unroll 1
-                for (int c = 0; c < BN / NC; ++c) {
-                    uint32_t v[NC];
-                    tmem_ld_32x32(taddr + c * NC, v);
-                    tmem_ld_wait();
-                    float f[NC];
-#pragma unroll
-                    for (int j = 0; j < NC; ++j) f[j] = __uint_as_float(v[j]);
-                    const int n = n0 + c * NC;
-                    if (n >= p.N) continue;
-                    epilogue_chunk<NC>(p, row, row_ok, n, f, step);
-                    if (p.colsum) colsum_chunk<NC>(p, row_ok, n, f);
-                    if (row_ok) store_row<NC>(p, 0, row, n, f);
-                }
+                fast_drain(taddr, n0, N, half * (CH / 2), (half + 1) * (CH / 2), mode, drow, arow, zrow,
+                           p.bias ? sb : nullptr);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tmem_empty[h]);
@@ -671,6 +893,215 @@ gemm_kernel_m256(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ---------------------------------------------------------------- two-SM tiles (cta_group::2)
+// One 256x256 output tile per CTA PAIR (a 2-CTA cluster = the two SMs of a TPC).  Each CTA stages
+// its own 128 rows of A and only HALF of B (128 of the 256 columns): the pair's tensor cores read
+// both halves, so an SM pulls 32 KB per k-block from L2 instead of the 48 KB of the single-SM
+// 128x256 kernel -- the mainloop of that kernel is bound by exactly this operand feed -- while each
+// SM keeps a double-buffered 128x256 fp32 accumulator (2 x 256 TMEM columns) so the epilogue of
+// tile i still overlaps the MMAs of tile i+1 (the 256x256 single-SM kernel cannot: its two
+// accumulators fill TMEM).
+//   * both CTAs run a TMA producer; every load completes on the LEADER's (rank 0) full barrier
+//   * the leader's MMA thread issues tcgen05.mma.cta_group::2 (M = 256) for both SMs; its commits
+//     are multicast to both CTAs' barriers (ring slot free / accumulator complete)
+//   * every epilogue warp of both CTAs arrives on the leader's tmem_empty barrier
+constexpr int STAGES_2SM = 6;
+constexpr uint32_t B_HALF_BYTES = 128 * BK * 2;  // 16 KB
+constexpr uint32_t GEMM_2SM_SMEM = STAGES_2SM * (A_STAGE_BYTES + B_HALF_BYTES) + 1024 + 256 + BIAS_SMEM_BYTES;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `smem_addr` (a shared::cta address) in CTA `rank` of this cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_pair(void* smem_dst, const CUtensorMap* map, uint32_t leader_bar,
+                                                 int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+                                               uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// arrives on the barrier at this offset in BOTH CTAs of the pair once all earlier MMAs retired
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+            smem_u32(bar)),
+        "h"((uint16_t)3)
+        : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(gemm_threads<true>(), 1)
+gemm_kernel_2sm(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                const GemmParams p) {
+    constexpr int BN = 256;
+    constexpr int STAGES = STAGES_2SM;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + STAGES * A_STAGE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + STAGES * B_HALF_BYTES);
+    uint64_t* full_bar = bars;                   // used in the leader only
+    uint64_t* empty_bar = bars + STAGES;         // per CTA (multicast commit)
+    uint64_t* tmem_full = bars + 2 * STAGES;     // per CTA (multicast commit)
+    uint64_t* tmem_empty = bars + 2 * STAGES + 2;  // leader only: 16 epilogue warps arrive
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+    float* sbias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+    const int num_tiles = p.num_m_blocks * p.num_n_blocks;   // 256 x 256 tiles
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], 2 * EpiWarps<true>::value);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(512u)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();   // the peer's barriers are initialised before anything is signalled across
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+                const int m0 = (tile % p.num_m_blocks) * 256 + (int)rank * 128;   // this CTA's A rows
+                const int n0 = (tile / p.num_m_blocks) * BN + (int)rank * 128;    // this CTA's half of B
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    const uint32_t lbar = mapa_u32(smem_u32(&full_bar[stage]), 0);
+                    if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (A_STAGE_BYTES + B_HALF_BYTES));
+                    uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
+                    uint8_t* sb = smem_b + stage * B_HALF_BYTES;
+                    const int k0 = kb * BK;
+                    if (!p.a_mn) {
+                        tma_load_4d_pair(sa, &tma_a, lbar, k0, m0, 0, 0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 2; ++j) tma_load_4d_pair(sa + j * 8192, &tma_a, lbar, m0 + j * 64, k0, 0, 0);
+                    }
+                    if (!p.b_mn) {
+                        tma_load_4d_pair(sb, &tma_b, lbar, k0, n0, 0, 0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 2; ++j) tma_load_4d_pair(sb + j * 8192, &tma_b, lbar, n0 + j * 64, k0, 0, 0);
+                    }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader CTA only) =====================
+        if (lane == 0 && rank == 0) {
+            uint32_t stage = 0, phase = 0;
+            int it = 0;
+            const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
+            const uint32_t a_kstep = p.a_mn ? 2048u : 32u, b_kstep = p.b_mn ? 2048u : 32u;
+            for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
+                const uint32_t as = it & 1;
+                mbar_wait(&tmem_empty[as], ((it >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
+                    const uint32_t sb = smem_u32(smem_b + stage * B_HALF_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) {
+                        const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024u);
+                        const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024u);
+                        umma_bf16_pair(d_tmem, da, db, p.idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit_pair(&empty_bar[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_pair(&tmem_full[as]);
+            }
+        }
+    } else {
+        // ===================== epilogue (both CTAs: own 128 rows x 256 columns) =====================
+        const int quarter = warp & 3;
+        const int half = (warp - 2) >> 2;
+        const int et = threadIdx.x - 64;
+        constexpr int CH = BN / 32;
+        const int mode = p.epilogue, N = p.N;
+        int it = 0;
+        for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
+            const int m0 = (tile % p.num_m_blocks) * 256 + (int)rank * 128;
+            const int n0 = (tile / p.num_m_blocks) * BN;
+            const uint32_t as = it & 1;
+            float* sb = sbias + as * 256;
+            if (p.bias) stage_bias<BN, 256>(p, sb, n0, et);
+            const int row = m0 + quarter * 32 + lane;
+            const bool row_ok = row < p.M;
+            __nv_bfloat16* drow = row_ok ? reinterpret_cast<__nv_bfloat16*>(p.D) + (int64_t)row * p.ldd : nullptr;
+            const __nv_bfloat16* arow = (row_ok && p.aux) ? p.aux + (int64_t)row * p.ldaux : nullptr;
+            __nv_bfloat16* zrow = (row_ok && p.aux_out) ? p.aux_out + (int64_t)row * p.ldd : nullptr;
+            mbar_wait(&tmem_full[as], (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
+            fast_drain(taddr, n0, N, half * (CH / 2), (half + 1) * (CH / 2), mode, drow, arow, zrow,
+                       p.bias ? sb : nullptr);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tmem_empty[as]), 0));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();   // the leader's MMAs read the peer's shared memory until the last commit
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
     }
 }
 
@@ -715,7 +1146,7 @@ static int make_map(CUtensorMap* map, const void* base, int64_t inner, int64_t o
     return 0;
 }
 
-template <int BN>
+template <int BN, bool FAST>
 static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int ctas, cudaStream_t s) {
     constexpr uint32_t smem = gemm_smem_bytes<BN>();
     // Programmatic dependent launch: the next GEMM's prologue (barrier init, TMEM
@@ -724,7 +1155,7 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams
     static const bool pdl = getenv("B200DDP_NO_PDL") == nullptr;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned)ctas);
-    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.blockDim = dim3(gemm_threads<FAST>());
     cfg.dynamicSmemBytes = smem;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
@@ -732,7 +1163,7 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel<BN>, ma, mb, p));
+    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, FAST>, ma, mb, p));
     b200_count_launch(1);
     B200_CUDA_OK(cudaGetLastError());
     return 0;
@@ -742,7 +1173,7 @@ static int launch_m256(const CUtensorMap& ma, const CUtensorMap& mb, const GemmP
     static const bool pdl = getenv("B200DDP_NO_PDL") == nullptr;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned)ctas);
-    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.blockDim = dim3(gemm_threads<true>());
     cfg.dynamicSmemBytes = GEMM2_SMEM;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
@@ -751,6 +1182,24 @@ static int launch_m256(const CUtensorMap& ma, const CUtensorMap& mb, const GemmP
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
     B200_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel_m256, ma, mb, p));
+    b200_count_launch(1);
+    B200_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+static int launch_2sm(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int ctas, cudaStream_t s) {
+    static const bool pdl = getenv("B200DDP_NO_PDL") == nullptr;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)ctas);   // even; the kernel carries __cluster_dims__(2, 1, 1)
+    cfg.blockDim = dim3(gemm_threads<true>());
+    cfg.dynamicSmemBytes = GEMM_2SM_SMEM;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel_2sm, ma, mb, p));
     b200_count_launch(1);
     B200_CUDA_OK(cudaGetLastError());
     return 0;
@@ -814,7 +1263,7 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
                  (long long)d->lda, (long long)d->ldb);
     B200_REQUIRE(((uintptr_t)d->A % 16) == 0 && ((uintptr_t)d->B % 16) == 0, "gemm: A/B must be 16-byte aligned");
     const int sms = sm_count();
-    int bn = d->tile_n ? d->tile_n : pick_tile_n(d, sms);
+    int bn = d->tile_n ? d->tile_n : (d->cta_pair == 1 ? 256 : pick_tile_n(d, sms));
     B200_REQUIRE(bn == 16 || bn == 32 || bn == 64 || bn == 128 || bn == 256, "gemm: tile_n %d unsupported", bn);
     B200_REQUIRE(!(d->b_mn_major && bn < 64), "gemm: MN-major B needs tile_n >= 64");
     if (d->epilogue == B200_EPI_SOFTMAX_CE) {
@@ -831,21 +1280,38 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
         B200_REQUIRE(d->epilogue == B200_EPI_NONE && !d->aux && !d->bias && !d->colsum && !d->split_k,
                      "gemm: batched mode supports the plain epilogue only");
     B200_REQUIRE(d->causal >= 0 && d->causal <= 3, "gemm: causal mode %d unknown", d->causal);
-    // 256x256 dual-accumulator tiles for large plain GEMMs (at least ~one wave of them)
+    // FAST epilogue kernels: bf16 output with 16-byte-aligned rows and one of the light epilogues
+    const bool light = d->epilogue == B200_EPI_NONE || d->epilogue == B200_EPI_GELU || d->epilogue == B200_EPI_GELU_BWD;
+    const bool vec_d = !d->d_fp32 && (d->ldd % 8) == 0 && ((uintptr_t)d->D % 16) == 0 &&
+                       (d->d_stride_inner % 8) == 0 && (d->d_stride_outer % 8) == 0;
+    const bool vec_aux = !d->aux || ((d->ldaux % 8) == 0 && ((uintptr_t)d->aux % 16) == 0 && (d->N % 8) == 0);
+    const bool vec_z = !d->aux_out || (((uintptr_t)d->aux_out % 16) == 0 && (d->N % 8) == 0);
+    static const bool fast_off = getenv("B200DDP_NO_FAST_EPILOGUE") != nullptr;
+    const bool fast = !fast_off && bn >= 64 && light && vec_d && vec_aux && vec_z && !d->colsum && !d->split_k &&
+                      !(d->epilogue == B200_EPI_GELU_BWD && !d->aux);
+    // Large-tile kernels for plain non-batched problems with a light epilogue:
+    //   256x256 dual accumulator, one SM   long reductions (K >= 4096) with at least a wave of tiles:
+    //                                      1481 vs 1288 TFLOP/s at 8192^3; with short K its
+    //                                      single-buffered accumulators expose the epilogue
+    //   256x256 per SM pair (cta_group::2) everything else that picked 256-wide tiles: double-buffered
+    //                                      accumulators and 32 KB of operands per SM per k-block
     static const bool m256_off = getenv("B200DDP_NO_M256") != nullptr;
-    bool m256 = false;
-    if (bn == 256 && nbi * nbo == 1 && !d->causal && !d->split_k && d->epilogue != B200_EPI_SOFTMAX_CE) {
-        const int64_t t2 = (int64_t)((d->M + BM2 - 1) / BM2) * ((d->N + 255) / 256);
-        // measured: wins for long reductions (K >= 4096: 1481 vs 1288 TFLOP/s at 8192^3); with short K its
-        // single-buffered accumulators expose the epilogue and 128x256 is faster
-        m256 = d->tile_m == 256 || (d->tile_m == 0 && !m256_off && d->M >= 512 && d->K >= 4096 && t2 >= sms);
-    }
+    static const bool pair_off = getenv("B200DDP_NO_PAIR") != nullptr;
+    const bool big_ok = bn == 256 && nbi * nbo == 1 && !d->causal && fast;
+    const int64_t t2 = (int64_t)((d->M + BM2 - 1) / BM2) * ((d->N + 255) / 256);
+    bool m256 = big_ok && (d->tile_m == 256 || (d->tile_m == 0 && d->cta_pair != 1 && !m256_off && d->M >= 512 &&
+                                                 d->K >= 4096 && t2 >= sms));
+    bool pair = big_ok && !m256 && d->M > 128 &&
+                (d->cta_pair == 1 || (d->cta_pair == 0 && d->tile_m == 0 && !pair_off));
+    B200_REQUIRE(d->cta_pair != 1 || pair,
+                 "gemm: cta_pair needs tile_n 256 (or auto), M > 128, a non-batched problem and a light epilogue with bf16 D");
     B200_REQUIRE(d->tile_m == 0 || d->tile_m == 128 || d->tile_m == 256, "gemm: tile_m must be 0, 128 or 256");
-    B200_REQUIRE(d->tile_m != 256 || m256, "gemm: tile_m 256 needs tile_n 256 and a plain, non-batched problem");
+    B200_REQUIRE(d->tile_m != 256 || m256,
+                 "gemm: tile_m 256 needs tile_n 256, a non-batched problem and a light epilogue with bf16 output");
     if (!d->a_mn_major) rc = make_map(&ma, d->A, d->K, d->M, d->lda, BK, m256 ? BM2 : BM, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
     else rc = make_map(&ma, d->A, d->M, d->K, d->lda, 64, BK, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
     if (rc) return rc;
-    if (!d->b_mn_major) rc = make_map(&mb, d->B, d->K, d->N, d->ldb, BK, bn, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
+    if (!d->b_mn_major) rc = make_map(&mb, d->B, d->K, d->N, d->ldb, BK, pair ? 128 : bn, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
     else rc = make_map(&mb, d->B, d->N, d->K, d->ldb, 64, BK, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
     if (rc) return rc;
 
@@ -860,13 +1326,13 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
     p.seed = d->seed; p.step_dev = d->step_dev; p.layer_id = d->layer_id;
     p.targets = d->targets; p.ce_grad_scale = d->ce_grad_scale;
     p.loss_out = d->loss_out; p.loss_scale = d->loss_scale; p.ce_write_grad = d->ce_write_grad;
-    p.num_m_blocks = m256 ? (d->M + BM2 - 1) / BM2 : (d->M + BM - 1) / BM;
+    p.num_m_blocks = (m256 || pair) ? (d->M + BM2 - 1) / BM2 : (d->M + BM - 1) / BM;
     p.num_n_blocks = (d->N + bn - 1) / bn;
     p.num_k_blocks = (d->K + BK - 1) / BK;
     // instruction descriptor: fp32 accumulate, bf16 A/B, majors, N>>3, M>>4
     p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(d->a_mn_major ? 1 : 0) << 15) |
               ((uint32_t)(d->b_mn_major ? 1 : 0) << 16) | ((uint32_t)(bn >> 3) << 17) |
-              ((uint32_t)(BM >> 4) << 24);
+              ((uint32_t)((pair ? 256 : BM) >> 4) << 24);
     p.batch_inner = nbi; p.batch_outer = nbo;
     p.d_stride_inner = d->d_stride_inner; p.d_stride_outer = d->d_stride_outer;
     p.causal = d->causal;
@@ -890,13 +1356,27 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
     int ctas = d->max_ctas > 0 ? d->max_ctas : sms;
     if (ctas > tiles) ctas = tiles;
     cudaStream_t s = (cudaStream_t)stream;
+    if (pair) {
+        int c2 = 2 * tiles < sms ? 2 * tiles : sms;
+        if (d->max_ctas > 0 && d->max_ctas < c2) c2 = d->max_ctas;
+        c2 &= ~1;
+        B200_REQUIRE(c2 >= 2, "gemm: the two-SM kernel needs at least 2 CTAs");
+        return launch_2sm(ma, mb, p, c2, s);
+    }
     if (m256) return launch_m256(ma, mb, p, ctas, s);
+    if (fast) {
+        switch (bn) {
+            case 64: return launch<64, true>(ma, mb, p, ctas, s);
+            case 128: return launch<128, true>(ma, mb, p, ctas, s);
+            default: return launch<256, true>(ma, mb, p, ctas, s);
+        }
+    }
     switch (bn) {
-        case 16: return launch<16>(ma, mb, p, ctas, s);
-        case 32: return launch<32>(ma, mb, p, ctas, s);
-        case 64: return launch<64>(ma, mb, p, ctas, s);
-        case 128: return launch<128>(ma, mb, p, ctas, s);
-        default: return launch<256>(ma, mb, p, ctas, s);
+        case 16: return launch<16, false>(ma, mb, p, ctas, s);
+        case 32: return launch<32, false>(ma, mb, p, ctas, s);
+        case 64: return launch<64, false>(ma, mb, p, ctas, s);
+        case 128: return launch<128, false>(ma, mb, p, ctas, s);
+        default: return launch<256, false>(ma, mb, p, ctas, s);
     }
 }
 
@@ -905,11 +1385,13 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
 int b200_gemm_init() {
     using namespace b200;
     B200_REQUIRE(get_encode_fn() != nullptr, "init: cuTensorMapEncodeTiled is unavailable");
-#define PREP(BN)                                                                                         \
-    B200_CUDA_OK(cudaFuncSetAttribute(gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+#define PREP(BN, FAST)                                                                                  \
+    B200_CUDA_OK(cudaFuncSetAttribute(gemm_kernel<BN, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                       (int)gemm_smem_bytes<BN>()))
-    PREP(16); PREP(32); PREP(64); PREP(128); PREP(256);
+    PREP(16, false); PREP(32, false); PREP(64, false); PREP(128, false); PREP(256, false);
+    PREP(64, true); PREP(128, true); PREP(256, true);
 #undef PREP
     B200_CUDA_OK(cudaFuncSetAttribute(gemm_kernel_m256, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM2_SMEM));
+    B200_CUDA_OK(cudaFuncSetAttribute(gemm_kernel_2sm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_2SM_SMEM));
     return 0;
 }

@@ -161,6 +161,10 @@ typedef struct {
     int split_k;                                /* 0 = off; 1 = choose; >1 = that many K slices.  Plain
                                                  * fp32 D only, zeroed by the caller: slices are combined
                                                  * with 16-byte vector atomics (wgrad: long K, few tiles) */
+    int cta_pair;                               /* 0 = choose; 1 = force the two-SM kernel (tcgen05
+                                                 * cta_group::2, one 256x256 tile per SM pair; needs a
+                                                 * non-batched problem, a light epilogue and bf16 D);
+                                                 * -1 = never */
 } b200_gemm_desc;
 
 int b200_gemm(const b200_gemm_desc* d, void* stream);

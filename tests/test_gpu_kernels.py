@@ -547,21 +547,70 @@ def test_batchnorm_act_kernels(C, H, relu, res):
     assert rel_err(ye, yer) < 8e-3
 
 
-@pytest.mark.parametrize("M,N,K,a_mn,b_mn", [(512, 512, 256, False, False), (1000, 700, 328, False, False),
-                                            (768, 512, 1024, True, True), (2048, 1024, 192, False, True)])
-def test_gemm_256x256_dual_accumulator_tiles(B, M, N, K, a_mn, b_mn):
-    torch.manual_seed(20)
+def _gelu_tanh_grad(z):
+    u = 0.7978845608028654 * (z + 0.044715 * z ** 3)
+    t = torch.tanh(u)
+    return 0.5 * (1 + t) + 0.5 * z * (1 - t * t) * 0.7978845608028654 * (1 + 3 * 0.044715 * z * z)
+
+
+def _check_big_tile_kernel(B, M, N, K, a_mn, b_mn, **tile):
+    """Bias, ragged-N store, residual, GELU (+ saved pre-activation) and GELU-backward epilogues of
+    the lean-epilogue kernels against fp32 references."""
     dev = torch.device("cuda")
     a = bf(torch.randn((K, M) if a_mn else (M, K), device=dev))
-    b = bf(torch.randn((K, N) if b_mn else (N, K), device=dev))
+    b = bf(torch.randn((K, N) if b_mn else (N, K), device=dev)) * 0.1
     want = _ref_gemm(a, b, a_mn, b_mn)
     bias = torch.randn(N, device=dev)
-    out = torch.full((M, N), 7.0, dtype=torch.bfloat16, device=dev)
-    B.gemm(a, b, out, M=M, N=N, K=K, a_mn_major=a_mn, b_mn_major=b_mn, tile_n=256, tile_m=256, bias=bias)
+    ld = (N + 7) // 8 * 8
+    buf = torch.full((M, ld), 7.0, dtype=torch.bfloat16, device=dev)
+    out = buf[:, :N]
+    kw = dict(M=M, N=N, K=K, a_mn_major=a_mn, b_mn_major=b_mn, **tile)
+    B.gemm(a, b, out, bias=bias, **kw)
     assert rel_err(out, want + bias) < 6e-3, rel_err(out, want + bias)
-    out32 = torch.empty(M, N, dtype=torch.float32, device=dev)
-    B.gemm(a, b, out32, M=M, N=N, K=K, a_mn_major=a_mn, b_mn_major=b_mn, tile_n=256, tile_m=256)
-    assert rel_err(out32, want) < 2e-5
+    if ld != N:
+        assert (buf[:, N:].float() == 7.0).all()        # nothing written past column N
+        return
+    r = bf(torch.randn(M, N, device=dev))
+    B.gemm(a, b, out, bias=bias, aux=r, **kw)
+    assert rel_err(out, want + bias + r.float()) < 6e-3
+    z = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    B.gemm(a, b, out, bias=bias, epilogue=B.EPI_GELU, aux_out=z, **kw)
+    assert rel_err(z, want + bias) < 6e-3
+    assert rel_err(out, F.gelu(want + bias, approximate="tanh")) < 8e-3
+    B.gemm(a, b, out, epilogue=B.EPI_GELU_BWD, aux=z, **kw)
+    assert rel_err(out, want * _gelu_tanh_grad(z.float())) < 8e-3
+
+
+_BIG_TILE_SHAPES = [(512, 512, 256, False, False), (1000, 700, 328, False, False), (1000, 704, 328, False, False),
+                    (768, 512, 1024, True, True), (2048, 1024, 192, False, True), (4096, 2304, 768, False, False)]
+
+
+@pytest.mark.parametrize("M,N,K,a_mn,b_mn", _BIG_TILE_SHAPES)
+def test_gemm_256x256_dual_accumulator_tiles(B, M, N, K, a_mn, b_mn):
+    torch.manual_seed(20)
+    _check_big_tile_kernel(B, M, N, K, a_mn, b_mn, tile_n=256, tile_m=256)
+
+
+@pytest.mark.parametrize("M,N,K,a_mn,b_mn", _BIG_TILE_SHAPES)
+def test_gemm_two_sm_pair_tiles(B, M, N, K, a_mn, b_mn):
+    """tcgen05 cta_group::2: one 256x256 tile per SM pair, each CTA staging half of B."""
+    torch.manual_seed(22)
+    _check_big_tile_kernel(B, M, N, K, a_mn, b_mn, cta_pair=1)
+
+
+@pytest.mark.parametrize("tile_n", [64, 128, 256])
+def test_gemm_lean_epilogue_kernels(B, tile_n):
+    torch.manual_seed(23)
+    _check_big_tile_kernel(B, 1000, 704, 328, False, False, tile_n=tile_n)
+    _check_big_tile_kernel(B, 640, 712, 136, False, True, tile_n=tile_n)
+
+
+def test_gemm_pair_rejects_unsupported(B):
+    dev = torch.device("cuda")
+    a = bf(torch.randn(512, 256, device=dev)); b = bf(torch.randn(512, 256, device=dev))
+    out32 = torch.empty(512, 512, dtype=torch.float32, device=dev)
+    with pytest.raises(RuntimeError, match="cta_pair"):
+        B.gemm(a, b, out32, M=512, N=512, K=256, cta_pair=1)
 
 
 @pytest.mark.parametrize("Bs,H,T", [(1, 1, 128), (2, 4, 384), (2, 12, 1024)])

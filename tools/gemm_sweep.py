@@ -22,7 +22,7 @@ for M, N, K in shapes:
     out = torch.empty(M, Np, dtype=torch.bfloat16, device=dev)
     fl = 2.0 * M * N * K
     row = [f"{M}x{N}x{K}"]
-    for name, kw in (("auto", {}), ("128x256", dict(tile_n=256, tile_m=128)), ("256x256", dict(tile_n=256, tile_m=256))):
+    for name, kw in (("auto", {}), ("128x256", dict(tile_n=256, tile_m=128)), ("256x256", dict(tile_n=256, tile_m=256)), ("2sm", dict(cta_pair=1))):
         ms = timeit(lambda: B.gemm(a, b, out, M=M, N=N, K=K, **kw))
         row.append(f"{name} {ms*1e3:8.1f}us {fl/ms/1e9:7.1f}TF")
     B.gemm(a, b, out, M=M, N=N, K=K, tile_n=256, tile_m=256)

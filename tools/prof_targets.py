@@ -13,6 +13,27 @@ if what == "gemm256":
     out = torch.empty(n, n, dtype=torch.bfloat16, device=dev)
     for _ in range(4):
         B.gemm(a, b, out, M=n, N=n, K=n)
+elif what == "gemm_qkv":
+    # short-K, epilogue-heavy: GPT-2 qkv forward (bias) and attn_proj forward (bias + residual)
+    a = torch.randn(8192, 768, device=dev).to(torch.bfloat16); b = torch.randn(2304, 768, device=dev).to(torch.bfloat16)
+    out = torch.empty(8192, 2304, dtype=torch.bfloat16, device=dev)
+    bias = torch.zeros(2304, dtype=torch.float32, device=dev)
+    for _ in range(4):
+        B.gemm(a, b, out, M=8192, N=2304, K=768, bias=bias)
+elif what == "gemm_shortk":
+    # plain epilogue, K = 768, many tiles per SM: steady-state mainloop vs epilogue
+    a = torch.randn(8192, 768, device=dev).to(torch.bfloat16); b = torch.randn(8192, 768, device=dev).to(torch.bfloat16)
+    out = torch.empty(8192, 8192, dtype=torch.bfloat16, device=dev)
+    for _ in range(4):
+        B.gemm(a, b, out, M=8192, N=8192, K=768)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        B.gemm(a, b, out, M=8192, N=8192, K=768)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 10
+    print(f"8192x8192x768 plain: {ms*1e3:.1f} us  {2*8192*8192*768/ms/1e9:.0f} TFLOP/s")
 elif what == "flash":
     from b200ddp.ops import functional as Fn
     qkv = torch.randn(8, 1024, 3 * 768, device=dev).to(torch.bfloat16)
