@@ -608,16 +608,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
     // on we read what earlier kernels wrote: wait for them (no-op without PDL).
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
+    // Producer and MMA loops are walked by their WHOLE warp with one elected lane issuing: control
+    // flow and every address/descriptor stay warp-uniform, so the compiler keeps them in uniform
+    // registers and issues UTMALDG / UTCHMMA directly.  (A `lane == 0` branch made it wrap each such
+    // instruction in an elect/broadcast loop: ~75 instructions per k-block on one thread, and the
+    // mainloop was bound by MMA *issue*, ~800 cycles per k-block against 540 of tensor work.)
     if (warp == 0) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
-            uint32_t stage = 0, phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const TileInfo t = decode_tile<BN>(p, tile);
-                if (t.skip) continue;
-                const int m0 = t.m0, n0 = t.n0;
-                for (int kb = t.kb0; kb < t.kb1; ++kb) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint32_t stage = 0, phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const TileInfo t = decode_tile<BN>(p, tile);
+            if (t.skip) continue;
+            const int m0 = t.m0, n0 = t.n0;
+            for (int kb = t.kb0; kb < t.kb1; ++kb) {
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                if (elect_one()) {
                     mbar_arrive_expect_tx(&full_bar[stage], A_STAGE_BYTES + B_STAGE_BYTES);
                     uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
                     uint8_t* sb = smem_b + stage * B_STAGE_BYTES;
@@ -636,45 +641,48 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                         for (int j = 0; j < (BN >= 64 ? BN / 64 : 1); ++j)
                             tma_load_4d(sb + j * 8192, &tma_b, &full_bar[stage], n0 + j * 64, k0, t.hb, t.bb);
                     }
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
+                __syncwarp();
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
-            uint32_t stage = 0, phase = 0;
-            int it = 0;
-            // K-major: 8-row groups 1024 B apart, K advances 32 B inside the swizzle row.
-            // MN-major: 64-element chunks 8192 B apart (LBO), 8-k groups 1024 B apart (SBO),
-            //           K advances 16 rows = 2048 B.
-            const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
-            const uint32_t a_kstep = p.a_mn ? 2048u : 32u, b_kstep = p.b_mn ? 2048u : 32u;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const TileInfo t = decode_tile<BN>(p, tile);
-                if (t.skip) continue;
-                const uint32_t as = it & 1;
-                mbar_wait(&tmem_empty[as], ((it >> 1) & 1) ^ 1);
+        uint32_t stage = 0, phase = 0;
+        int it = 0;
+        // K-major: 8-row groups 1024 B apart, K advances 32 B inside the swizzle row.
+        // MN-major: 64-element chunks 8192 B apart (LBO), 8-k groups 1024 B apart (SBO),
+        //           K advances 16 rows = 2048 B.
+        // Descriptors differ only in their 14-bit start-address field (bytes >> 4): build one per
+        // operand and add stage / k-step offsets to it.
+        const uint64_t da0 = umma_smem_desc(smem_u32(smem_a), p.a_mn ? 8192u : 16u, 1024u);
+        const uint64_t db0 = umma_smem_desc(smem_u32(smem_b), p.b_mn ? 8192u : 16u, 1024u);
+        const uint32_t a_k16 = (p.a_mn ? 2048u : 32u) >> 4, b_k16 = (p.b_mn ? 2048u : 32u) >> 4;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const TileInfo t = decode_tile<BN>(p, tile);
+            if (t.skip) continue;
+            const uint32_t as = it & 1;
+            mbar_wait(&tmem_empty[as], ((it >> 1) & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + as * BN;
+            const int kb0 = t.kb0, kb1 = t.kb1;
+            for (int kb = kb0; kb < kb1; ++kb) {
+                mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + as * BN;
-                const int kb0 = t.kb0, kb1 = t.kb1;
-                for (int kb = kb0; kb < kb1; ++kb) {
-                    mbar_wait(&full_bar[stage], phase);
-                    tc_fence_after();
-                    const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
-                    const uint32_t sb = smem_u32(smem_b + stage * B_STAGE_BYTES);
+                const uint64_t da = da0 + (uint64_t)(stage * (A_STAGE_BYTES >> 4));
+                const uint64_t db = db0 + (uint64_t)(stage * (B_STAGE_BYTES >> 4));
+                if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < BK / 16; ++k) {
-                        const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024u);
-                        const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024u);
-                        umma_bf16(d_tmem, da, db, p.idesc, ((kb - kb0) | k) != 0 ? 1u : 0u);
-                    }
+                    for (int k = 0; k < BK / 16; ++k)
+                        umma_bf16(d_tmem, da + (uint64_t)(k * a_k16), db + (uint64_t)(k * b_k16), p.idesc,
+                                  (kb > kb0 || k > 0) ? 1u : 0u);
                     umma_commit(&empty_bar[stage]);  // slot reusable once these MMAs retire
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                    if (kb == kb1 - 1) umma_commit(&tmem_full[as]);  // accumulator complete
                 }
-                umma_commit(&tmem_full[as]);  // accumulator complete
-                ++it;
+                __syncwarp();
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
+            ++it;
         }
     } else {
         // ===================== epilogue =====================
@@ -790,13 +798,14 @@ gemm_kernel_m256(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
     if (warp == 0) {
-        if (lane == 0) {
-            uint32_t stage = 0, phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m0 = (tile % p.num_m_blocks) * BM2;
-                const int n0 = (tile / p.num_m_blocks) * BN;
-                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
+        // TMA producer: whole warp walks the loop, one elected lane issues (see gemm_kernel)
+        uint32_t stage = 0, phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int m0 = (tile % p.num_m_blocks) * BM2;
+            const int n0 = (tile / p.num_m_blocks) * BN;
+            for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                if (elect_one()) {
                     mbar_arrive_expect_tx(&full_bar[stage], A2_STAGE_BYTES + B2_STAGE_BYTES);
                     uint8_t* sa = smem_a + stage * A2_STAGE_BYTES;
                     uint8_t* sb = smem_b + stage * B2_STAGE_BYTES;
@@ -815,24 +824,27 @@ gemm_kernel_m256(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
                         for (int j = 0; j < BN / 64; ++j)
                             tma_load_4d(sb + j * 8192, &tma_b, &full_bar[stage], n0 + j * 64, k0, 0, 0);
                     }
-                    if (++stage == STAGES2) { stage = 0; phase ^= 1; }
                 }
+                __syncwarp();
+                if (++stage == STAGES2) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            uint32_t stage = 0, phase = 0;
-            int it = 0;
-            const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
-            const uint32_t a_kstep = p.a_mn ? 2048u : 32u, b_kstep = p.b_mn ? 2048u : 32u;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-                const uint32_t par = (uint32_t)(it & 1);
-                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-                    mbar_wait(&full_bar[stage], phase);
-                    tc_fence_after();
-                    const uint32_t sa = smem_u32(smem_a + stage * A2_STAGE_BYTES);
-                    const uint32_t sb = smem_u32(smem_b + stage * B2_STAGE_BYTES);
-                    const bool last = kb == p.num_k_blocks - 1;
+        // MMA issuer: whole warp, one elected lane
+        uint32_t stage = 0, phase = 0;
+        int it = 0;
+        const uint64_t da0 = umma_smem_desc(smem_u32(smem_a), p.a_mn ? 8192u : 16u, 1024u);
+        const uint64_t db0 = umma_smem_desc(smem_u32(smem_b), p.b_mn ? 8192u : 16u, 1024u);
+        const uint32_t a_k16 = (p.a_mn ? 2048u : 32u) >> 4, b_k16 = (p.b_mn ? 2048u : 32u) >> 4;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+            const uint32_t par = (uint32_t)(it & 1);
+            for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                mbar_wait(&full_bar[stage], phase);
+                tc_fence_after();
+                const uint64_t da = da0 + (uint64_t)(stage * (A2_STAGE_BYTES >> 4));
+                const uint64_t db = db0 + (uint64_t)(stage * (B2_STAGE_BYTES >> 4));
+                const bool last = kb == p.num_k_blocks - 1;
+                if (elect_one()) {
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
                         if (kb == 0) {  // this half of TMEM must have been drained (previous tile)
@@ -841,18 +853,16 @@ gemm_kernel_m256(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
                         }
                         // rows 128..255 of the A stage start 16 KB in (K-major: 128 rows x 128 B;
                         // MN-major: two 8 KB chunks)
-                        const uint32_t sah = sa + h * 16384u;
 #pragma unroll
-                        for (int k = 0; k < BK / 16; ++k) {
-                            const uint64_t da = umma_smem_desc(sah + k * a_kstep, a_lbo, 1024u);
-                            const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024u);
-                            umma_bf16(tmem_base + h * BN, da, db, p.idesc, (kb | k) != 0 ? 1u : 0u);
-                        }
+                        for (int k = 0; k < BK / 16; ++k)
+                            umma_bf16(tmem_base + h * BN, da + (uint64_t)(h * (16384 >> 4) + k * a_k16),
+                                      db + (uint64_t)(k * b_k16), p.idesc, (kb | k) != 0 ? 1u : 0u);
                         if (last) umma_commit(&tmem_full[h]);  // upper half completes first
                     }
                     umma_commit(&empty_bar[stage]);
-                    if (++stage == STAGES2) { stage = 0; phase ^= 1; }
                 }
+                __syncwarp();
+                if (++stage == STAGES2) { stage = 0; phase ^= 1; }
             }
         }
     } else {
@@ -908,9 +918,13 @@ gemm_kernel_m256(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 //   * the leader's MMA thread issues tcgen05.mma.cta_group::2 (M = 256) for both SMs; its commits
 //     are multicast to both CTAs' barriers (ring slot free / accumulator complete)
 //   * every epilogue warp of both CTAs arrives on the leader's tmem_empty barrier
-constexpr int STAGES_2SM = 6;
-constexpr uint32_t B_HALF_BYTES = 128 * BK * 2;  // 16 KB
-constexpr uint32_t GEMM_2SM_SMEM = STAGES_2SM * (A_STAGE_BYTES + B_HALF_BYTES) + 1024 + 256 + BIAS_SMEM_BYTES;
+// Pair tiles are 256 x BN with BN = 256 or 128 (the narrower one for problems with few tiles:
+// weight gradients, N = 768 outputs).
+template <int BN> struct Stages2sm { static constexpr int value = BN >= 256 ? 6 : 8; };
+template <int BN>
+constexpr uint32_t gemm_2sm_smem() {
+    return Stages2sm<BN>::value * (A_STAGE_BYTES + (BN / 2) * BK * 2) + 1024 + 256 + BIAS_SMEM_BYTES;
+}
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
@@ -927,7 +941,7 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t rank) 
     return r;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ void tma_load_4d_pair(void* smem_dst, const CUtensorMap* map, uint32_t leader_bar,
                                                  int c0, int c1, int c2, int c3) {
@@ -957,11 +971,13 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
         : "memory");
 }
 
+template <int BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(gemm_threads<true>(), 1)
 gemm_kernel_2sm(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                 const GemmParams p) {
-    constexpr int BN = 256;
-    constexpr int STAGES = STAGES_2SM;
+    constexpr int STAGES = Stages2sm<BN>::value;
+    constexpr uint32_t B_HALF_BYTES = (BN / 2) * BK * 2;   // this CTA's half of the B tile
+    constexpr uint32_t TMEM_COLS = 2 * BN;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smem_a = smem;
@@ -996,7 +1012,7 @@ gemm_kernel_2sm(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "r"(512u)
+                     "r"(TMEM_COLS)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     }
@@ -1008,14 +1024,14 @@ gemm_kernel_2sm(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
     if (warp == 0) {
-        // ===================== TMA producer (both CTAs) =====================
-        if (lane == 0) {
-            uint32_t stage = 0, phase = 0;
-            for (int tile = pair; tile < num_tiles; tile += num_pairs) {
-                const int m0 = (tile % p.num_m_blocks) * 256 + (int)rank * 128;   // this CTA's A rows
-                const int n0 = (tile / p.num_m_blocks) * BN + (int)rank * 128;    // this CTA's half of B
-                for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
+        // ===================== TMA producer (both CTAs; whole warp, one elected lane) =====================
+        uint32_t stage = 0, phase = 0;
+        for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+            const int m0 = (tile % p.num_m_blocks) * 256 + (int)rank * 128;   // this CTA's A rows
+            const int n0 = (tile / p.num_m_blocks) * BN + (int)rank * (BN / 2);  // this CTA's half of B
+            for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                if (elect_one()) {
                     const uint32_t lbar = mapa_u32(smem_u32(&full_bar[stage]), 0);
                     if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * (A_STAGE_BYTES + B_HALF_BYTES));
                     uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
@@ -1031,19 +1047,21 @@ gemm_kernel_2sm(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
                         tma_load_4d_pair(sb, &tma_b, lbar, k0, n0, 0, 0);
                     } else {
 #pragma unroll
-                        for (int j = 0; j < 2; ++j) tma_load_4d_pair(sb + j * 8192, &tma_b, lbar, n0 + j * 64, k0, 0, 0);
+                        for (int j = 0; j < BN / 128; ++j) tma_load_4d_pair(sb + j * 8192, &tma_b, lbar, n0 + j * 64, k0, 0, 0);
                     }
-                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
+                __syncwarp();
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer (leader CTA only) =====================
-        if (lane == 0 && rank == 0) {
+        // ===================== MMA issuer (leader CTA only; whole warp, one elected lane) =====================
+        if (rank == 0) {
             uint32_t stage = 0, phase = 0;
             int it = 0;
-            const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
-            const uint32_t a_kstep = p.a_mn ? 2048u : 32u, b_kstep = p.b_mn ? 2048u : 32u;
+            const uint64_t da0 = umma_smem_desc(smem_u32(smem_a), p.a_mn ? 8192u : 16u, 1024u);
+            const uint64_t db0 = umma_smem_desc(smem_u32(smem_b), p.b_mn ? 8192u : 16u, 1024u);
+            const uint32_t a_k16 = (p.a_mn ? 2048u : 32u) >> 4, b_k16 = (p.b_mn ? 2048u : 32u) >> 4;
             for (int tile = pair; tile < num_tiles; tile += num_pairs, ++it) {
                 const uint32_t as = it & 1;
                 mbar_wait(&tmem_empty[as], ((it >> 1) & 1) ^ 1);
@@ -1052,18 +1070,19 @@ gemm_kernel_2sm(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
                 for (int kb = 0; kb < p.num_k_blocks; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
-                    const uint32_t sb = smem_u32(smem_b + stage * B_HALF_BYTES);
+                    const uint64_t da = da0 + (uint64_t)(stage * (A_STAGE_BYTES >> 4));
+                    const uint64_t db = db0 + (uint64_t)(stage * (B_HALF_BYTES >> 4));
+                    if (elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < BK / 16; ++k) {
-                        const uint64_t da = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024u);
-                        const uint64_t db = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024u);
-                        umma_bf16_pair(d_tmem, da, db, p.idesc, (kb | k) != 0 ? 1u : 0u);
+                        for (int k = 0; k < BK / 16; ++k)
+                            umma_bf16_pair(d_tmem, da + (uint64_t)(k * a_k16), db + (uint64_t)(k * b_k16), p.idesc,
+                                           (kb | k) != 0 ? 1u : 0u);
+                        umma_commit_pair(&empty_bar[stage]);
+                        if (kb == p.num_k_blocks - 1) umma_commit_pair(&tmem_full[as]);
                     }
-                    umma_commit_pair(&empty_bar[stage]);
+                    __syncwarp();
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                umma_commit_pair(&tmem_full[as]);
             }
         }
     } else {
@@ -1085,7 +1104,7 @@ gemm_kernel_2sm(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
             __nv_bfloat16* drow = row_ok ? reinterpret_cast<__nv_bfloat16*>(p.D) + (int64_t)row * p.ldd : nullptr;
             const __nv_bfloat16* arow = (row_ok && p.aux) ? p.aux + (int64_t)row * p.ldaux : nullptr;
             __nv_bfloat16* zrow = (row_ok && p.aux_out) ? p.aux_out + (int64_t)row * p.ldd : nullptr;
-            mbar_wait(&tmem_full[as], (it >> 1) & 1);
+            mbar_wait(&tmem_full[as], (it >> 1) & 1);  // multicast commit from the leader
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + as * BN;
             fast_drain(taddr, n0, N, half * (CH / 2), (half + 1) * (CH / 2), mode, drow, arow, zrow,
@@ -1101,7 +1120,7 @@ gemm_kernel_2sm(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
     cluster_sync_all();   // the leader's MMAs read the peer's shared memory until the last commit
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
     }
 }
 
@@ -1187,19 +1206,20 @@ static int launch_m256(const CUtensorMap& ma, const CUtensorMap& mb, const GemmP
     return 0;
 }
 
+template <int BN>
 static int launch_2sm(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int ctas, cudaStream_t s) {
     static const bool pdl = getenv("B200DDP_NO_PDL") == nullptr;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned)ctas);   // even; the kernel carries __cluster_dims__(2, 1, 1)
     cfg.blockDim = dim3(gemm_threads<true>());
-    cfg.dynamicSmemBytes = GEMM_2SM_SMEM;
+    cfg.dynamicSmemBytes = gemm_2sm_smem<BN>();
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel_2sm, ma, mb, p));
+    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel_2sm<BN>, ma, mb, p));
     b200_count_launch(1);
     B200_CUDA_OK(cudaGetLastError());
     return 0;
@@ -1236,6 +1256,19 @@ static int pick_tile_n(const b200_gemm_desc* d, int sms) {
     return best;
 }
 
+// Pair-tile width by a two-term cost: waves of pair tiles x (k-blocks x time per k-block + epilogue).
+// Units of 10 ns, fitted to the GPT-2 shapes on B200 (tools/gpt2_gemm_shapes.py).
+static int pick_pair_tile_n(const b200_gemm_desc* d, int sms) {
+    if (d->N <= 128) return 128;
+    const int64_t pairs = sms / 2 > 0 ? sms / 2 : 1;
+    const int64_t mblk = (d->M + 255) / 256, kb = (d->K + BK - 1) / BK;
+    const int64_t w256 = (mblk * ((d->N + 255) / 256) + pairs - 1) / pairs;
+    const int64_t w128 = (mblk * ((d->N + 127) / 128) + pairs - 1) / pairs;
+    // per k-block 0.34 us (256 wide) / 0.28 us (128 wide) per SM, plus the exposed epilogue
+    const int64_t c256 = w256 * (kb * 34 + 150), c128 = w128 * (kb * 28 + 75);
+    return c128 < c256 ? 128 : 256;
+}
+
 }  // namespace b200
 
 int b200_gemm_init();
@@ -1263,23 +1296,16 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
                  (long long)d->lda, (long long)d->ldb);
     B200_REQUIRE(((uintptr_t)d->A % 16) == 0 && ((uintptr_t)d->B % 16) == 0, "gemm: A/B must be 16-byte aligned");
     const int sms = sm_count();
-    int bn = d->tile_n ? d->tile_n : (d->cta_pair == 1 ? 256 : pick_tile_n(d, sms));
-    B200_REQUIRE(bn == 16 || bn == 32 || bn == 64 || bn == 128 || bn == 256, "gemm: tile_n %d unsupported", bn);
-    B200_REQUIRE(!(d->b_mn_major && bn < 64), "gemm: MN-major B needs tile_n >= 64");
-    if (d->epilogue == B200_EPI_SOFTMAX_CE) {
-        B200_REQUIRE(d->N <= bn && bn <= 32, "gemm: fused cross-entropy needs N <= 32 (got %d)", d->N);
-        B200_REQUIRE(d->targets != nullptr, "gemm: fused cross-entropy needs targets");
-    }
-    if (d->epilogue == B200_EPI_GATE_POSITIVE || d->epilogue == B200_EPI_GELU_BWD)
-        B200_REQUIRE(d->aux != nullptr, "gemm: epilogue %d needs aux", d->epilogue);
-
-    CUtensorMap ma, mb;
-    int rc;
     const int nbi = d->batch_inner > 1 ? d->batch_inner : 1, nbo = d->batch_outer > 1 ? d->batch_outer : 1;
     if (nbi * nbo > 1)
         B200_REQUIRE(d->epilogue == B200_EPI_NONE && !d->aux && !d->bias && !d->colsum && !d->split_k,
                      "gemm: batched mode supports the plain epilogue only");
     B200_REQUIRE(d->causal >= 0 && d->causal <= 3, "gemm: causal mode %d unknown", d->causal);
+    B200_REQUIRE(d->tile_m == 0 || d->tile_m == 128 || d->tile_m == 256, "gemm: tile_m must be 0, 128 or 256");
+    if (d->epilogue == B200_EPI_GATE_POSITIVE || d->epilogue == B200_EPI_GELU_BWD)
+        B200_REQUIRE(d->aux != nullptr, "gemm: epilogue %d needs aux", d->epilogue);
+
+    // ---- kernel selection
     // FAST epilogue kernels: bf16 output with 16-byte-aligned rows and one of the light epilogues
     const bool light = d->epilogue == B200_EPI_NONE || d->epilogue == B200_EPI_GELU || d->epilogue == B200_EPI_GELU_BWD;
     const bool vec_d = !d->d_fp32 && (d->ldd % 8) == 0 && ((uintptr_t)d->D % 16) == 0 &&
@@ -1287,31 +1313,47 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
     const bool vec_aux = !d->aux || ((d->ldaux % 8) == 0 && ((uintptr_t)d->aux % 16) == 0 && (d->N % 8) == 0);
     const bool vec_z = !d->aux_out || (((uintptr_t)d->aux_out % 16) == 0 && (d->N % 8) == 0);
     static const bool fast_off = getenv("B200DDP_NO_FAST_EPILOGUE") != nullptr;
-    const bool fast = !fast_off && bn >= 64 && light && vec_d && vec_aux && vec_z && !d->colsum && !d->split_k &&
-                      !(d->epilogue == B200_EPI_GELU_BWD && !d->aux);
+    static const bool m256_off = getenv("B200DDP_NO_M256") != nullptr;
+    static const bool pair_off = getenv("B200DDP_NO_PAIR") != nullptr;
+    const bool fast_cfg = !fast_off && light && vec_d && vec_aux && vec_z && !d->colsum && !d->split_k;
     // Large-tile kernels for plain non-batched problems with a light epilogue:
     //   256x256 dual accumulator, one SM   long reductions (K >= 4096) with at least a wave of tiles:
     //                                      1481 vs 1288 TFLOP/s at 8192^3; with short K its
     //                                      single-buffered accumulators expose the epilogue
-    //   256x256 per SM pair (cta_group::2) everything else that picked 256-wide tiles: double-buffered
-    //                                      accumulators and 32 KB of operands per SM per k-block
-    static const bool m256_off = getenv("B200DDP_NO_M256") != nullptr;
-    static const bool pair_off = getenv("B200DDP_NO_PAIR") != nullptr;
-    const bool big_ok = bn == 256 && nbi * nbo == 1 && !d->causal && fast;
+    //   256xBN per SM pair (cta_group::2)  everything else: double-buffered accumulators, and each SM
+    //                                      stages only half of B
+    const bool big_cfg = fast_cfg && nbi * nbo == 1 && !d->causal;
     const int64_t t2 = (int64_t)((d->M + BM2 - 1) / BM2) * ((d->N + 255) / 256);
-    bool m256 = big_ok && (d->tile_m == 256 || (d->tile_m == 0 && d->cta_pair != 1 && !m256_off && d->M >= 512 &&
-                                                 d->K >= 4096 && t2 >= sms));
-    bool pair = big_ok && !m256 && d->M > 128 &&
-                (d->cta_pair == 1 || (d->cta_pair == 0 && d->tile_m == 0 && !pair_off));
+    bool m256 = big_cfg && (d->tile_n == 0 || d->tile_n == 256) &&
+                (d->tile_m == 256 || (d->tile_m == 0 && d->tile_n == 0 && d->cta_pair != 1 && !m256_off &&
+                                      d->M >= 512 && d->K >= 4096 && t2 >= sms));
+    int pair_bn = 0;   // 0: not the pair kernel
+    if (big_cfg && !m256 && d->tile_m == 0 && d->M > 128 && d->N > 64 &&
+        (d->cta_pair == 1 || (d->cta_pair == 0 && d->tile_n == 0 && !pair_off))) {
+        if (d->tile_n == 128 || d->tile_n == 256) pair_bn = d->tile_n;
+        else if (d->tile_n == 0) pair_bn = pick_pair_tile_n(d, sms);
+    }
+    const bool pair = pair_bn != 0;
     B200_REQUIRE(d->cta_pair != 1 || pair,
-                 "gemm: cta_pair needs tile_n 256 (or auto), M > 128, a non-batched problem and a light epilogue with bf16 D");
-    B200_REQUIRE(d->tile_m == 0 || d->tile_m == 128 || d->tile_m == 256, "gemm: tile_m must be 0, 128 or 256");
+                 "gemm: cta_pair needs tile_n 0/128/256, tile_m 0, M > 128, N > 64, a non-batched problem and a light "
+                 "epilogue with bf16 D");
     B200_REQUIRE(d->tile_m != 256 || m256,
                  "gemm: tile_m 256 needs tile_n 256, a non-batched problem and a light epilogue with bf16 output");
+    int bn = pair ? pair_bn : (m256 ? 256 : (d->tile_n ? d->tile_n : pick_tile_n(d, sms)));
+    B200_REQUIRE(bn == 16 || bn == 32 || bn == 64 || bn == 128 || bn == 256, "gemm: tile_n %d unsupported", bn);
+    B200_REQUIRE(!(d->b_mn_major && bn < 64), "gemm: MN-major B needs tile_n >= 64");
+    if (d->epilogue == B200_EPI_SOFTMAX_CE) {
+        B200_REQUIRE(d->N <= bn && bn <= 32, "gemm: fused cross-entropy needs N <= 32 (got %d)", d->N);
+        B200_REQUIRE(d->targets != nullptr, "gemm: fused cross-entropy needs targets");
+    }
+    const bool fast = fast_cfg && bn >= 64;
+
+    CUtensorMap ma, mb;
+    int rc;
     if (!d->a_mn_major) rc = make_map(&ma, d->A, d->K, d->M, d->lda, BK, m256 ? BM2 : BM, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
     else rc = make_map(&ma, d->A, d->M, d->K, d->lda, 64, BK, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
     if (rc) return rc;
-    if (!d->b_mn_major) rc = make_map(&mb, d->B, d->K, d->N, d->ldb, BK, pair ? 128 : bn, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
+    if (!d->b_mn_major) rc = make_map(&mb, d->B, d->K, d->N, d->ldb, BK, pair ? bn / 2 : bn, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
     else rc = make_map(&mb, d->B, d->N, d->K, d->ldb, 64, BK, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
     if (rc) return rc;
 
@@ -1361,7 +1403,7 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
         if (d->max_ctas > 0 && d->max_ctas < c2) c2 = d->max_ctas;
         c2 &= ~1;
         B200_REQUIRE(c2 >= 2, "gemm: the two-SM kernel needs at least 2 CTAs");
-        return launch_2sm(ma, mb, p, c2, s);
+        return bn == 256 ? launch_2sm<256>(ma, mb, p, c2, s) : launch_2sm<128>(ma, mb, p, c2, s);
     }
     if (m256) return launch_m256(ma, mb, p, ctas, s);
     if (fast) {
@@ -1392,6 +1434,7 @@ int b200_gemm_init() {
     PREP(64, true); PREP(128, true); PREP(256, true);
 #undef PREP
     B200_CUDA_OK(cudaFuncSetAttribute(gemm_kernel_m256, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM2_SMEM));
-    B200_CUDA_OK(cudaFuncSetAttribute(gemm_kernel_2sm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GEMM_2SM_SMEM));
+    B200_CUDA_OK(cudaFuncSetAttribute(gemm_kernel_2sm<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_2sm_smem<256>()));
+    B200_CUDA_OK(cudaFuncSetAttribute(gemm_kernel_2sm<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gemm_2sm_smem<128>()));
     return 0;
 }

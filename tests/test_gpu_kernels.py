@@ -591,11 +591,12 @@ def test_gemm_256x256_dual_accumulator_tiles(B, M, N, K, a_mn, b_mn):
     _check_big_tile_kernel(B, M, N, K, a_mn, b_mn, tile_n=256, tile_m=256)
 
 
+@pytest.mark.parametrize("tile_n", [0, 128, 256])
 @pytest.mark.parametrize("M,N,K,a_mn,b_mn", _BIG_TILE_SHAPES)
-def test_gemm_two_sm_pair_tiles(B, M, N, K, a_mn, b_mn):
-    """tcgen05 cta_group::2: one 256x256 tile per SM pair, each CTA staging half of B."""
+def test_gemm_two_sm_pair_tiles(B, M, N, K, a_mn, b_mn, tile_n):
+    """tcgen05 cta_group::2: one 256 x tile_n tile per SM pair, each CTA staging half of B."""
     torch.manual_seed(22)
-    _check_big_tile_kernel(B, M, N, K, a_mn, b_mn, cta_pair=1)
+    _check_big_tile_kernel(B, M, N, K, a_mn, b_mn, cta_pair=1, tile_n=tile_n)
 
 
 @pytest.mark.parametrize("tile_n", [64, 128, 256])

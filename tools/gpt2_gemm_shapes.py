@@ -32,7 +32,7 @@ def bf(*shape):
 T = 8192
 C = 768
 tiles = (("auto", {}), ("128x256", dict(tile_n=256, tile_m=128)), ("128x128", dict(tile_n=128, tile_m=128)),
-         ("256x256", dict(tile_n=256, tile_m=256)), ("2sm", dict(cta_pair=1)))
+         ("256x256", dict(tile_n=256, tile_m=256)), ("2sm256", dict(cta_pair=1, tile_n=256)), ("2sm128", dict(cta_pair=1, tile_n=128)))
 total = {k: 0.0 for k, _ in tiles}
 total["cublas"] = 0.0
 per_layer = 12
@@ -91,7 +91,12 @@ for lname, N, K, extra in (("qkv", 2304, C, {}), ("attn_proj", C, C, {"res": Tru
     msr = timeit(lambda i: torch.matmul(dyv[i % POOL].t(), x[i % POOL]))
     for k in total:
         total[k] += (msr if k == "cublas" else ms) * count
-    print(f"{lname + ' wgrad':<22s} {N}x{K}x{T}  policy {ms*1e3:7.1f}us {fl/ms/1e9:6.0f}TF  cublas {msr*1e3:7.1f}us {fl/msr/1e9:6.0f}TF",
-          flush=True)
+    extra_cols = []
+    for tname, tkw in (("2sm256", dict(cta_pair=1, tile_n=256)), ("2sm128", dict(cta_pair=1, tile_n=128))):
+        m2 = timeit(lambda i: B.gemm(dyv[i % POOL], x[i % POOL], dsts[i % POOL], M=N, N=K, K=T, a_mn_major=True,
+                                     b_mn_major=True, **tkw))
+        extra_cols.append(f"{tname} {m2*1e3:7.1f}us {fl/m2/1e9:6.0f}TF")
+    print(f"{lname + ' wgrad':<22s} {N}x{K}x{T}  policy {ms*1e3:7.1f}us {fl/ms/1e9:6.0f}TF  " + "  ".join(extra_cols) +
+          f"  cublas {msr*1e3:7.1f}us {fl/msr/1e9:6.0f}TF", flush=True)
 
 print("per-step GEMM time (ms):", {k: round(v, 3) for k, v in total.items()})
