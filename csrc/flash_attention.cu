@@ -96,49 +96,63 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaParam
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
     if (warp == 4) {
-        if (lane == 0) {
-            auto load_kv = [&](int j) {
-                const int st = j & 1;
-                mbar_arrive_expect_tx(&k_full[st], FA_TILE_BYTES);
-                tma_load_4d(s_k + st * FA_TILE_BYTES, &tma_qkv, &k_full[st], 0, 1 * p.H + h, j * FA_BLOCK, b);
-                mbar_arrive_expect_tx(&v_full[st], FA_TILE_BYTES);
-                tma_load_4d(s_v + st * FA_TILE_BYTES, &tma_qkv, &v_full[st], 0, 2 * p.H + h, j * FA_BLOCK, b);
-            };
+        // The whole warp walks the loop; one elected lane issues TMA / MMA / commits.  Addresses and
+        // descriptors stay warp-uniform (uniform registers), so each UTCHMMA is a single instruction
+        // instead of an elect/broadcast loop -- the MMA issue sits on the critical path between the
+        // softmax phases.  Descriptors differ only in the start-address field (bytes >> 4).
+        auto load_kv = [&](int j) {
+            const int st = j & 1;
+            mbar_arrive_expect_tx(&k_full[st], FA_TILE_BYTES);
+            tma_load_4d(s_k + st * FA_TILE_BYTES, &tma_qkv, &k_full[st], 0, 1 * p.H + h, j * FA_BLOCK, b);
+            mbar_arrive_expect_tx(&v_full[st], FA_TILE_BYTES);
+            tma_load_4d(s_v + st * FA_TILE_BYTES, &tma_qkv, &v_full[st], 0, 2 * p.H + h, j * FA_BLOCK, b);
+        };
+        if (elect_one()) {
             mbar_arrive_expect_tx(q_full, FA_TILE_BYTES);
             tma_load_4d(s_q, &tma_qkv, q_full, 0, 0 * p.H + h, q0, b);
             load_kv(0);
             if (nblocks > 1) load_kv(1);
-            const uint32_t idesc_s = fa_idesc(128, false), idesc_o = fa_idesc(64, true);
-            const uint32_t aq = smem_u32(s_q), ap = smem_u32(s_p);
-            mbar_wait(q_full, 0);
-            for (int j = 0; j < nblocks; ++j) {
-                const int st = j & 1;
-                const uint32_t kv_par = (uint32_t)((j >> 1) & 1);
-                // ---- S = Q K^T
-                mbar_wait(&k_full[st], kv_par);
-                tc_fence_after();
-                const uint32_t ak = smem_u32(s_k + st * FA_TILE_BYTES);
+        }
+        __syncwarp();
+        const uint32_t idesc_s = fa_idesc(128, false), idesc_o = fa_idesc(64, true);
+        const uint64_t dq_k = umma_smem_desc(smem_u32(s_q), 16, 1024);       // Q, K-major
+        const uint64_t dk_k0 = umma_smem_desc(smem_u32(s_k), 16, 1024);      // K stage 0, K-major
+        const uint64_t dp_k = umma_smem_desc(smem_u32(s_p), 16, 1024);       // P, K-major
+        const uint64_t dv_mn0 = umma_smem_desc(smem_u32(s_v), 8192, 1024);   // V stage 0, MN-major
+        mbar_wait(q_full, 0);
+        for (int j = 0; j < nblocks; ++j) {
+            const int st = j & 1;
+            const uint32_t kv_par = (uint32_t)((j >> 1) & 1);
+            const uint64_t dk_k = dk_k0 + (uint64_t)(st * (FA_TILE_BYTES >> 4));
+            const uint64_t dv_mn = dv_mn0 + (uint64_t)(st * (FA_TILE_BYTES >> 4));
+            // ---- S = Q K^T
+            mbar_wait(&k_full[st], kv_par);
+            tc_fence_after();
+            if (elect_one()) {
 #pragma unroll
                 for (int k = 0; k < FA_D / 16; ++k)
-                    umma_bf16(tmem_s, umma_smem_desc(aq + k * 32, 16, 1024), umma_smem_desc(ak + k * 32, 16, 1024),
-                              idesc_s, k != 0 ? 1u : 0u);
+                    umma_bf16(tmem_s, dq_k + (uint64_t)(2 * k), dk_k + (uint64_t)(2 * k), idesc_s, k != 0 ? 1u : 0u);
                 umma_commit(s_full);
-                // ---- O_j = P V once the softmax warps have written P (and left S)
-                mbar_wait(p_full, (uint32_t)(j & 1));
-                tc_fence_after();
-                mbar_wait(&v_full[st], kv_par);
-                tc_fence_after();
-                const uint32_t av = smem_u32(s_v + st * FA_TILE_BYTES);
+            }
+            __syncwarp();
+            // ---- O_j = P V once the softmax warps have written P (and left S)
+            mbar_wait(p_full, (uint32_t)(j & 1));
+            tc_fence_after();
+            mbar_wait(&v_full[st], kv_par);
+            tc_fence_after();
+            if (elect_one()) {
 #pragma unroll
                 for (int kk = 0; kk < FA_BLOCK / 16; ++kk)
-                    umma_bf16(tmem_o, umma_smem_desc(ap + (kk >> 2) * FA_TILE_BYTES + (kk & 3) * 32, 16, 1024),
-                              umma_smem_desc(av + kk * 2048, 8192, 1024), idesc_o, kk != 0 ? 1u : 0u);
+                    umma_bf16(tmem_o, dp_k + (uint64_t)((kk >> 2) * (FA_TILE_BYTES >> 4) + (kk & 3) * 2),
+                              dv_mn + (uint64_t)(kk * 128), idesc_o, kk != 0 ? 1u : 0u);
                 umma_commit(o_full);
                 umma_commit(&kv_empty[st]);
-                if (j + 2 < nblocks) {  // refill this K/V stage for block j+2
-                    mbar_wait(&kv_empty[st], kv_par);
-                    load_kv(j + 2);
-                }
+            }
+            __syncwarp();
+            if (j + 2 < nblocks) {  // refill this K/V stage for block j+2
+                mbar_wait(&kv_empty[st], kv_par);
+                if (elect_one()) load_kv(j + 2);
+                __syncwarp();
             }
         }
     } else {
@@ -315,60 +329,77 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
                    t_dq = tmem_base + 384;
 
     if (warp == 4) {
-        if (lane == 0) {
-            auto load_qdo = [&](int it) {
-                const int st = it & 1, i = kj + it;
-                mbar_arrive_expect_tx(&qdo_full[st], 2 * FA_TILE_BYTES);
-                tma_load_4d(s_q + st * FA_TILE_BYTES, &tma_qkv, &qdo_full[st], 0, 0 * p.H + h, i * FA_BLOCK, b);
-                tma_load_4d(s_do + st * FA_TILE_BYTES, &tma_do, &qdo_full[st], 0, h, i * FA_BLOCK, b);
-            };
+        // whole warp walks the loop, one elected lane issues (see the forward kernel)
+        auto load_qdo = [&](int it) {
+            const int st = it & 1, i = kj + it;
+            mbar_arrive_expect_tx(&qdo_full[st], 2 * FA_TILE_BYTES);
+            tma_load_4d(s_q + st * FA_TILE_BYTES, &tma_qkv, &qdo_full[st], 0, 0 * p.H + h, i * FA_BLOCK, b);
+            tma_load_4d(s_do + st * FA_TILE_BYTES, &tma_do, &qdo_full[st], 0, h, i * FA_BLOCK, b);
+        };
+        if (elect_one()) {
             mbar_arrive_expect_tx(kv_full, 2 * FA_TILE_BYTES);
             tma_load_4d(s_k, &tma_qkv, kv_full, 0, 1 * p.H + h, k0, b);
             tma_load_4d(s_v, &tma_qkv, kv_full, 0, 2 * p.H + h, k0, b);
             load_qdo(0);
             if (niter > 1) load_qdo(1);
-            const uint32_t id_s = fab_idesc(128, false, false);   // S, dP: both operands K-major
-            const uint32_t id_kv = fab_idesc(64, true, true);     // dV, dK: both MN-major
-            const uint32_t id_dq = fab_idesc(64, false, true);    // dQ: dS K-major, K_j MN-major
-            const uint32_t ak = smem_u32(s_k), av = smem_u32(s_v), ap = smem_u32(s_p), ads = smem_u32(s_ds);
-            mbar_wait(kv_full, 0);
-            for (int it = 0; it < niter; ++it) {
-                const int st = it & 1;
-                const uint32_t par2 = (uint32_t)((it >> 1) & 1);
-                mbar_wait(&qdo_full[st], par2);
-                tc_fence_after();
-                const uint32_t aq = smem_u32(s_q + st * FA_TILE_BYTES), ado = smem_u32(s_do + st * FA_TILE_BYTES);
+        }
+        __syncwarp();
+        const uint32_t id_s = fab_idesc(128, false, false);   // S, dP: both operands K-major
+        const uint32_t id_kv = fab_idesc(64, true, true);     // dV, dK: both MN-major
+        const uint32_t id_dq = fab_idesc(64, false, true);    // dQ: dS K-major, K_j MN-major
+        constexpr uint32_t TILE16 = FA_TILE_BYTES >> 4;
+        const uint64_t k_k = umma_smem_desc(smem_u32(s_k), 16, 1024);         // K_j K-major (S)
+        const uint64_t k_mn = umma_smem_desc(smem_u32(s_k), 8192, 1024);      // K_j MN-major (dQ)
+        const uint64_t v_k = umma_smem_desc(smem_u32(s_v), 16, 1024);         // V_j K-major (dP)
+        const uint64_t q_k0 = umma_smem_desc(smem_u32(s_q), 16, 1024);        // Q_i K-major (S)
+        const uint64_t q_mn0 = umma_smem_desc(smem_u32(s_q), 8192, 1024);     // Q_i MN-major (dK)
+        const uint64_t do_k0 = umma_smem_desc(smem_u32(s_do), 16, 1024);      // dO_i K-major (dP)
+        const uint64_t do_mn0 = umma_smem_desc(smem_u32(s_do), 8192, 1024);   // dO_i MN-major (dV)
+        const uint64_t p_mn = umma_smem_desc(smem_u32(s_p), 16384, 1024);     // P^T view (dV)
+        const uint64_t ds_mn = umma_smem_desc(smem_u32(s_ds), 16384, 1024);   // dS^T view (dK)
+        const uint64_t ds_k = umma_smem_desc(smem_u32(s_ds), 16, 1024);       // dS K-major (dQ)
+        mbar_wait(kv_full, 0);
+        for (int it = 0; it < niter; ++it) {
+            const int st = it & 1;
+            const uint32_t par2 = (uint32_t)((it >> 1) & 1);
+            const uint64_t so = (uint64_t)(st * TILE16);
+            mbar_wait(&qdo_full[st], par2);
+            tc_fence_after();
+            if (elect_one()) {
 #pragma unroll
                 for (int k = 0; k < FA_D / 16; ++k)
-                    umma_bf16(t_s, umma_smem_desc(aq + k * 32, 16, 1024), umma_smem_desc(ak + k * 32, 16, 1024), id_s,
-                              k != 0 ? 1u : 0u);
+                    umma_bf16(t_s, q_k0 + so + (uint64_t)(2 * k), k_k + (uint64_t)(2 * k), id_s, k != 0 ? 1u : 0u);
 #pragma unroll
                 for (int k = 0; k < FA_D / 16; ++k)
-                    umma_bf16(t_dp, umma_smem_desc(ado + k * 32, 16, 1024), umma_smem_desc(av + k * 32, 16, 1024), id_s,
-                              k != 0 ? 1u : 0u);
+                    umma_bf16(t_dp, do_k0 + so + (uint64_t)(2 * k), v_k + (uint64_t)(2 * k), id_s, k != 0 ? 1u : 0u);
                 umma_commit(sdp_full);
-                mbar_wait(pds_full, (uint32_t)(it & 1));   // P and dS are in smem, S/dP consumed
-                tc_fence_after();
+            }
+            __syncwarp();
+            mbar_wait(pds_full, (uint32_t)(it & 1));   // P and dS are in smem, S/dP consumed
+            tc_fence_after();
+            if (elect_one()) {
 #pragma unroll
                 for (int kk = 0; kk < FA_BLOCK / 16; ++kk) {   // reduce over the 128 query rows
                     // A^T views of P / dS: [q rows, keys] read MN-major (64-key chunks 16 KB apart)
-                    umma_bf16(t_dv, umma_smem_desc(ap + kk * 2048, 16384, 1024), umma_smem_desc(ado + kk * 2048, 8192, 1024),
-                              id_kv, (it | kk) != 0 ? 1u : 0u);
-                    umma_bf16(t_dk, umma_smem_desc(ads + kk * 2048, 16384, 1024), umma_smem_desc(aq + kk * 2048, 8192, 1024),
-                              id_kv, (it | kk) != 0 ? 1u : 0u);
+                    umma_bf16(t_dv, p_mn + (uint64_t)(kk * 128), do_mn0 + so + (uint64_t)(kk * 128), id_kv,
+                              (it | kk) != 0 ? 1u : 0u);
+                    umma_bf16(t_dk, ds_mn + (uint64_t)(kk * 128), q_mn0 + so + (uint64_t)(kk * 128), id_kv,
+                              (it | kk) != 0 ? 1u : 0u);
                 }
 #pragma unroll
                 for (int kk = 0; kk < FA_BLOCK / 16; ++kk)     // reduce over the 128 keys
-                    umma_bf16(t_dq, umma_smem_desc(ads + (kk >> 2) * FA_TILE_BYTES + (kk & 3) * 32, 16, 1024),
-                              umma_smem_desc(ak + kk * 2048, 8192, 1024), id_dq, kk != 0 ? 1u : 0u);
+                    umma_bf16(t_dq, ds_k + (uint64_t)((kk >> 2) * TILE16 + (kk & 3) * 2), k_mn + (uint64_t)(kk * 128),
+                              id_dq, kk != 0 ? 1u : 0u);
                 umma_commit(dq_full);
                 umma_commit(&qdo_empty[st]);
-                if (it + 2 < niter) {
-                    mbar_wait(&qdo_empty[st], par2);
-                    load_qdo(it + 2);
-                }
+                if (it == niter - 1) umma_commit(dkv_full);
             }
-            umma_commit(dkv_full);
+            __syncwarp();
+            if (it + 2 < niter) {
+                mbar_wait(&qdo_empty[st], par2);
+                if (elect_one()) load_qdo(it + 2);
+                __syncwarp();
+            }
         }
     } else {
         const int r = threadIdx.x;
