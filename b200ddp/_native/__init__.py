@@ -65,6 +65,7 @@ def check(rc: int, what: str) -> None:
         raise RuntimeError(f"{what} failed (code {rc}): {msg.decode() if msg else '?'}")
 
 
-def optimizer_step(opt, start: int, end: int, grad_scale: float) -> None:
+def optimizer_step(opt, start: int, end: int, grad_scale: float, *, device_step: bool = False,
+                   advance: bool = False) -> None:
     from . import bindings
-    bindings.optimizer_step(opt, start, end, grad_scale)
+    bindings.optimizer_step(opt, start, end, grad_scale, device_step=device_step, advance=advance)

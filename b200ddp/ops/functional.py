@@ -598,14 +598,16 @@ class _Conv2d(torch.autograd.Function):
         Q = (W_ + 2 * pad - S) // stride + 1
         y = torch.empty(N * P * Q, Cout, dtype=torch.bfloat16, device=x.device)
         B.gemm(a, w2, y, M=N * P * Q, N=Cout, K=w2.shape[1])
-        ctx.save_for_backward(xh, w2)
+        # the gathered operand is kept for the weight gradient (2.2 GB across ResNet-50 at batch 64:
+        # cheap next to 180 GB of HBM, and it halves the im2col traffic of a step)
+        ctx.save_for_backward(xh, w2, a)
         ctx.w, ctx.geom = w, (R, S, stride, pad, direct, cpad, Cin, P, Q)
         return y.view(N, P, Q, Cout).permute(0, 3, 1, 2)
 
     @staticmethod
     def backward(ctx, dy):
         B = _B()
-        xh, w2 = ctx.saved_tensors
+        xh, w2, a = ctx.saved_tensors
         w = ctx.w
         R, S, stride, pad, direct, cpad, Cin, P, Q = ctx.geom
         N, H, W_, Cp = xh.shape
@@ -628,10 +630,11 @@ class _Conv2d(torch.autograd.Function):
             if cpad:
                 dxh = dxh[..., :Cin]
             dx = dxh.permute(0, 3, 1, 2)
-        a = xh.view(N * H * W_, Cp) if direct else _im2col(xh, R, S, stride, pad)  # recomputed, not stored
-        # reduction over all N*P*Q pixels into a small [Cout, R*S*Cin] output: split-K across SMs
-        dw2 = torch.zeros(Cout, Kt, dtype=torch.float32, device=dy.device)
-        B.gemm(dy2, a, dw2, M=Cout, N=Kt, K=M, a_mn_major=True, b_mn_major=True, split_k=1)
+        # reduction over all N*P*Q pixels into a small [Cout, R*S*Cin] output: split-K across the SMs,
+        # or the two-SM kernel straight to bf16 when the output has enough tiles (_wgrad_into)
+        garena = getattr(w, "_b200_grad", None)
+        dw2 = torch.empty(Cout, Kt, dtype=garena.dtype if garena is not None else torch.bfloat16, device=dy.device)
+        _wgrad_into(dy2, a, dw2)
         dw = dw2.view(Cout, R, S, Cp)[..., :Cin].permute(0, 3, 1, 2)  # back to [Cout, Cin, R, S]
 
         def emit(dst):

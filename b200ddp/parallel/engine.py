@@ -26,6 +26,7 @@ The wrapper exposes ``.module`` like DDP, so the reference's
 from __future__ import annotations
 
 import hashlib
+import os
 from typing import Callable, Dict, List, Optional
 
 import torch
@@ -44,6 +45,11 @@ logger = get_logger("b200ddp")
 def _native():
     from .. import _native as nat
     return nat
+
+
+class _StepGraph:
+    """A captured training step: static input placeholders, the graph, the loss it writes."""
+    __slots__ = ("x", "y", "graph", "loss")
 
 
 class DataParallel(nn.Module):
@@ -68,6 +74,7 @@ class DataParallel(nn.Module):
         use_program: bool = True,
         overlap: bool = True,
         seed: int = 0,
+        step_graph: Optional[bool] = None,
     ):
         super().__init__()
         self.module = module
@@ -186,6 +193,19 @@ class DataParallel(nn.Module):
             from .mlp_program import MLPProgram
             self.program = MLPProgram(self)
 
+        # ---- whole-step CUDA graph for every other model on the b200 backend ----------
+        # zero-grad, forward, loss, backward (with the per-bucket fused all-reduce+optimizer
+        # kernels on the side stream) and the update are captured once per input shape and
+        # replayed: a ResNet-50 step is ~1000 launches and otherwise bound by the host.
+        if step_graph is None:
+            step_graph = os.environ.get("B200DDP_NO_STEP_GRAPH") is None
+        self._graph_ok = bool(step_graph and self.program is None and self.is_cuda and backend == "b200"
+                              and _native().available())
+        self._step_graphs: Dict[tuple, "_StepGraph"] = {}
+        self._graph_warmup: Dict[tuple, int] = {}
+        self._capturing = False
+        self._dev_step_synced = False
+
     # ------------------------------------------------------------------ allocation
     def _alloc(self, n: int, dtype: torch.dtype, peer: bool = False) -> torch.Tensor:
         if peer and self.symm is not None:
@@ -216,7 +236,7 @@ class DataParallel(nn.Module):
 
     # ------------------------------------------------------------------ nn.Module
     def forward(self, *args, **kwargs):
-        if self.training and self.broadcast_buffers and torch.is_grad_enabled():
+        if self.training and self.broadcast_buffers and torch.is_grad_enabled() and not self._capturing:
             self._sync_buffers()
         if self.compute_dtype != torch.float32:
             args = tuple(a.to(self.compute_dtype) if torch.is_tensor(a) and a.dtype == torch.float32
@@ -237,6 +257,13 @@ class DataParallel(nn.Module):
             self.optimizer.step_count += 1
             self._step_index += 1
             return loss
+        if self._graph_ok:
+            return self._graphed_step(data, target)
+        return self._eager_step(data, target)
+
+    def _eager_step(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        if not self._capturing:
+            self._dev_step_synced = False   # eager steps advance the host counter only
         self.module.train()
         self.zero_grad()
         self.begin_backward()
@@ -248,6 +275,60 @@ class DataParallel(nn.Module):
         loss.backward()
         self.finish_step()
         return loss.detach()
+
+    # -- whole-step CUDA graph ---------------------------------------------------------
+    GRAPH_WARMUP_STEPS = 2     # eager steps per input shape before capture (lazy initialisation)
+    GRAPH_MAX_SHAPES = 2       # e.g. the full batch and the short last batch of an epoch
+
+    def _graphed_step(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        key = (tuple(data.shape), data.dtype, tuple(target.shape), target.dtype)
+        st = self._step_graphs.get(key)
+        if st is None:
+            seen = self._graph_warmup.get(key, 0)
+            if seen < self.GRAPH_WARMUP_STEPS or len(self._step_graphs) >= self.GRAPH_MAX_SHAPES:
+                self._graph_warmup[key] = seen + 1
+                return self._eager_step(data, target)
+            st = self._capture_step(key, data, target)
+            if st is None:   # capture failed: stay eager from now on
+                return self._eager_step(data, target)
+        opt = self.optimizer
+        if not self._dev_step_synced:   # eager steps advance the host counter only
+            opt.step_dev[0] = opt.step_count
+            self._dev_step_synced = True
+        if self.training and self.broadcast_buffers:
+            self._sync_buffers()   # SURVEY K4, outside the graph (NCCL plumbing)
+        st.x.copy_(data, non_blocking=True)
+        st.y.copy_(target, non_blocking=True)
+        st.graph.replay()
+        opt.step_count += 1
+        self._step_index += 1
+        return st.loss.clone()
+
+    def _capture_step(self, key, data: torch.Tensor, target: torch.Tensor):
+        opt = self.optimizer
+        saved = (opt.step_count, self._step_index)
+        st = _StepGraph()
+        st.x, st.y = torch.empty_like(data), torch.empty_like(target)
+        st.x.copy_(data)
+        st.y.copy_(target)
+        torch.cuda.synchronize(self.device)
+        st.graph = torch.cuda.CUDAGraph()
+        self._capturing = True
+        try:
+            # thread_local: NCCL's watchdog and the allocator may make CUDA calls on other threads
+            with torch.cuda.graph(st.graph, capture_error_mode="thread_local"):
+                st.loss = self._eager_step(st.x, st.y)
+        except Exception as e:  # noqa: BLE001 - any capture-illegal op in a user model
+            self._graph_ok = False
+            import warnings
+            warnings.warn(f"b200ddp: step graph capture failed, running eagerly ({type(e).__name__}: {e})")
+            st = None
+        finally:
+            self._capturing = False
+            opt.step_count, self._step_index = saved   # nothing ran: capture only records
+        if st is not None:
+            self._step_graphs[key] = st
+        return st
 
     def eval_step(self, data: torch.Tensor, target: torch.Tensor):
         """Validation batch: returns ``(mean loss, correct count)`` as device tensors."""
@@ -294,7 +375,9 @@ class DataParallel(nn.Module):
             # the backward kernels that are still running
             self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(self._comm_stream):
+                last = b.index == len(self.layout.buckets) - 1
                 self.symm.launch_bucket(self, b, 1.0 / self.world_size, step_host=self._step_t,
+                                        device_step=self._capturing, advance=self._capturing and last,
                                         max_blocks=self.comm_max_blocks if self._in_backward else 0)
             return
         if self.is_cuda:
@@ -329,7 +412,8 @@ class DataParallel(nn.Module):
                 if w is not None:
                     w.wait()
                 if use_native:
-                    nat.optimizer_step(opt, b.start, b.end, scale)
+                    nat.optimizer_step(opt, b.start, b.end, scale, device_step=self._capturing,
+                                       advance=self._capturing and b.index == len(self.layout.buckets) - 1)
                 else:
                     opt.step(b.start, b.end, grad_scale=scale, advance=False)
         self._step_index += 1

@@ -90,29 +90,33 @@ __global__ void __launch_bounds__(BN_THREADS) bn_reduce_kernel(
 }
 
 // Sums the per-block partials of both quantities for 32 channels per block: thread (x, y) adds
-// partial rows y, y+8, ... (coalesced), the 8 groups are combined in a fixed order in smem.
+// partial rows y, y+32, ... (coalesced; up to 592 rows, so 32 row groups keep each thread's chain
+// of dependent L2 round trips short), the groups are combined in a fixed order in smem.
+constexpr int BN_FIN_THREADS = 1024;
 __device__ __forceinline__ bool bn_sum_partials(const float* __restrict__ partials, int nparts, int C, int c,
                                                 float& s, float& q) {
-    __shared__ float sm[2][8][33];
+    __shared__ float sm[2][32][33];
     const int x = threadIdx.x & 31, y = threadIdx.x >> 5;
     float a0 = 0.f, a1 = 0.f;
-    if (c < C)
-        for (int p = y; p < nparts; p += 8) {
+    if (c < C) {
+#pragma unroll 4
+        for (int p = y; p < nparts; p += 32) {
             a0 += partials[(int64_t)p * 2 * C + c];
             a1 += partials[(int64_t)p * 2 * C + C + c];
         }
+    }
     sm[0][y][x] = a0;
     sm[1][y][x] = a1;
     __syncthreads();
     s = 0.f; q = 0.f;
     if (y != 0 || c >= C) return false;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) { s += sm[0][k][x]; q += sm[1][k][x]; }
+    for (int k = 0; k < 32; ++k) { s += sm[0][k][x]; q += sm[1][k][x]; }
     return true;
 }
 
 // Forward finalize: mean / rstd from the partial sums, running statistics update.
-__global__ void __launch_bounds__(256) bn_finalize_fwd_kernel(const float* __restrict__ partials, int nparts, int C,
+__global__ void __launch_bounds__(BN_FIN_THREADS) bn_finalize_fwd_kernel(const float* __restrict__ partials, int nparts, int C,
                                                               int64_t rows, float eps, float momentum,
                                                               float* __restrict__ mean, float* __restrict__ rstd,
                                                               float* running_mean, float* running_var) {
@@ -131,7 +135,7 @@ __global__ void __launch_bounds__(256) bn_finalize_fwd_kernel(const float* __res
 }
 
 // Backward finalize: dbeta = sum g, dgamma = sum g*xhat (bf16 or fp32 out) + fp32 copies for dx.
-__global__ void __launch_bounds__(256) bn_finalize_bwd_kernel(const float* __restrict__ partials, int nparts, int C,
+__global__ void __launch_bounds__(BN_FIN_THREADS) bn_finalize_bwd_kernel(const float* __restrict__ partials, int nparts, int C,
                                                               float* __restrict__ sums, void* dgamma, void* dbeta,
                                                               int grads_bf16) {
     const int c = blockIdx.x * 32 + (threadIdx.x & 31);
@@ -262,7 +266,7 @@ extern "C" int b200_batchnorm_fwd(const void* x, const void* residual, void* y, 
         const int grid = bn_reduce_grid(rows, C);
         bn_reduce_kernel<0><<<grid, BN_THREADS, 0, s>>>((const __nv_bfloat16*)x, nullptr, nullptr, nullptr, nullptr,
                                                         (float*)scratch, rows, C, 0);
-        bn_finalize_fwd_kernel<<<(C + 31) / 32, 256, 0, s>>>((const float*)scratch, grid, C, rows, eps, momentum,
+        bn_finalize_fwd_kernel<<<(C + 31) / 32, BN_FIN_THREADS, 0, s>>>((const float*)scratch, grid, C, rows, eps, momentum,
                                                                mean, rstd, running_mean, running_var);
         b200_count_launch(2);
     }
@@ -287,7 +291,7 @@ extern "C" int b200_batchnorm_bwd(const void* dy, const void* x, const void* y, 
     float* sums = partials + (int64_t)BN_MAX_BLOCKS * 2 * C;
     bn_reduce_kernel<1><<<grid, BN_THREADS, 0, s>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,
                                                     (const __nv_bfloat16*)y, mean, rstd, partials, rows, C, relu);
-    bn_finalize_bwd_kernel<<<(C + 31) / 32, 256, 0, s>>>(partials, grid, C, sums, dgamma, dbeta, grads_bf16);
+    bn_finalize_bwd_kernel<<<(C + 31) / 32, BN_FIN_THREADS, 0, s>>>(partials, grid, C, sums, dgamma, dbeta, grads_bf16);
     const int64_t vecs = rows * (C >> 3);
     bn_bwd_apply_kernel<<<bn_ew_grid(vecs), 256, 0, s>>>(
         (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, mean, rstd, gamma, sums,

@@ -1241,6 +1241,9 @@ static int pick_tile_n(const b200_gemm_desc* d, int sms) {
     if (d->N <= 16 && !d->b_mn_major) return 16;
     if (d->N <= 32 && !d->b_mn_major) return 32;
     if (d->N <= 64) return 64;
+    // split-K fills the SMs with K slices, so take the widest tile the output allows (an N = 64
+    // MMA runs the tensor pipe at a quarter of its N = 256 rate)
+    if (d->split_k) return d->N >= 192 ? 256 : (d->N >= 96 ? 128 : 64);
     const int64_t mblk = (d->M + BM - 1) / BM;
     int best = 64;
     int64_t best_cost = INT64_MAX;
