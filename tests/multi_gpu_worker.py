@@ -151,15 +151,17 @@ def check_autograd_overlap(rank, world, dev):
     b = DataParallel(copy.deepcopy(net), backend="nccl", compute_dtype=torch.float32,
                      bucket_cap_mb=0.25, first_bucket_mb=0.01, use_program=False)
     assert len(a.layout.buckets) >= 3
-    for step in range(4):
+    for step in range(8):   # 2 eager steps, then the captured whole-step graph is replayed
         torch.manual_seed(31 * rank + step)
         x = torch.randn(32, 784, device=dev); y = torch.randint(0, 10, (32,), device=dev)
         la = a.train_step(x, y); lb = b.train_step(x, y)
     torch.cuda.synchronize()
     a.consolidate_state()
+    assert len(a._step_graphs) == 1 and a.optimizer.step_count == 8
     assert abs(la.item() - lb.item()) < 1e-4
     assert torch.allclose(a.master, b.master, rtol=1e-4, atol=1e-6), rel(a.master, b.master)
-    log(f"autograd path, {len(a.layout.buckets)} buckets overlapped with backward: b200 == nccl")
+    log(f"autograd path, {len(a.layout.buckets)} buckets overlapped with backward, eager then CUDA-graph replay: "
+        f"b200 == nccl")
 
 
 def main():
