@@ -50,7 +50,24 @@ class GemmDesc(C.Structure):
     ]
 
 
+class RunnerDesc(C.Structure):
+    _fields_ = [
+        ("graph_exec", C.c_void_p), ("stream", C.c_void_p),
+        ("mode", C.c_int), ("slots", C.c_int),
+        ("in_bytes", C.c_int64 * 2),
+        ("dst", C.c_void_p * 2),
+        ("loss_dev", C.c_void_p),
+        ("zero_ptrs", C.c_void_p * 8),
+        ("zero_counts", C.c_int * 8),
+        ("nzero", C.c_int),
+    ]
+
+
 def declare(L: C.CDLL) -> None:
+    L.b200_runner_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(RunnerDesc)]
+    L.b200_runner_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int)]
+    L.b200_runner_finish.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int)]
+    L.b200_runner_destroy.argtypes = [C.c_void_p]
     L.b200_last_error.restype = C.c_char_p
     L.b200_launch_count.restype = C.c_uint64
     L.b200_device_info.argtypes = [C.POINTER(C.c_int)]

@@ -330,6 +330,12 @@ class DataParallel(nn.Module):
             self._step_graphs[key] = st
         return st
 
+    def host_stepper(self, slots: int = 3):
+        """End-to-end stepping from pinned host batches with one native call per step
+        (``parallel/host_stepper.py``): H2D, staging, the captured step and the loss read-back."""
+        from .host_stepper import HostStepper
+        return HostStepper(self, slots=slots)
+
     def eval_step(self, data: torch.Tensor, target: torch.Tensor):
         """Validation batch: returns ``(mean loss, correct count)`` as device tensors."""
         if self.program is not None:

@@ -1,0 +1,150 @@
+"""End-to-end stepping from pinned host batches through the native runner (csrc/runner.cu).
+
+The reference's loop moves every batch with ``.to(device)`` and reads ``loss.item()`` after every
+step (ref ``train.py:133,141``).  ``HostStepper`` is the same contract — host tensors in, a Python
+float out — with the per-step host work done by ONE C call: H2D on a copy stream, staging, launch
+of the captured step, D2H of the loss, and a wait for the *previous* step's loss, so one step is
+always queued behind the one the GPU is running.
+
+    stepper = engine.host_stepper()
+    for hx, hy in pinned_batches:
+        loss_of_previous_step = stepper.step(hx, hy)      # None on the first call
+    last = stepper.finish()
+
+Until the engine has a captured step for the batch shape (the MLP program captures on first use;
+other models after ``DataParallel.GRAPH_WARMUP_STEPS`` eager steps) ``step`` takes the ordinary
+``train_step`` path, so it is always correct to use.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional
+
+import torch
+
+from .. import _native as nat
+from .._native import bindings as B
+
+
+class HostStepper:
+    def __init__(self, engine, slots: int = 3):
+        if not engine.is_cuda or not nat.available():
+            raise RuntimeError("HostStepper needs the model on a CUDA device and the native library")
+        self.engine = engine
+        self.device = engine.device
+        self.slots = slots
+        self._runners: Dict[tuple, int] = {}        # shape key -> native runner handle
+        self._live: Optional[int] = None            # runner with a step in flight
+        self._slow_pending: Optional[torch.Tensor] = None
+        self._prev = C.c_float(0.0)
+        self._valid = C.c_int(0)
+
+    # ------------------------------------------------------------------ graph lookup
+    def _captured(self, hx: torch.Tensor, hy: torch.Tensor):
+        """(graph, mode, dst0, dst1, loss_ptr, zero_list) of the captured step for this shape,
+        or None while the engine is still warming up."""
+        eng = self.engine
+        if eng.program is not None:
+            bsz = int(hx.shape[0])
+            prog = eng.program
+            bufs = prog._get(bsz)
+            if bufs.train_graph is None:
+                bufs.train_graph = prog._capture(prog._train_body, bufs)
+            return bufs.train_graph, 1, bufs.x, bufs.y, bufs.loss.data_ptr(), bufs.zero_train
+        key = (tuple(hx.shape), hx.dtype, tuple(hy.shape), hy.dtype)
+        st = eng._step_graphs.get(key)
+        if st is None:
+            return None
+        return st.graph, 0, st.x, st.y, st.loss.data_ptr(), None
+
+    def _runner_for(self, hx: torch.Tensor, hy: torch.Tensor) -> Optional[int]:
+        key = (tuple(hx.shape), hx.dtype, tuple(hy.shape), hy.dtype)
+        h = self._runners.get(key)
+        if h is not None:
+            return h
+        cap = self._captured(hx, hy)
+        if cap is None:
+            return None
+        graph, mode, dst0, dst1, loss_ptr, zero_list = cap
+        d = B.RunnerDesc()
+        d.graph_exec = graph.raw_cuda_graph_exec()
+        d.stream = torch.cuda.current_stream(self.device).cuda_stream
+        d.mode, d.slots = mode, self.slots
+        d.in_bytes[0], d.in_bytes[1] = hx.numel() * hx.element_size(), hy.numel() * hy.element_size()
+        d.dst[0], d.dst[1] = dst0.data_ptr(), dst1.data_ptr()
+        d.loss_dev = loss_ptr
+        d.nzero = 0
+        if zero_list is not None:
+            ptrs, counts, n = zero_list
+            d.nzero = n
+            for k in range(n):
+                d.zero_ptrs[k], d.zero_counts[k] = ptrs[k], counts[k]
+        if mode == 1 and (hx.dtype != torch.float32 or hy.dtype != torch.int64):
+            raise TypeError("the MLP program stages fp32 features and int64 labels")
+        if mode == 0 and (hx.dtype != dst0.dtype or hy.dtype != dst1.dtype):
+            raise TypeError("host batch dtypes differ from the captured step's inputs")
+        handle = C.c_void_p()
+        nat.check(nat.lib().b200_runner_create(C.byref(handle), C.byref(d)), "b200_runner_create")
+        self._runners[key] = handle.value
+        return handle.value
+
+    # ------------------------------------------------------------------ stepping
+    def step(self, hx: torch.Tensor, hy: torch.Tensor) -> Optional[float]:
+        """Submits one training step on pinned host tensors; returns the loss of the step
+        submitted before it (``None`` on the very first call)."""
+        if not (hx.is_pinned() and hy.is_pinned() and hx.is_contiguous() and hy.is_contiguous()):
+            raise ValueError("HostStepper.step wants contiguous pinned host tensors")
+        eng = self.engine
+        runner = self._runner_for(hx, hy)
+        if runner is None:   # engine still warming up for this shape: ordinary path
+            prev = self._take_previous()
+            self._slow_pending = eng.train_step(hx.to(self.device, non_blocking=True),
+                                                hy.to(self.device, non_blocking=True))
+            return prev
+        # the previous step's loss comes back from the native call itself when it ran on the
+        # same runner; otherwise collect it first
+        prev = None if self._live == runner else self._take_previous()
+        opt = eng.optimizer
+        if eng.program is None:
+            if not eng._dev_step_synced:     # eager steps advance the host counter only
+                opt.step_dev[0] = opt.step_count
+                eng._dev_step_synced = True
+            if eng.training and eng.broadcast_buffers:
+                eng._sync_buffers()          # SURVEY K4 (NCCL plumbing, outside the graph)
+        same = self._live == runner
+        nat.check(nat.lib().b200_runner_step(runner, hx.data_ptr(), hy.data_ptr(), C.byref(self._prev),
+                                             C.byref(self._valid)), "b200_runner_step")
+        self._live = runner
+        opt.step_count += 1
+        eng._step_index += 1
+        if same and self._valid.value:
+            return float(self._prev.value)
+        return prev
+
+    def _take_previous(self) -> Optional[float]:
+        """Loss of the last submitted step, whichever path it took; clears the pending state."""
+        if self._live is not None:
+            nat.check(nat.lib().b200_runner_finish(self._live, C.byref(self._prev), C.byref(self._valid)),
+                      "b200_runner_finish")
+            self._live = None
+            return float(self._prev.value) if self._valid.value else None
+        if self._slow_pending is not None:
+            prev, self._slow_pending = float(self._slow_pending), None
+            return prev
+        return None
+
+    def finish(self) -> Optional[float]:
+        """Waits for the last submitted step and returns its loss."""
+        return self._take_previous()
+
+    def close(self) -> None:
+        self._take_previous()
+        for h in self._runners.values():
+            nat.lib().b200_runner_destroy(h)
+        self._runners.clear()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001 - interpreter shutdown
+            pass

@@ -82,8 +82,9 @@ def max_over_ranks(v: float, device) -> float:
     return float(t.item())
 
 
-def timed(fn_step, steps: int, warmup: int, device, sample_clocks: bool):
-    """fn_step(i) runs step i.  Returns (ms total max-over-ranks, clocks dict)."""
+def timed(fn_step, steps: int, warmup: int, device, sample_clocks: bool, fn_end=None):
+    """fn_step(i) runs step i; fn_end() (optional) drains whatever the steps left pending, still
+    inside the timed region.  Returns (ms total max-over-ranks, clocks dict)."""
     from b200ddp.utils.profiling import ClockSampler
     for i in range(warmup):
         fn_step(i)
@@ -95,6 +96,8 @@ def timed(fn_step, steps: int, warmup: int, device, sample_clocks: bool):
     e0.record()
     for i in range(steps):
         fn_step(warmup + i)
+    if fn_end is not None:
+        fn_end()
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
@@ -131,48 +134,30 @@ def run_ours(args):
     if not args.no_e2e:
         del xs, ys
         hx, hy, n = make_pool(bsz, device, pinned=True, seed=200 + rank)
-        slots = 3
-        dx = [torch.empty(bsz, IN_FEATURES, device=device) for _ in range(slots)]
-        dy = [torch.empty(bsz, dtype=torch.int64, device=device) for _ in range(slots)]
-        host_loss = torch.zeros(args.steps + args.warmup + 1, dtype=torch.float32).pin_memory()
-        copy_stream = torch.cuda.Stream(device)
-        copied = [torch.cuda.Event() for _ in range(slots)]
-        consumed = [torch.cuda.Event() for _ in range(slots)]
-        read_back = [torch.cuda.Event() for _ in range(slots)]
-
-        def stage(i):
-            s = i % slots
-            with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(consumed[s])
-                dx[s].copy_(hx[i % n], non_blocking=True)
-                dy[s].copy_(hy[i % n], non_blocking=True)
-                copied[s].record(copy_stream)
-
-        cur = torch.cuda.current_stream(device)
-        for s in range(slots):
-            consumed[s].record(cur)
-        stage(0)
-        state = {"next": 1}
+        # The public end-to-end API: pinned host batch in, Python float loss out.  Every step
+        # copies its inputs host->device and its loss device->host (read one step late, so a
+        # step is always queued behind the running one); the per-step host work is one native
+        # call (csrc/runner.cu).
+        stepper = engine.host_stepper()
+        losses = []
 
         def e2e_step(i):
-            s = i % slots
-            if state["next"] <= i + 1:      # keep one batch in flight ahead of compute
-                stage(state["next"]); state["next"] += 1
-            cur.wait_event(copied[s])
-            loss = engine.train_step(dx[s], dy[s])
-            consumed[s].record(cur)
-            host_loss[i].copy_(loss, non_blocking=True)      # D2H of this step's result
-            read_back[s].record(cur)
-            if i > 0:
-                read_back[(i - 1) % slots].synchronize()      # previous step's loss is on the host
-                _ = float(host_loss[i - 1])
+            prev = stepper.step(hx[i % n], hy[i % n])
+            if prev is not None:
+                losses.append(prev)
+
+        def e2e_end():
+            losses.append(stepper.finish())     # the last step's loss, inside the timed region
 
         torch.cuda.synchronize()
-        t_ms, _ = timed(e2e_step, args.steps, args.warmup, device, sample_clocks=False)
+        t_ms, _ = timed(e2e_step, args.steps, args.warmup, device, sample_clocks=False, fn_end=e2e_end)
+        assert len(losses) == args.steps + args.warmup, (len(losses), args.steps + args.warmup)
+        host_loss = losses
         e2e = {"value": world * bsz * args.steps / (t_ms / 1e3), "unit": "samples/s",
                "ms_per_step": t_ms / args.steps,
-               "h2d_bytes_per_step": bsz * IN_FEATURES * 4 + bsz * 8, "d2h_bytes_per_step": 4,
-               "final_loss": float(host_loss[args.warmup + args.steps - 2])}
+               "h2d_bytes_per_step": bsz * IN_FEATURES * 4 + bsz * 8,
+               "d2h_bytes_per_step": 8,   # the loss and its sequence number, stored to pinned host memory
+               "final_loss": float(host_loss[-1]), "api": "DataParallel.host_stepper().step(pinned_x, pinned_y)"}
 
     if rank == 0:
         out = {

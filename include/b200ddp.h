@@ -307,6 +307,29 @@ int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200_opt_hparam
 int b200_allreduce(const b200_comm* c, int algo, int64_t start, int64_t n, int is_bf16, void* out,
                    float scale, void* stream);
 
+/* ---------------------------------------------------------------- host step runner
+ * One call per training step on the end-to-end path (ref train.py:133,141: `.to(device)` x2, the
+ * step, `loss.item()`): H2D of the pinned host inputs on a copy stream, staging, cudaGraphLaunch of
+ * a captured step, D2H of the loss, and a wait for the PREVIOUS step's loss.  csrc/runner.cu. */
+typedef struct {
+    void* graph_exec;          /* cudaGraphExec_t of the captured step */
+    void* stream;              /* compute stream the graph is launched on (0 = default stream) */
+    int mode;                  /* 0: D2D copy of the inputs into dst[]; 1: MLP staging kernel
+                                * (dst[0] = bf16 x, dst[1] = int64 labels, clears the zero regions) */
+    int slots;                 /* device input ring, 2..4 */
+    int64_t in_bytes[2];       /* bytes of input 0 (fp32 x / tokens) and input 1 (labels; 0 = none) */
+    void* dst[2];              /* static device buffers the captured step reads */
+    const float* loss_dev;     /* device scalar the captured step writes */
+    float* zero_ptrs[B200_STAGE_MAX_ZERO];   /* mode 1: fp32 regions cleared by the staging kernel */
+    int zero_counts[B200_STAGE_MAX_ZERO];
+    int nzero;
+} b200_runner_desc;
+int b200_runner_create(void** out, const b200_runner_desc* d);
+/* *prev_valid = 1 and *prev_loss = loss of the step before this one (0 on the first call) */
+int b200_runner_step(void* runner, const void* host_in0, const void* host_in1, float* prev_loss, int* prev_valid);
+int b200_runner_finish(void* runner, float* last_loss, int* valid);
+int b200_runner_destroy(void* runner);
+
 #ifdef __cplusplus
 }
 #endif
