@@ -212,6 +212,26 @@ class BatchLoader:
                 nxt += 1
 
 
+    # -- host batches for the native end-to-end runner ------------------------
+    def host_batches(self, slots: int = 4) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
+        """Yields each batch as pinned host tensors (views of a small ring) for
+        ``HostStepper.step``, which does the H2D itself.  A slot is reused `slots` batches
+        later; the stepper returns from step i+1 only after step i has finished, so with
+        slots >= 3 the asynchronous H2D out of a slot has always drained by then."""
+        if not self._cuda or self._resident:
+            raise RuntimeError("host_batches needs a CUDA target device and a host-resident data set")
+        d = self.dataset
+        ring = [(torch.empty(self.batch_size, *d.data.shape[1:], dtype=d.data.dtype).pin_memory(),
+                 torch.empty(self.batch_size, *d.labels.shape[1:], dtype=d.labels.dtype).pin_memory())
+                for _ in range(max(3, slots))]
+        for i, idx in enumerate(torch.split(self.sampler.indices(), self.batch_size)):
+            hx, hy = ring[i % len(ring)]
+            n = idx.numel()
+            torch.index_select(d.data, 0, idx, out=hx[:n])
+            torch.index_select(d.labels, 0, idx, out=hy[:n])
+            yield hx[:n], hy[:n]
+
+
 def create_data_loader(
     dataset: SyntheticDataset,
     batch_size: int,

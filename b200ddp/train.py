@@ -63,12 +63,48 @@ def build_datasets(args, device):
             SyntheticImages(max(1, args.num_samples // 10), seed=seed, device=dev))
 
 
+def _use_host_stepper(engine, loader) -> bool:
+    """The native end-to-end runner applies when batches come from host memory to a CUDA engine
+    running on the b200 backend (MLP step program or whole-step graph)."""
+    return (getattr(engine, "is_cuda", False) and hasattr(loader, "host_batches")
+            and not getattr(loader, "_resident", True)
+            and (engine.program is not None or getattr(engine, "_graph_ok", False))
+            and os.environ.get("B200DDP_NO_HOST_STEPPER") is None)
+
+
 def train_epoch(engine, loader, device, epoch: int, rank: int, log_interval: int = 10,
                 fault=None, global_step: int = 0) -> float:
     engine.train()
+    n = len(loader)
+    if _use_host_stepper(engine, loader):
+        # ref train.py:132-148 with the per-batch `.to(device)` x2 and `loss.item()` issued by
+        # one native call per step; a batch's loss arrives while the next batch is running
+        stepper = getattr(engine, "_train_stepper", None)
+        if stepper is None:
+            stepper = engine._train_stepper = engine.host_stepper()
+        total, num_batches = 0.0, 0
+
+        def account(idx: int, value: float) -> None:
+            nonlocal total
+            total += value
+            if idx % log_interval == 0 and rank == 0:
+                logger.info(f"Epoch {epoch}, Batch {idx}/{n}, Loss: {value:.4f}")
+
+        for batch_idx, (hx, hy) in enumerate(loader.host_batches()):
+            if fault is not None and fault == (rank, global_step + batch_idx):
+                logger.error(f"injected fault at step {global_step + batch_idx}")
+                os._exit(17)
+            with nvtx_range("train_step"):
+                prev = stepper.step(hx, hy)
+            if prev is not None:
+                account(batch_idx - 1, prev)
+            num_batches += 1
+        last = stepper.finish()
+        if last is not None:
+            account(num_batches - 1, last)
+        return total / max(1, num_batches)
     total = torch.zeros((), dtype=torch.float32, device=device)
     num_batches = 0
-    n = len(loader)
     for batch_idx, (data, target) in enumerate(loader):
         if fault is not None and fault == (rank, global_step + batch_idx):
             logger.error(f"injected fault at step {global_step + batch_idx}")
