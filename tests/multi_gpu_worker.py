@@ -100,8 +100,8 @@ def check_fused_optimizer(rank, world, dev, compute_dtype, two_shot, kind):
     # in-switch bf16 reduction rounds more than one fp32 accumulation would (hardware property,
     # same class of error as an NCCL bf16 all-reduce): the moments get a looser bound
     # (the SGD momentum buffer holds raw gradient sums, so it sees the full in-switch rounding)
-    assert torch.allclose(eng.optimizer.exp_avg, ref.optimizer.exp_avg, rtol=3e-2 if nvls_bf16 else rtol,
-                          atol=3e-2 if nvls_bf16 else atol)
+    assert torch.allclose(eng.optimizer.exp_avg, ref.optimizer.exp_avg, rtol=5e-2 if nvls_bf16 else rtol,
+                          atol=5e-2 if nvls_bf16 else atol)
     if eng.shadow is not None:
         assert torch.equal(eng.shadow, eng.master.to(torch.bfloat16))
     got = [torch.empty_like(eng.master) for _ in range(world)]
