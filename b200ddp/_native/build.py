@@ -21,6 +21,9 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 CSRC = os.path.join(ROOT, "csrc")
 OBJ = os.path.join(ROOT, "build", "obj")
 LIB = os.path.join(HERE, "libb200ddp.so")
+ORACLE_SRC = os.path.join(ROOT, "oracle", "oracle.cpp")
+ORACLE_LIB = os.path.join(HERE, "liboracle.so")
+CXX = os.environ.get("CXX", "g++")
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
@@ -68,9 +71,23 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+def build_oracle(force: bool = False) -> str:
+    """Host-only numerics oracle (oracle/oracle.cpp): plain g++, no CUDA.  -ffp-contract=off keeps
+    the optimizer math shared with the kernels (csrc/optim_math.h) bit-exact."""
+    deps = [ORACLE_SRC, os.path.join(CSRC, "optim_math.h"), os.path.join(ROOT, "include", "b200ddp.h")]
+    if not force and os.path.exists(ORACLE_LIB) and os.path.getmtime(ORACLE_LIB) >= max(os.path.getmtime(d) for d in deps):
+        return ORACLE_LIB
+    cmd = [CXX, "-O2", "-std=c++17", "-ffp-contract=off", "-shared", "-fPIC", "-Wall", "-o", ORACLE_LIB, ORACLE_SRC]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"oracle build failed:\n{r.stdout}\n{r.stderr}")
+    return ORACLE_LIB
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
     a = ap.parse_args()
     print(build(a.force, a.verbose))
+    print(build_oracle(a.force))

@@ -55,6 +55,52 @@ def test_optimizer_kernel_matches_torch_ops(B, kind, kw, gdtype):
         assert torch.equal(got.shadow, got.master.to(torch.bfloat16))
 
 
+@pytest.mark.parametrize("kind,kw", [("adam", {"weight_decay": 0.1}), ("adamw", {"weight_decay": 0.05}),
+                                     ("sgd", {"momentum": 0.9})])
+def test_optimizer_kernel_matches_host_oracle(B, kind, kw):
+    """Device and host compile the same update code (csrc/optim_math.h): optimizer_kernel on the
+    GPU against oracle/oracle.cpp on the CPU, three steps."""
+    from b200ddp._native import oracle as O
+    from b200ddp.models.simplenet import SimpleNet
+    from b200ddp.parallel.engine import DataParallel
+    torch.manual_seed(1)
+    dev = torch.device("cuda")
+    eng = DataParallel(SimpleNet().to(dev), optimizer=kind, lr=1e-2, backend="nccl",
+                       compute_dtype=torch.float32, use_program=False, **kw)
+    n = eng.layout.total
+    p, m = eng.master.cpu().clone(), torch.zeros(n)
+    v = torch.zeros(n) if kind != "sgd" else None
+    for step in range(1, 4):
+        g = torch.randn(n, device=dev)
+        eng.grad.copy_(g)
+        eng.optimizer.step_count = step
+        B.optimizer_step(eng.optimizer, 0, n, 0.5)
+        O.optimizer_step(kind, p, g.cpu(), m, v, step, lr=1e-2, weight_decay=kw.get("weight_decay", 0.0),
+                         momentum=kw.get("momentum", 0.0), grad_scale=0.5)
+    torch.cuda.synchronize()
+    assert torch.allclose(eng.master.cpu(), p, rtol=1e-6, atol=1e-7), (eng.master.cpu() - p).abs().max()
+    assert torch.allclose(eng.optimizer.exp_avg.cpu(), m, rtol=1e-6, atol=1e-7)
+
+
+def test_gemm_epilogues_match_host_oracle(B):
+    """tcgen05 GEMM with the GELU (+ saved pre-activation) and residual epilogues against the
+    plain-loop oracle on the host."""
+    from b200ddp._native import oracle as O
+    torch.manual_seed(2)
+    dev = torch.device("cuda")
+    M, N, K = 200, 136, 72
+    a, b = bf(torch.randn(M, K)), bf(torch.randn(N, K) * 0.2)
+    bias, r = torch.randn(N), bf(torch.randn(M, N))
+    want, zwant = O.gemm(a, b, bias=bias, epilogue=O.EPI_GELU, want_aux_out=True)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    z = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+    B.gemm(a.to(dev), b.to(dev), out, M=M, N=N, K=K, bias=bias.to(dev), epilogue=B.EPI_GELU, aux_out=z)
+    assert rel_err(z.cpu(), zwant) < 4e-3 and rel_err(out.cpu(), want) < 6e-3
+    want2, _ = O.gemm(a, b, bias=bias, aux=r)
+    B.gemm(a.to(dev), b.to(dev), out, M=M, N=N, K=K, bias=bias.to(dev), aux=r.to(dev))
+    assert rel_err(out.cpu(), want2) < 4e-3
+
+
 def test_optimizer_device_step_counter(B):
     from b200ddp.models.simplenet import SimpleNet
     from b200ddp.parallel.engine import DataParallel
