@@ -88,6 +88,7 @@ class FlatOptimizer:
         # Device-resident step counter: the captured CUDA graph cannot take a new
         # host scalar every replay, so bias correction is computed on device.
         self.step_dev = torch.zeros(2, dtype=torch.int32, device=master.device)
+        self.hp_version = 0   # bumped whenever hp changes (see set_hparams)
         self._group_template = _torch_param_group_template(kind, self.hp)
 
     # -- torch.optim surface ---------------------------------------------------
@@ -102,7 +103,16 @@ class FlatOptimizer:
         self.grad.zero_()
 
     def set_lr(self, lr: float) -> None:
-        self.hp["lr"] = float(lr)
+        self.set_hparams(lr=lr)
+
+    def set_hparams(self, **kw) -> None:
+        """Changes lr / betas / eps / weight_decay / momentum.  Captured steps bake these into
+        their kernel arguments; bumping ``hp_version`` makes the engine re-capture."""
+        for k, v in kw.items():
+            if k not in self.hp:
+                raise KeyError(f"unknown optimizer hyper-parameter {k!r}")
+            self.hp[k] = (float(v[0]), float(v[1])) if k == "betas" else float(v)
+        self.hp_version += 1
 
     # -- the update -------------------------------------------------------------
     def step(self, start: int = 0, end: Optional[int] = None, grad_scale: float = 1.0,
@@ -188,6 +198,7 @@ class FlatOptimizer:
         if "momentum" in g:
             self.hp["momentum"] = float(g["momentum"])
         self._group_template = {k: v for k, v in g.items()}
+        self.hp_version += 1
         steps = set()
         index_of = {pid: i for i, pid in enumerate(g["params"])}
         self.exp_avg.zero_()

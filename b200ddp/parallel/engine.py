@@ -27,6 +27,7 @@ from __future__ import annotations
 
 import hashlib
 import os
+import weakref
 from typing import Callable, Dict, List, Optional
 
 import torch
@@ -205,6 +206,8 @@ class DataParallel(nn.Module):
         self._graph_warmup: Dict[tuple, int] = {}
         self._capturing = False
         self._dev_step_synced = False
+        self._graphs_hp_version = self.optimizer.hp_version
+        self._steppers = weakref.WeakSet()
 
     # ------------------------------------------------------------------ allocation
     def _alloc(self, n: int, dtype: torch.dtype, peer: bool = False) -> torch.Tensor:
@@ -252,6 +255,7 @@ class DataParallel(nn.Module):
 
     def train_step(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         """One full optimisation step; returns the (detached, on-device) loss."""
+        self.check_graphs_current()
         if self.program is not None:
             loss = self.program.train_step(data, target)
             self.optimizer.step_count += 1
@@ -260,6 +264,20 @@ class DataParallel(nn.Module):
         if self._graph_ok:
             return self._graphed_step(data, target)
         return self._eager_step(data, target)
+
+    def check_graphs_current(self) -> None:
+        """Captured steps bake lr / betas / eps / weight decay into kernel arguments: when the
+        optimizer's hyper-parameters changed since capture, drop the graphs and re-capture."""
+        if self.optimizer.hp_version != self._graphs_hp_version:
+            self.invalidate_graphs()
+
+    def invalidate_graphs(self) -> None:
+        for st in list(self._steppers):
+            st.reset_runners()        # native runners hold raw graph handles
+        self._step_graphs.clear()
+        if self.program is not None:
+            self.program.invalidate()
+        self._graphs_hp_version = self.optimizer.hp_version
 
     def _eager_step(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         if not self._capturing:
@@ -334,7 +352,9 @@ class DataParallel(nn.Module):
         """End-to-end stepping from pinned host batches with one native call per step
         (``parallel/host_stepper.py``): H2D, staging, the captured step and the loss read-back."""
         from .host_stepper import HostStepper
-        return HostStepper(self, slots=slots)
+        st = HostStepper(self, slots=slots)
+        self._steppers.add(st)
+        return st
 
     def eval_step(self, data: torch.Tensor, target: torch.Tensor):
         """Validation batch: returns ``(mean loss, correct count)`` as device tensors."""

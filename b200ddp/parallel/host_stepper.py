@@ -36,6 +36,7 @@ class HostStepper:
         self._runners: Dict[tuple, int] = {}        # shape key -> native runner handle
         self._live: Optional[int] = None            # runner with a step in flight
         self._slow_pending: Optional[torch.Tensor] = None
+        self._carry: Optional[float] = None         # loss collected by reset_runners(), not yet returned
         self._prev = C.c_float(0.0)
         self._valid = C.c_int(0)
 
@@ -95,6 +96,7 @@ class HostStepper:
         if not (hx.is_pinned() and hy.is_pinned() and hx.is_contiguous() and hy.is_contiguous()):
             raise ValueError("HostStepper.step wants contiguous pinned host tensors")
         eng = self.engine
+        eng.check_graphs_current()       # hyper-parameters changed: graphs (and runners) are rebuilt
         runner = self._runner_for(hx, hy)
         if runner is None:   # engine still warming up for this shape: ordinary path
             prev = self._take_previous()
@@ -123,6 +125,9 @@ class HostStepper:
 
     def _take_previous(self) -> Optional[float]:
         """Loss of the last submitted step, whichever path it took; clears the pending state."""
+        if self._carry is not None:
+            prev, self._carry = self._carry, None
+            return prev
         if self._live is not None:
             nat.check(nat.lib().b200_runner_finish(self._live, C.byref(self._prev), C.byref(self._valid)),
                       "b200_runner_finish")
@@ -137,11 +142,19 @@ class HostStepper:
         """Waits for the last submitted step and returns its loss."""
         return self._take_previous()
 
-    def close(self) -> None:
-        self._take_previous()
+    def reset_runners(self) -> None:
+        """Destroys the native runners (the engine is about to drop the graphs they launch); the
+        loss of the step in flight is kept and returned by the next ``step`` / ``finish``."""
+        prev = self._take_previous()
+        if prev is not None:
+            self._carry = prev
         for h in self._runners.values():
             nat.lib().b200_runner_destroy(h)
         self._runners.clear()
+
+    def close(self) -> None:
+        self.reset_runners()
+        self._carry = None
 
     def __del__(self):
         try:

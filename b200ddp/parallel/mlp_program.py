@@ -86,6 +86,13 @@ class MLPProgram:
     def on_params_changed(self) -> None:
         pass  # weights are read in place from the arenas; nothing is cached
 
+    def invalidate(self) -> None:
+        """Drops the captured graphs (they bake the optimizer hyper-parameters into kernel
+        arguments); the next step re-captures."""
+        for b in self._bufs.values():
+            b.train_graph = None
+            b.eval_graph = None
+
     # ------------------------------------------------------------------ schedule
     def _forward(self, bufs: _Buffers, train: bool) -> None:
         step_dev = self.engine.optimizer.step_dev

@@ -561,6 +561,49 @@ def test_host_stepper_matches_train_step(model):
     stepper.close()
 
 
+@pytest.mark.parametrize("model", ["simplenet", "gpt2"])
+def test_hyperparameter_change_recaptures_the_step(model):
+    """Captured steps bake lr into kernel arguments; set_lr must make train_step and the native
+    runner re-capture (lr = 0 leaves the parameters bit-identical)."""
+    from b200ddp import SimpleNet
+    from b200ddp.parallel.engine import DataParallel
+    dev = torch.device("cuda")
+    torch.manual_seed(51)
+    if model == "simplenet":
+        net = SimpleNet(dropout=0.0).to(dev)
+        hx, hy = torch.randn(64, 784).pin_memory(), torch.randint(0, 10, (64,)).pin_memory()
+    else:
+        from b200ddp.models.gpt2 import GPT2, GPT2Config
+        cfg = GPT2Config(vocab_size=512, n_positions=64, n_embd=256, n_layer=2, n_head=4)
+        net = GPT2(cfg).to(dev)
+        hx = torch.randint(0, cfg.vocab_size, (8, 64)).pin_memory()
+        hy = torch.randint(0, cfg.vocab_size, (8, 64)).pin_memory()
+    eng = DataParallel(net, optimizer="adam", lr=1e-3, backend="b200", compute_dtype=torch.bfloat16)
+    x, y = hx.to(dev), hy.to(dev)
+    for _ in range(5):
+        eng.train_step(x, y)
+    torch.cuda.synchronize()
+    eng.optimizer.set_lr(0.0)
+    before = eng.master.clone()
+    eng.train_step(x, y)
+    torch.cuda.synchronize()
+    assert torch.equal(eng.master, before)
+    stepper = eng.host_stepper()
+    eng.optimizer.set_lr(1e-3)
+    for _ in range(4):
+        stepper.step(hx, hy)
+    assert stepper.finish() is not None
+    assert not torch.equal(eng.master, before) and len(stepper._runners) == 1
+    eng.optimizer.set_lr(0.0)
+    before = eng.master.clone()
+    for _ in range(4 if model == "gpt2" else 2):     # gpt2: two eager warm-up steps, capture, replay
+        stepper.step(hx, hy)
+    stepper.finish()
+    assert torch.equal(eng.master, before)
+    assert eng.optimizer.step_count == 5 + 1 + 4 + (4 if model == "gpt2" else 2)
+    stepper.close()
+
+
 def test_resnet50_engine_step():
     """Config 3 smoke: a ResNet-50 step through the engine (bf16, channels-last) trains."""
     from b200ddp.models.resnet50 import resnet50
