@@ -64,6 +64,10 @@ class RunnerDesc(C.Structure):
 
 
 def declare(L: C.CDLL) -> None:
+    L.b200_maxpool_fwd.argtypes = [C.c_void_p] * 3 + [C.c_int] * 8 + [C.c_void_p]
+    L.b200_maxpool_bwd.argtypes = [C.c_void_p] * 3 + [C.c_int] * 8 + [C.c_void_p]
+    L.b200_avgpool_fwd.argtypes = [C.c_void_p] * 2 + [C.c_int] * 3 + [C.c_void_p]
+    L.b200_avgpool_bwd.argtypes = [C.c_void_p] * 2 + [C.c_int] * 3 + [C.c_void_p]
     L.b200_runner_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(RunnerDesc)]
     L.b200_runner_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int)]
     L.b200_runner_finish.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int)]

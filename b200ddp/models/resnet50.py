@@ -14,7 +14,7 @@ wgrad) and the classifier on the tcgen05 GEMM: 1x1 convolutions feed the NHWC
 activation to the GEMM directly, 3x3/7x7 and strided ones go through the
 im2col/col2im gather kernels (``csrc/conv.cu``); BatchNorm is our kernel too, fused
 with ReLU and the residual add (``csrc/batchnorm.cu``: 2 passes forward, 2 backward).
-Max/avg pooling run through torch on the same channels-last tensors (zero-copy views).
+Max and global average pooling are NHWC gather kernels too (csrc/pool.cu); torch's on the CPU.
 """
 from __future__ import annotations
 
@@ -91,15 +91,15 @@ class ResNet50(nn.Module):
         return nn.Sequential(*layers)
 
     def forward(self, x):
+        from ..ops import functional as Fn
         w = self.conv1.weight
         if x.dtype != w.dtype:
             x = x.to(w.dtype)
         if x.is_cuda:
             x = x.contiguous(memory_format=torch.channels_last)
-        x = self.maxpool(self.bn1(self.conv1(x), relu=True))
+        x = Fn.max_pool2d(self.bn1(self.conv1(x), relu=True), 3, 2, 1)
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
-        x = torch.flatten(F.adaptive_avg_pool2d(x, 1), 1)
-        from ..ops import functional as Fn
+        x = Fn.global_avg_pool(x)
         return Fn.linear(x, self.fc.weight, self.fc.bias)
 
 

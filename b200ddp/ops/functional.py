@@ -741,3 +741,77 @@ def batch_norm_act(x, weight, bias, running_mean, running_var, training: bool, m
     if residual is not None:
         y = y + residual
     return F.relu(y) if relu else y
+
+
+# ------------------------------------------------------------------ pooling (channels-last bf16)
+class _MaxPool2d(torch.autograd.Function):
+    """Max pooling on NHWC storage (csrc/pool.cu): the forward keeps one byte per output element
+    (the winning tap), the backward is a gather over the windows that contain each input pixel."""
+
+    @staticmethod
+    def forward(ctx, x, k, stride, pad):
+        L = nat.lib()
+        xh = x.permute(0, 2, 3, 1)
+        if not xh.is_contiguous():
+            xh = xh.contiguous()
+        N, H, W_, Cc = xh.shape
+        P = (H + 2 * pad - k) // stride + 1
+        Q = (W_ + 2 * pad - k) // stride + 1
+        y = torch.empty(N, P, Q, Cc, dtype=torch.bfloat16, device=x.device)
+        idx = torch.empty(N, P, Q, Cc, dtype=torch.uint8, device=x.device)
+        nat.check(L.b200_maxpool_fwd(xh.data_ptr(), y.data_ptr(), idx.data_ptr(), N, H, W_, Cc, k, k, stride, pad,
+                                     nat.stream_ptr(x.device)), "b200_maxpool_fwd")
+        ctx.save_for_backward(idx)
+        ctx.geom = (N, H, W_, Cc, k, stride, pad)
+        return y.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = nat.lib()
+        (idx,) = ctx.saved_tensors
+        N, H, W_, Cc, k, stride, pad = ctx.geom
+        dyh = dy.permute(0, 2, 3, 1)
+        if not dyh.is_contiguous():
+            dyh = dyh.contiguous()
+        dx = torch.empty(N, H, W_, Cc, dtype=torch.bfloat16, device=dy.device)
+        nat.check(L.b200_maxpool_bwd(dyh.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W_, Cc, k, k, stride, pad,
+                                     nat.stream_ptr(dy.device)), "b200_maxpool_bwd")
+        return dx.permute(0, 3, 1, 2), None, None, None
+
+
+def max_pool2d(x, kernel_size: int, stride: int, padding: int = 0):
+    if native_ok(x) and x.dim() == 4 and x.shape[1] % 8 == 0 and 2 * padding <= kernel_size and kernel_size <= 15:
+        return _MaxPool2d.apply(x, kernel_size, stride, padding)
+    return F.max_pool2d(x, kernel_size, stride, padding)
+
+
+class _GlobalAvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        L = nat.lib()
+        xh = x.permute(0, 2, 3, 1)
+        if not xh.is_contiguous():
+            xh = xh.contiguous()
+        N, H, W_, Cc = xh.shape
+        y = torch.empty(N, Cc, dtype=torch.bfloat16, device=x.device)
+        nat.check(L.b200_avgpool_fwd(xh.data_ptr(), y.data_ptr(), N, H * W_, Cc, nat.stream_ptr(x.device)),
+                  "b200_avgpool_fwd")
+        ctx.geom = (N, H, W_, Cc)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = nat.lib()
+        N, H, W_, Cc = ctx.geom
+        dy2 = dy.contiguous()
+        dx = torch.empty(N, H, W_, Cc, dtype=torch.bfloat16, device=dy.device)
+        nat.check(L.b200_avgpool_bwd(dy2.data_ptr(), dx.data_ptr(), N, H * W_, Cc, nat.stream_ptr(dy.device)),
+                  "b200_avgpool_bwd")
+        return dx.permute(0, 3, 1, 2)
+
+
+def global_avg_pool(x):
+    """[N, C, H, W] -> [N, C] (mean over the spatial positions)."""
+    if native_ok(x) and x.dim() == 4 and x.shape[1] % 8 == 0:
+        return _GlobalAvgPool.apply(x)
+    return torch.flatten(F.adaptive_avg_pool2d(x, 1), 1)

@@ -307,6 +307,18 @@ int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200_opt_hparam
 int b200_allreduce(const b200_comm* c, int algo, int64_t start, int64_t n, int is_bf16, void* out,
                    float scale, void* stream);
 
+/* ---------------------------------------------------------------- pooling (NHWC bf16, C % 8 == 0)
+ * BASELINE.json config 3 (ResNet-50); no counterpart in the reference (its baseline runs ATen's
+ * pooling kernels).  idx: one byte per output element, the winning tap r*S + s (first maximum in
+ * scan order, as torch); the backward is a deterministic gather. */
+int b200_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, int R, int S, int stride,
+                     int pad, void* stream);
+int b200_maxpool_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int R, int S,
+                     int stride, int pad, void* stream);
+/* global average pool: x [N, HW, C] -> y [N, C]; backward dx = dy / HW */
+int b200_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
+int b200_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
+
 /* ---------------------------------------------------------------- host step runner
  * One call per training step on the end-to-end path (ref train.py:133,141: `.to(device)` x2, the
  * step, `loss.item()`): H2D of the pinned host inputs on a copy stream, staging, cudaGraphLaunch of

@@ -604,6 +604,38 @@ def test_hyperparameter_change_recaptures_the_step(model):
     stepper.close()
 
 
+@pytest.mark.parametrize("N,C,H,k,stride,pad", [(4, 64, 112, 3, 2, 1), (2, 16, 9, 3, 2, 1), (3, 8, 10, 2, 2, 0),
+                                                (2, 24, 7, 3, 1, 1)])
+def test_maxpool_matches_torch(N, C, H, k, stride, pad):
+    from b200ddp.ops import functional as Fn
+    torch.manual_seed(61)
+    dev = torch.device("cuda")
+    x = bf(torch.randn(N, C, H, H, device=dev)).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    y = Fn.max_pool2d(x, k, stride, pad)
+    xr = x.detach().float().requires_grad_(True)
+    yr = F.max_pool2d(xr, k, stride, pad)
+    assert y.shape == yr.shape and torch.equal(y.float(), yr)
+    dy = bf(torch.randn_like(yr))
+    y.backward(dy)
+    yr.backward(dy.float())
+    assert rel_err(x.grad, xr.grad) < 4e-3
+
+
+def test_global_avgpool_matches_torch():
+    from b200ddp.ops import functional as Fn
+    torch.manual_seed(62)
+    dev = torch.device("cuda")
+    x = bf(torch.randn(8, 2048, 7, 7, device=dev)).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    y = Fn.global_avg_pool(x)
+    xr = x.detach().float().requires_grad_(True)
+    yr = torch.flatten(F.adaptive_avg_pool2d(xr, 1), 1)
+    assert rel_err(y, yr) < 4e-3
+    dy = bf(torch.randn_like(yr))
+    y.backward(dy)
+    yr.backward(dy.float())
+    assert rel_err(x.grad, xr.grad) < 4e-3
+
+
 def test_resnet50_engine_step():
     """Config 3 smoke: a ResNet-50 step through the engine (bf16, channels-last) trains."""
     from b200ddp.models.resnet50 import resnet50
