@@ -83,6 +83,7 @@ def declare(L: C.CDLL) -> None:
     L.b200_cross_entropy.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_int64, C.c_int,
                                      C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
     L.b200_gemm.argtypes = [C.POINTER(GemmDesc), C.c_void_p]
+    L.b200_gemm_plan.argtypes = [C.POINTER(GemmDesc), C.c_int, C.POINTER(C.c_int)]
     L.b200_cast_f32_to_bf16.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     L.b200_cast_bf16_to_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     L.b200_stage_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
@@ -242,6 +243,33 @@ def cast_f32_to_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
     assert src.is_contiguous() and dst.is_contiguous() and src.numel() == dst.numel()
     check(lib().b200_cast_f32_to_bf16(src.data_ptr(), dst.data_ptr(), src.numel(),
                                       stream_ptr(src.device)), "b200_cast_f32_to_bf16")
+
+
+GEMM_KERNELS = ("general", "lean", "m256", "pair")
+
+
+def gemm_plan(M: int, N: int, K: int, *, sms: int = 148, d_fp32: bool = False, epilogue: int = EPI_NONE,
+              bias: bool = False, aux: bool = False, aux_out: bool = False, colsum: bool = False, split_k: int = 0,
+              tile_n: int = 0, tile_m: int = 0, cta_pair: int = 0, batch: int = 1, causal: int = 0, ldd=None,
+              b_mn_major: bool = False):
+    """(kernel family name, N tile) b200_gemm would pick — host logic only, works without a GPU."""
+    d = GemmDesc()
+    d.M, d.N, d.K = M, N, K
+    fake = 0x10000   # only alignment and null-ness of the pointers enter the decision
+    d.A = d.B = d.D = fake
+    d.lda = d.ldb = (K + 7) // 8 * 8
+    d.ldd = ldd if ldd is not None else N
+    d.d_fp32, d.epilogue, d.b_mn_major = int(d_fp32), epilogue, int(b_mn_major)
+    d.bias = fake if bias else None
+    d.aux, d.ldaux = (fake, d.ldd) if aux else (None, 0)
+    d.aux_out = fake if aux_out else None
+    d.colsum = fake if colsum else None
+    d.targets = fake if epilogue == EPI_SOFTMAX_CE else None
+    d.split_k, d.tile_n, d.tile_m, d.cta_pair, d.causal = split_k, tile_n, tile_m, cta_pair, causal
+    d.batch_inner = batch
+    out = (C.c_int * 2)()
+    check(lib().b200_gemm_plan(C.byref(d), sms, out), "b200_gemm_plan")
+    return GEMM_KERNELS[out[0]], out[1]
 
 
 def make_zero_list(tensors):

@@ -115,24 +115,33 @@ def _emit_param_grad(p: torch.Tensor, compute_into, signal: bool = True):
     return g
 
 
-def _wgrad_into(dy2: torch.Tensor, x2: torch.Tensor, dst: torch.Tensor) -> None:
-    # dW[n_out, n_in] = dy^T @ x : both operands read MN-major, nothing is transposed
-    n_out, n_in = dst.shape
-    K = x2.shape[0]
+def wgrad_plan(n_out: int, n_in: int, K: int, bf16_dst: bool, row_stride_ok: bool = True) -> str:
+    """How dW[n_out, n_in] = dy^T @ x (reduction over K rows) fills 148 SMs when the output has few
+    tiles; constants fitted to B200 measurements (tools/gpt2_gemm_shapes.py):
+
+    direct   the two-SM kernel with 256x128 pair tiles writing bf16 straight into the arena:
+             ~0.28 us per k-block, one wave per 74 pair tiles
+    split    K slices across the idle SMs, fp32 partials combined with vector atomics into a
+             zeroed temp, then one cast: ~0.45 us per k-block spread over all SMs plus ~30 us of
+             memset / atomic / cast overhead
+    plain    whatever b200_gemm picks (enough tiles, or a short reduction)
+    """
     kb = (K + 63) // 64
     tiles = ((n_out + 127) // 128) * ((n_in + 255) // 256)
-    # Two ways to fill 148 SMs when the output has few tiles and the reduction is long
-    # (fitted to B200 measurements, tools/gpt2_gemm_shapes.py):
-    #   direct   the two-SM kernel with 256x128 pair tiles writing bf16 straight into the arena:
-    #            ~0.28 us per k-block, one wave per 74 pair tiles
-    #   split-K  K slices across the idle SMs, fp32 partials combined with vector atomics into
-    #            a zeroed temp, then one cast: ~0.45 us per k-block spread over all SMs plus
-    #            ~30 us of memset / atomic / cast overhead
-    direct_ok = dst.dtype == torch.bfloat16 and n_out > 128 and n_in > 64 and dst.stride(0) % 8 == 0
+    direct_ok = bf16_dst and n_out > 128 and n_in > 64 and row_stride_ok
     pair_tiles = ((n_out + 255) // 256) * ((n_in + 127) // 128)
     direct_us = -(-pair_tiles // 74) * kb * 0.28 + 3 if direct_ok else float("inf")
     split_us = tiles * kb * 0.45 / 148 + 30 if (tiles < 100 and K >= 2048) else float("inf")
     if split_us < direct_us:
+        return "split"
+    return "direct" if direct_ok else "plain"
+
+
+def _wgrad_into(dy2: torch.Tensor, x2: torch.Tensor, dst: torch.Tensor) -> None:
+    # dW[n_out, n_in] = dy^T @ x : both operands read MN-major, nothing is transposed
+    n_out, n_in = dst.shape
+    K = x2.shape[0]
+    if wgrad_plan(n_out, n_in, K, dst.dtype == torch.bfloat16, dst.stride(0) % 8 == 0) == "split":
         tmp = torch.zeros(n_out, n_in, dtype=torch.float32, device=dst.device)
         _B().gemm(dy2, x2, tmp, M=n_out, N=n_in, K=K, a_mn_major=True, b_mn_major=True, split_k=1)
         dst.copy_(tmp)

@@ -1280,25 +1280,14 @@ static int ensure_init() {
     return rc;
 }
 
-extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
+// Which kernel family and N tile a problem runs on.  Pure host logic (no CUDA calls), also exported
+// as b200_gemm_plan so the policy is unit-tested on boxes without a GPU.
+enum { GEMM_K_GENERAL = 0, GEMM_K_FAST = 1, GEMM_K_M256 = 2, GEMM_K_PAIR = 3 };
+struct GemmPlan {
+    int kernel, bn;
+};
+static int select_kernel(const b200_gemm_desc* d, int sms, GemmPlan* out) {
     using namespace b200;
-    if (int rc = ensure_init()) return rc;
-    // cuTensorMapEncodeTiled is a driver call and needs the primary context current on THIS
-    // thread (CUDA_ERROR_INVALID_CONTEXT otherwise).  Autograd runs backward on worker threads
-    // whose first CUDA work may be this GEMM, so bind the context once per thread.
-    static thread_local bool ctx_bound = false;
-    if (!ctx_bound) {
-        int dev = 0;
-        B200_CUDA_OK(cudaGetDevice(&dev));
-        B200_CUDA_OK(cudaSetDevice(dev));  // binds the primary context; legal during stream capture
-        ctx_bound = true;
-    }
-    B200_REQUIRE(d && d->A && d->B && d->D, "gemm: null pointer");
-    B200_REQUIRE(d->M > 0 && d->N > 0 && d->K > 0, "gemm: bad shape %dx%dx%d", d->M, d->N, d->K);
-    B200_REQUIRE((d->lda % 8) == 0 && (d->ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements (got %lld, %lld)",
-                 (long long)d->lda, (long long)d->ldb);
-    B200_REQUIRE(((uintptr_t)d->A % 16) == 0 && ((uintptr_t)d->B % 16) == 0, "gemm: A/B must be 16-byte aligned");
-    const int sms = sm_count();
     const int nbi = d->batch_inner > 1 ? d->batch_inner : 1, nbo = d->batch_outer > 1 ? d->batch_outer : 1;
     if (nbi * nbo > 1)
         B200_REQUIRE(d->epilogue == B200_EPI_NONE && !d->aux && !d->bias && !d->colsum && !d->split_k,
@@ -1349,7 +1338,37 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
         B200_REQUIRE(d->N <= bn && bn <= 32, "gemm: fused cross-entropy needs N <= 32 (got %d)", d->N);
         B200_REQUIRE(d->targets != nullptr, "gemm: fused cross-entropy needs targets");
     }
-    const bool fast = fast_cfg && bn >= 64;
+    out->bn = bn;
+    out->kernel = pair ? GEMM_K_PAIR : (m256 ? GEMM_K_M256 : ((fast_cfg && bn >= 64) ? GEMM_K_FAST : GEMM_K_GENERAL));
+    return 0;
+
+}
+
+extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
+    using namespace b200;
+    if (int rc = ensure_init()) return rc;
+    // cuTensorMapEncodeTiled is a driver call and needs the primary context current on THIS
+    // thread (CUDA_ERROR_INVALID_CONTEXT otherwise).  Autograd runs backward on worker threads
+    // whose first CUDA work may be this GEMM, so bind the context once per thread.
+    static thread_local bool ctx_bound = false;
+    if (!ctx_bound) {
+        int dev = 0;
+        B200_CUDA_OK(cudaGetDevice(&dev));
+        B200_CUDA_OK(cudaSetDevice(dev));  // binds the primary context; legal during stream capture
+        ctx_bound = true;
+    }
+    B200_REQUIRE(d && d->A && d->B && d->D, "gemm: null pointer");
+    B200_REQUIRE(d->M > 0 && d->N > 0 && d->K > 0, "gemm: bad shape %dx%dx%d", d->M, d->N, d->K);
+    B200_REQUIRE((d->lda % 8) == 0 && (d->ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements (got %lld, %lld)",
+                 (long long)d->lda, (long long)d->ldb);
+    B200_REQUIRE(((uintptr_t)d->A % 16) == 0 && ((uintptr_t)d->B % 16) == 0, "gemm: A/B must be 16-byte aligned");
+    const int sms = sm_count();
+    const int nbi = d->batch_inner > 1 ? d->batch_inner : 1, nbo = d->batch_outer > 1 ? d->batch_outer : 1;
+    GemmPlan plan;
+    if (int rc = select_kernel(d, sms, &plan)) return rc;
+    const int bn = plan.bn;
+    const bool pair = plan.kernel == GEMM_K_PAIR, m256 = plan.kernel == GEMM_K_M256;
+    const bool fast = plan.kernel == GEMM_K_FAST;
 
     CUtensorMap ma, mb;
     int rc;
@@ -1423,6 +1442,18 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
         case 128: return launch<128, false>(ma, mb, p, ctas, s);
         default: return launch<256, false>(ma, mb, p, ctas, s);
     }
+}
+
+// out[0] = kernel family (0 general, 1 lean epilogue, 2 256x256 dual accumulator, 3 SM pair),
+// out[1] = N tile.  `sms` <= 0 means the current device (148 without one).
+extern "C" int b200_gemm_plan(const b200_gemm_desc* d, int sms, int* out) {
+    B200_REQUIRE(d && out, "gemm_plan: null pointer");
+    B200_REQUIRE(d->M > 0 && d->N > 0 && d->K > 0, "gemm: bad shape %dx%dx%d", d->M, d->N, d->K);
+    GemmPlan plan;
+    if (int rc = select_kernel(d, sms > 0 ? sms : b200::sm_count(), &plan)) return rc;
+    out[0] = plan.kernel;
+    out[1] = plan.bn;
+    return 0;
 }
 
 // Load every kernel variant and set its shared-memory opt-in up front, so the first

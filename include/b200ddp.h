@@ -168,6 +168,10 @@ typedef struct {
 } b200_gemm_desc;
 
 int b200_gemm(const b200_gemm_desc* d, void* stream);
+/* The kernel b200_gemm would run for `d`, without launching anything (pure host logic; usable
+ * without a GPU): out[0] = family (0 general 128 x N, 1 lean-epilogue 128 x N, 2 256 x 256 dual
+ * accumulator, 3 SM pair / cta_group::2), out[1] = N tile.  sms <= 0: the current device (148). */
+int b200_gemm_plan(const b200_gemm_desc* d, int sms, int* out2);
 
 /* ---------------------------------------------------------------- elementwise
  * ref: train.py:133 `.to(device)` + the implicit fp32 input; the bf16 compute
