@@ -8,18 +8,25 @@
 // GELU fwd/bwd, residual add, bias-gradient column sums and, for the classifier
 // layer, the whole softmax cross-entropy forward+backward.
 //
-// Structure (persistent, one CTA per SM, 320 threads):
+// Three kernel families share the pieces below (selection: select_kernel / b200_gemm_plan):
+//   gemm_kernel<BN, FAST>   128 x BN tiles, one SM.  General form (4 epilogue warps, every
+//                           epilogue) and lean form (8 epilogue warps, light epilogues, bf16 out).
+//   gemm_kernel_2sm<BN>     256 x BN tiles per SM pair: tcgen05 cta_group::2 on a 2-CTA cluster.
+//   gemm_kernel_m256        256 x 256 tiles, one SM, two accumulators sharing each B tile.
+//
+// Structure of each (persistent, one CTA per SM, 192 or 320 threads):
 //   warp 0      TMA producer: cp.async.bulk.tensor tiles of A and B into a
 //               STAGES-deep ring of 128B-swizzled shared memory, mbarrier tx-count.
-//   warp 1      MMA issuer: one thread issues tcgen05.mma (M=128, N=BN, K=16) from
-//               shared-memory descriptors into a TMEM accumulator; tcgen05.commit
-//               frees ring slots and publishes finished accumulators.
-//   warps 2..9  epilogue: tcgen05.ld the accumulator (one row per thread, two warps per
-//               TMEM lane quarter splitting the columns), apply the fused epilogue,
-//               store.  TMEM holds two accumulators so the epilogue of tile i overlaps
-//               the MMAs of tile i+1.  The tile's bias slice is staged in shared memory
-//               and the aux operand is fetched one chunk ahead: with one warp per
-//               scheduler every exposed load latency is paid in full (ncu: the bias
+//   warp 1      MMA issuer: tcgen05.mma (M=128, N=BN, K=16) from shared-memory descriptors
+//               into a TMEM accumulator; tcgen05.commit frees ring slots and publishes
+//               finished accumulators.  Both warps walk their loops whole, one elected lane
+//               issues (keeps every operand in uniform registers; see gemm_kernel).
+//   warps 2..   epilogue: tcgen05.ld the accumulator (one row per thread; the lean kernels put
+//               two warps on each TMEM lane quarter, splitting the columns), apply the fused
+//               epilogue, store.  TMEM holds two accumulators so the epilogue of tile i
+//               overlaps the MMAs of tile i+1.  The tile's bias slice is staged in shared
+//               memory and the aux operand is fetched one chunk ahead: with one or two warps
+//               per scheduler every exposed load latency is paid in full (ncu: the bias
 //               loads were 38 % of all stall samples at K = 768).
 //
 // Operand layouts: K-major (reduction index contiguous: activations [M,K],
