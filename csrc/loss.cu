@@ -12,6 +12,7 @@
 // them in block order, so the mean loss is deterministic.
 #include "common.cuh"
 
+#include <cstdlib>
 #include <mutex>
 
 void b200_count_launch(int n);
@@ -128,6 +129,123 @@ __global__ void __launch_bounds__(256) ce_kernel(const void* __restrict__ logits
     }
 }
 
+// Large vocabularies in bf16 (the LM head: 50257 classes, rows 16-byte aligned): one block per
+// row with 16-byte loads and stores.  The scalar kernel above moves 2 bytes per thread per access
+// (64 contiguous bytes per warp instruction) and reached 0.45 of the HBM roofline on the 823 MB of
+// GPT-2 logits; here a warp instruction covers 512 contiguous bytes.  Two passes over the row (row
+// statistics, then the gradient written in place); the grid is capped so that the rows in flight
+// (100 KB each) stay in L2 between the passes.
+__device__ __forceinline__ void ce_unpack8(const uint4& raw, float (&f)[8]) {
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[q]));
+        f[2 * q] = t.x;
+        f[2 * q + 1] = t.y;
+    }
+}
+__device__ __forceinline__ void ce_online(RowStat& st, float x, int c) {
+    if (x > st.mx) {
+        st.sum = st.sum * __expf(st.mx - x) + 1.f;
+        st.mx = x;
+        st.arg = c;
+    } else {
+        st.sum += __expf(x - st.mx);
+    }
+}
+
+__global__ void __launch_bounds__(256) ce_row_vec_kernel(const __nv_bfloat16* logits, int64_t ld,
+                                                         const int64_t* __restrict__ targets, int64_t rows, int classes,
+                                                         __nv_bfloat16* dlogits, float grad_scale,
+                                                         float* __restrict__ loss_out, unsigned int* __restrict__ ticket,
+                                                         float2* __restrict__ partials) {
+    __shared__ RowStat s_stat[8];
+    const int lane = threadIdx.x, warp = threadIdx.x >> 5;
+    const int nvec = classes >> 3, tail0 = nvec << 3;
+    float acc_loss = 0.f, acc_ok = 0.f;
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+        const __nv_bfloat16* src = logits + row * ld;
+        const uint4* src4 = reinterpret_cast<const uint4*>(src);
+        const int tgt = (int)targets[row];
+        // read before anything of this row is overwritten (dlogits may alias logits)
+        const float x_tgt = lane == 0 ? __bfloat162float(src[tgt]) : 0.f;
+        RowStat st{-INFINITY, 0.f, 0x7fffffff};
+        for (int v = lane; v < nvec; v += 256) {
+            float x[8];
+            ce_unpack8(src4[v], x);
+            float m8 = x[0];
+            int a8 = 0;
+#pragma unroll
+            for (int k = 1; k < 8; ++k)
+                if (x[k] > m8) { m8 = x[k]; a8 = k; }
+            if (m8 > st.mx) {
+                st.sum *= __expf(st.mx - m8);
+                st.mx = m8;
+                st.arg = v * 8 + a8;
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) st.sum += __expf(x[k] - st.mx);
+        }
+        if (tail0 + lane < classes) ce_online(st, __bfloat162float(src[tail0 + lane]), tail0 + lane);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            RowStat other;
+            other.mx = __shfl_xor_sync(0xffffffffu, st.mx, o);
+            other.sum = __shfl_xor_sync(0xffffffffu, st.sum, o);
+            other.arg = __shfl_xor_sync(0xffffffffu, st.arg, o);
+            st = merge(st, other);
+        }
+        if ((threadIdx.x & 31) == 0) s_stat[warp] = st;
+        __syncthreads();
+        st = s_stat[0];
+#pragma unroll
+        for (int w = 1; w < 8; ++w) st = merge(st, s_stat[w]);
+        __syncthreads();
+        if (lane == 0) {
+            acc_loss += st.mx + __logf(st.sum) - x_tgt;
+            acc_ok += (st.arg == tgt) ? 1.f : 0.f;
+        }
+        if (dlogits) {
+            const float inv = 1.f / st.sum;
+            uint4* dst4 = reinterpret_cast<uint4*>(dlogits + row * ld);
+            for (int v = lane; v < nvec; v += 256) {
+                float x[8];
+                ce_unpack8(src4[v], x);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    float g = __expf(x[k] - st.mx) * inv;
+                    if (v * 8 + k == tgt) g -= 1.f;
+                    x[k] = g * grad_scale;
+                }
+                dst4[v] = make_uint4(pack_bf16(x[0], x[1]), pack_bf16(x[2], x[3]), pack_bf16(x[4], x[5]),
+                                     pack_bf16(x[6], x[7]));
+            }
+            if (tail0 + lane < classes) {
+                const int c = tail0 + lane;
+                float g = __expf(__bfloat162float(src[c]) - st.mx) * inv;
+                if (c == tgt) g -= 1.f;
+                dlogits[row * ld + c] = __float2bfloat16_rn(g * grad_scale);
+            }
+        }
+    }
+    if (threadIdx.x == 0) {   // block partial -> scratch; the last block reduces in block order
+        partials[blockIdx.x] = make_float2(acc_loss, acc_ok);
+        __threadfence();
+        const unsigned int t = atomicAdd(ticket, 1u);
+        if (t == gridDim.x - 1) {
+            __threadfence();
+            float L = 0.f, K = 0.f;
+            for (unsigned int b = 0; b < gridDim.x; ++b) {
+                L += __ldcg(&partials[b].x);
+                K += __ldcg(&partials[b].y);
+            }
+            loss_out[0] = L / (float)rows;
+            loss_out[1] = K;
+            *ticket = 0u;
+        }
+    }
+}
+
 }  // namespace b200
 
 extern "C" int64_t b200_ce_scratch_bytes(int64_t rows) {
@@ -146,6 +264,16 @@ extern "C" int b200_cross_entropy(const void* logits, int logits_bf16, int64_t l
     float2* partials = reinterpret_cast<float2*>(reinterpret_cast<char*>(scratch) + 16);
     cudaStream_t s = (cudaStream_t)stream;
     const bool big = classes > 2048;
+    static const bool vec_off = getenv("B200DDP_NO_VEC_CE") != nullptr;
+    if (big && logits_bf16 && !vec_off && (ld % 8) == 0 && ((uintptr_t)logits % 16) == 0 &&
+        (!dlogits || ((uintptr_t)dlogits % 16) == 0)) {
+        int64_t vb = rows < 148 * 4 ? rows : 148 * 4;   // rows in flight stay L2-resident between the passes
+        b200::ce_row_vec_kernel<<<(int)vb, 256, 0, s>>>((const __nv_bfloat16*)logits, ld, targets, rows, classes,
+                                                        (__nv_bfloat16*)dlogits, grad_scale, loss_out, ticket, partials);
+        b200_count_launch(1);
+        B200_CUDA_OK(cudaGetLastError());
+        return 0;
+    }
     const int teams = big ? 1 : 8;
     int64_t blocks = (rows + teams - 1) / teams;
     if (blocks > b200::CE_MAX_BLOCKS) blocks = b200::CE_MAX_BLOCKS;

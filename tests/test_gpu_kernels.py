@@ -142,6 +142,32 @@ def test_cross_entropy_kernel(B, rows, classes, dtype):
     assert rel_err(dl, ref_in.grad) < tol
 
 
+@pytest.mark.parametrize("rows,inplace", [(37, False), (700, True)])
+def test_cross_entropy_vectorised_rows(B, rows, inplace):
+    """LM-head shape: 50257 classes in rows padded to 50264 (16-byte aligned) take the 16-byte
+    vector kernel; in place, as the LM head uses it, and with more rows than blocks."""
+    torch.manual_seed(3)
+    dev = torch.device("cuda")
+    classes, ld = 50257, 50264
+    buf = (torch.randn(rows, ld, device=dev) * 3).to(torch.bfloat16)
+    logits = buf[:, :classes]
+    pad_before = buf[:, classes:].clone()
+    tgt = torch.randint(0, classes, (rows,), device=dev)
+    tgt[0], tgt[1] = classes - 1, 0           # tail element and first element as targets
+    ref_in = logits.float().requires_grad_(True)
+    ref_loss = F.cross_entropy(ref_in, tgt)
+    ref_loss.backward()
+    want_ok = (logits.float().argmax(1) == tgt).sum().item()
+    dl = logits if inplace else torch.empty(rows, ld, dtype=torch.bfloat16, device=dev)[:, :classes]
+    out = torch.zeros(2, device=dev)
+    B.cross_entropy(logits, tgt, dl, 1.0 / rows, out)
+    torch.cuda.synchronize()
+    assert abs(out[0].item() - ref_loss.item()) < 2e-4 * max(1.0, abs(ref_loss.item()))
+    assert out[1].item() == want_ok
+    assert rel_err(dl, ref_in.grad) < 1e-2
+    assert torch.equal(buf[:, classes:], pad_before)     # padding columns untouched
+
+
 # ------------------------------------------------------------------ GEMM
 def _ref_gemm(a, b, a_mn, b_mn):
     A = a.float().t() if a_mn else a.float()
