@@ -221,7 +221,12 @@ class BatchLoader:
         if not self._cuda or self._resident:
             raise RuntimeError("host_batches needs a CUDA target device and a host-resident data set")
         d = self.dataset
-        ring = [(torch.empty(self.batch_size, *d.data.shape[1:], dtype=d.data.dtype).pin_memory(),
+        # pinned once and kept with the loader: the runner's asynchronous H2D of the last batches
+        # of an epoch may still be reading a slot when the generator is exhausted
+        ring = getattr(self, "_host_ring", None)
+        if ring is None or len(ring) < max(3, slots):
+            ring = self._host_ring = [
+                (torch.empty(self.batch_size, *d.data.shape[1:], dtype=d.data.dtype).pin_memory(),
                  torch.empty(self.batch_size, *d.labels.shape[1:], dtype=d.labels.dtype).pin_memory())
                 for _ in range(max(3, slots))]
         for i, idx in enumerate(torch.split(self.sampler.indices(), self.batch_size)):

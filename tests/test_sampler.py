@@ -56,3 +56,38 @@ def test_loader_handles_sequence_labels():
     shapes = [(x.shape, y.shape) for x, y in loader]
     assert shapes[0] == (torch.Size([8, 16]), torch.Size([8, 16])) and shapes[-1][0][0] == 4
     assert torch.equal(ds.data[:, 1:], ds.labels[:, :-1])  # labels are the inputs shifted by one
+
+
+def test_host_batches_cover_the_shard_in_order_and_reuse_the_ring():
+    """BatchLoader.host_batches (pinned batches for the native runner), with pinning stubbed out."""
+    from unittest import mock
+
+    import pytest
+
+    from b200ddp.data import BatchLoader, ShardSampler, SyntheticDataset
+    ds = SyntheticDataset(200, seed=1)
+    sm = ShardSampler(len(ds), 2, 0)
+    ld = BatchLoader(ds, 64, sm)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        next(ld.host_batches())
+    ld._cuda, ld._resident = True, False          # pretend the target is a GPU
+    with mock.patch.object(torch.Tensor, "pin_memory", lambda self: self):
+        got = [(x.clone(), y.clone()) for x, y in ld.host_batches()]
+        ring = ld._host_ring
+        assert len(ring) >= 3
+        list(ld.host_batches())
+        assert ld._host_ring is ring             # pinned once, reused across epochs
+    idx = sm.indices()
+    assert [x.shape[0] for x, _ in got] == [64, 36]
+    assert torch.equal(torch.cat([x for x, _ in got]), ds.data[idx])
+    assert torch.equal(torch.cat([y for _, y in got]), ds.labels[idx])
+
+
+def test_cpu_engine_does_not_take_the_host_stepper_path():
+    from b200ddp import DataParallel, SimpleNet
+    from b200ddp.data import BatchLoader, ShardSampler, SyntheticDataset
+    from b200ddp.train import _use_host_stepper
+    ds = SyntheticDataset(64, seed=2)
+    ld = BatchLoader(ds, 32, ShardSampler(len(ds), 1, 0))
+    eng = DataParallel(SimpleNet(), backend="gloo", init_sync=False)
+    assert not _use_host_stepper(eng, ld)
