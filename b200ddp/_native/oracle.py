@@ -26,7 +26,8 @@ def lib() -> C.CDLL:
         _lib = C.CDLL(build_oracle())
         for name in ("oracle_optimizer_step", "oracle_allreduce_sum", "oracle_gemm_bf16", "oracle_cross_entropy",
                      "oracle_layernorm_fwd", "oracle_layernorm_bwd", "oracle_batchnorm_fwd", "oracle_im2col",
-                     "oracle_col2im", "oracle_causal_attention"):
+                     "oracle_col2im", "oracle_causal_attention", "oracle_maxpool_fwd", "oracle_maxpool_bwd",
+                     "oracle_avgpool_fwd"):
             getattr(_lib, name).restype = None
     return _lib
 
@@ -113,6 +114,29 @@ def col2im(dcol, shape_nhwc, R, S, stride, pad):
     dx = torch.empty(N, H, W, Cc, dtype=torch.bfloat16)
     lib().oracle_col2im(_p(dcol), _p(dx), N, H, W, Cc, R, S, stride, pad)
     return dx
+
+
+def maxpool_fwd(x_nhwc, k, stride, pad):
+    N, H, W, Cc = x_nhwc.shape
+    P, Q = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+    y = torch.empty(N, P, Q, Cc, dtype=torch.bfloat16)
+    idx = torch.empty(N, P, Q, Cc, dtype=torch.uint8)
+    lib().oracle_maxpool_fwd(_p(x_nhwc), _p(y), _p(idx), N, H, W, Cc, k, k, stride, pad)
+    return y, idx
+
+
+def maxpool_bwd(dy_nhwc, idx, shape_nhwc, k, stride, pad):
+    N, H, W, Cc = shape_nhwc
+    dx = torch.empty(N, H, W, Cc, dtype=torch.bfloat16)
+    lib().oracle_maxpool_bwd(_p(dy_nhwc), _p(idx), _p(dx), N, H, W, Cc, k, k, stride, pad)
+    return dx
+
+
+def avgpool_fwd(x_nhwc):
+    N, H, W, Cc = x_nhwc.shape
+    y = torch.empty(N, Cc, dtype=torch.bfloat16)
+    lib().oracle_avgpool_fwd(_p(x_nhwc), _p(y), N, H * W, Cc)
+    return y
 
 
 def causal_attention(qkv: torch.Tensor, n_head: int):

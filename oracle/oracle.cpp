@@ -223,6 +223,56 @@ void oracle_col2im(const uint16_t* dcol, uint16_t* dx, int N, int H, int W, int 
     for (size_t i = 0; i < acc.size(); ++i) dx[i] = f32_to_bf16(acc[i]);
 }
 
+// ---- max pooling (csrc/pool.cu), NHWC bf16: first maximum in scan order wins; the backward routes
+// each output gradient to its winner, summing in fp32.
+void oracle_maxpool_fwd(const uint16_t* x, uint16_t* y, uint8_t* idx, int N, int H, int W, int C, int R, int S,
+                        int stride, int pad) {
+    const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
+    for (int n = 0; n < N; ++n)
+        for (int p = 0; p < P; ++p)
+            for (int q = 0; q < Q; ++q)
+                for (int c = 0; c < C; ++c) {
+                    float best = -INFINITY;
+                    int arg = 0;
+                    bool first = true;
+                    for (int r = 0; r < R; ++r)
+                        for (int s = 0; s < S; ++s) {
+                            const int h = p * stride - pad + r, w = q * stride - pad + s;
+                            if (h < 0 || h >= H || w < 0 || w >= W) continue;
+                            const float v = bf16_to_f32(x[(((int64_t)n * H + h) * W + w) * C + c]);
+                            if (first || v > best) { best = v; arg = r * S + s; }
+                            first = false;
+                        }
+                    const int64_t o = (((int64_t)n * P + p) * Q + q) * C + c;
+                    y[o] = f32_to_bf16(best);
+                    idx[o] = (uint8_t)arg;
+                }
+}
+void oracle_maxpool_bwd(const uint16_t* dy, const uint8_t* idx, uint16_t* dx, int N, int H, int W, int C, int R, int S,
+                        int stride, int pad) {
+    const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
+    std::vector<float> acc((size_t)N * H * W * C, 0.f);
+    for (int n = 0; n < N; ++n)
+        for (int p = 0; p < P; ++p)
+            for (int q = 0; q < Q; ++q)
+                for (int c = 0; c < C; ++c) {
+                    const int64_t o = (((int64_t)n * P + p) * Q + q) * C + c;
+                    const int r = idx[o] / S, s = idx[o] % S;
+                    const int h = p * stride - pad + r, w = q * stride - pad + s;
+                    acc[(((int64_t)n * H + h) * W + w) * C + c] += bf16_to_f32(dy[o]);
+                }
+    for (size_t i = 0; i < acc.size(); ++i) dx[i] = f32_to_bf16(acc[i]);
+}
+// global average pool: x [N, HW, C] -> y [N, C]
+void oracle_avgpool_fwd(const uint16_t* x, uint16_t* y, int N, int HW, int C) {
+    for (int n = 0; n < N; ++n)
+        for (int c = 0; c < C; ++c) {
+            float acc = 0.f;
+            for (int px = 0; px < HW; ++px) acc += bf16_to_f32(x[((int64_t)n * HW + px) * C + c]);
+            y[(int64_t)n * C + c] = f32_to_bf16(acc * (1.f / (float)HW));
+        }
+}
+
 // ---- causal attention forward (csrc/flash_attention.cu): qkv [B, T, 3, H, D] bf16 -> out [B, T, H*D]
 // bf16 and the natural-log LSE of the scaled scores [B, H, T]; probabilities rounded to bf16
 // before the PV product, as on the device.

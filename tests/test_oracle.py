@@ -177,6 +177,22 @@ def test_im2col_matches_unfold_and_col2im_is_its_adjoint(k, stride, pad, H):
     assert rel_err(dx, want_dx) < 4e-3
 
 
+@pytest.mark.parametrize("k,stride,pad,H", [(3, 2, 1, 9), (2, 2, 0, 8), (3, 1, 1, 5)])
+def test_pooling(k, stride, pad, H):
+    torch.manual_seed(10)
+    N, Cc = 2, 8
+    x = bf(torch.randn(N, H, H, Cc))
+    y, idx = O.maxpool_fwd(x, k, stride, pad)
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    yr = F.max_pool2d(xr, k, stride, pad)
+    assert torch.equal(y.float(), yr.detach().permute(0, 2, 3, 1))
+    dy = bf(torch.randn(*y.shape))
+    yr.backward(dy.float().permute(0, 3, 1, 2))
+    dx = O.maxpool_bwd(dy, idx, x.shape, k, stride, pad)
+    assert rel_err(dx, xr.grad.permute(0, 2, 3, 1)) < 4e-3
+    assert rel_err(O.avgpool_fwd(x), x.float().mean((1, 2))) < 4e-3
+
+
 def test_causal_attention_matches_sdpa():
     torch.manual_seed(8)
     B, T, H, D = 2, 40, 3, 16
