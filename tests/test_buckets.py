@@ -59,3 +59,31 @@ def test_layout_is_bucket_ordered_and_aligned():
     assert seen == lay.total
     # reverse registration order: the last layer's bias is first in the arena
     assert lay.slots[len(named) - 1].offset == 0
+
+
+@settings(max_examples=200, deadline=None)
+@given(world=st.sampled_from([2, 4, 8]), vec=st.sampled_from([4, 8]), start_v=st.integers(0, 4096),
+       numel_v=st.integers(1, 200_000))
+def test_two_shot_shard_ranges_partition_the_bucket(world, vec, start_v, numel_v):
+    """Host mirror of comm.cu's shard ownership (who reduces, updates and later re-broadcasts which
+    slice; `consolidate_state` relies on it): contiguous, ordered, disjoint, covering, and every
+    shard but the last a multiple of 16 vectors."""
+    from types import SimpleNamespace
+
+    from b200ddp.parallel.symm import SymmetricArena
+    arena = object.__new__(SymmetricArena)
+    arena.world, arena.vec_elems = world, vec
+    b = SimpleNamespace(start=start_v * vec, numel=numel_v * vec)
+    ranges = arena.shard_ranges(b)
+    assert len(ranges) == world
+    assert ranges[0][0] == b.start
+    cursor = b.start
+    for lo, hi in ranges:
+        assert lo <= hi
+        if hi > lo:
+            assert lo == cursor
+            cursor = hi
+    assert cursor == b.start + b.numel
+    sizes = [hi - lo for lo, hi in ranges if hi > lo]
+    for sz in sizes[:-1]:
+        assert sz % (16 * vec) == 0
