@@ -12,9 +12,16 @@ Behaviour kept from torchrun as the reference uses it:
   ``ROLE_RANK``, ``MASTER_ADDR``, ``MASTER_PORT``, ``TORCHELASTIC_*``,
   ``TORCH_NCCL_ASYNC_ERROR_HANDLING=1`` and ``OMP_NUM_THREADS=1`` when more than
   one worker shares the node and the variable is unset;
-* workers are polled every 0.1 s; ``max_restarts`` is 0: the first worker that
-  exits non-zero fails the node, its siblings are terminated (SIGTERM, then
-  SIGKILL after a grace period) and the launcher exits with that worker's code.
+* workers are polled every 0.1 s; with the default ``--max-restarts 0`` (what the
+  reference runs with) the first worker that exits non-zero fails the node, its
+  siblings are terminated (SIGTERM, then SIGKILL after a grace period) and the
+  launcher exits with that worker's code;
+* ``--max-restarts N`` restarts the whole worker group up to N times, like torchrun's
+  agent: ``TORCHELASTIC_RESTART_COUNT`` counts the attempt, the rendezvous port moves
+  by one per attempt (the old TCPStore may linger in TIME_WAIT), and
+  ``--restart-args`` appends arguments to the training script on restarts — e.g.
+  ``--restart-args="--resume ck/latest_model.pt --resume-next-epoch"``.  Single node
+  only: a static rendezvous cannot re-admit nodes that restart at different times.
 
 What is different: there is no agent-side store or elastic machinery.  Global
 rank 0 hosts the env:// TCPStore itself, and the supervisor is ~100 lines with
@@ -59,7 +66,7 @@ def master_from_hostname(hostname: str, discovery_service: str) -> str:
 
 def worker_env(base: Dict[str, str], *, rank: int, local_rank: int, world_size: int,
                nproc: int, node_rank: int, master_addr: str, master_port: int,
-               run_id: str) -> Dict[str, str]:
+               run_id: str, restart_count: int = 0, max_restarts: int = 0) -> Dict[str, str]:
     env = dict(base)
     env.update({
         "RANK": str(rank),
@@ -72,8 +79,8 @@ def worker_env(base: Dict[str, str], *, rank: int, local_rank: int, world_size: 
         "GROUP_WORLD_SIZE": str(world_size // nproc),
         "MASTER_ADDR": master_addr,
         "MASTER_PORT": str(master_port),
-        "TORCHELASTIC_RESTART_COUNT": "0",
-        "TORCHELASTIC_MAX_RESTARTS": "0",
+        "TORCHELASTIC_RESTART_COUNT": str(restart_count),
+        "TORCHELASTIC_MAX_RESTARTS": str(max_restarts),
         "TORCHELASTIC_RUN_ID": run_id,
         "TORCH_NCCL_ASYNC_ERROR_HANDLING": "1",
     })
@@ -149,6 +156,10 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--master-addr", "--master_addr", type=str, default="127.0.0.1")
     p.add_argument("--master-port", "--master_port", type=int, default=29500)
     p.add_argument("--run-id", type=str, default=None)
+    p.add_argument("--max-restarts", "--max_restarts", type=int, default=0,
+                   help="restarts of the whole worker group after a failure (single node)")
+    p.add_argument("--restart-args", type=str, default="",
+                   help="extra training-script arguments on restarts, e.g. '--resume ck/latest_model.pt'")
     p.add_argument("--no-python", action="store_true", help="run the script as an executable")
     p.add_argument("-m", "--module", action="store_true", help="treat the script as a module name")
     p.add_argument("--dry-run", action="store_true", help="print the worker commands and exit")
@@ -185,25 +196,40 @@ def main(argv: Optional[List[str]] = None) -> int:
     else:
         cmd = [sys.executable, "-u", args.training_script]
     cmd += args.training_script_args
-    envs = [
-        worker_env(dict(os.environ), rank=args.node_rank * nproc + lr, local_rank=lr,
-                   world_size=world, nproc=nproc, node_rank=args.node_rank,
-                   master_addr=args.master_addr, master_port=args.master_port, run_id=run_id)
-        for lr in range(nproc)
-    ]
+    if args.max_restarts > 0 and args.nnodes > 1:
+        log("ERROR: --max-restarts needs --nnodes 1 (static rendezvous cannot re-admit restarted nodes)")
+        return 1
+
+    def envs_for(attempt: int) -> List[Dict[str, str]]:
+        return [
+            worker_env(dict(os.environ), rank=args.node_rank * nproc + lr, local_rank=lr,
+                       world_size=world, nproc=nproc, node_rank=args.node_rank,
+                       master_addr=args.master_addr, master_port=args.master_port + attempt, run_id=run_id,
+                       restart_count=attempt, max_restarts=args.max_restarts)
+            for lr in range(nproc)
+        ]
+
     if args.dry_run:
-        for e in envs:
+        for e in envs_for(0):
             print(f"RANK={e['RANK']} LOCAL_RANK={e['LOCAL_RANK']} WORLD_SIZE={e['WORLD_SIZE']} "
                   f"MASTER_ADDR={e['MASTER_ADDR']} MASTER_PORT={e['MASTER_PORT']} "
                   + " ".join(shlex.quote(c) for c in cmd))
         return 0
     log(f"node {args.node_rank}/{args.nnodes}: starting {nproc} worker(s), world size {world}, "
         f"rendezvous {args.master_addr}:{args.master_port} on {socket.gethostname()}")
-    sup = Supervisor(cmd, envs)
-    signal.signal(signal.SIGTERM, sup.on_signal)
-    signal.signal(signal.SIGINT, sup.on_signal)
-    sup.start()
-    return sup.wait()
+    rc = 0
+    for attempt in range(args.max_restarts + 1):
+        attempt_cmd = cmd + (shlex.split(args.restart_args) if attempt > 0 else [])
+        sup = Supervisor(attempt_cmd, envs_for(attempt))
+        signal.signal(signal.SIGTERM, sup.on_signal)
+        signal.signal(signal.SIGINT, sup.on_signal)
+        sup.start()
+        rc = sup.wait()
+        if rc == 0 or sup._stopping or attempt == args.max_restarts:
+            return rc
+        log(f"worker group failed with code {rc}; restart {attempt + 1}/{args.max_restarts}"
+            + (f" with {args.restart_args!r}" if args.restart_args else ""))
+    return rc
 
 
 if __name__ == "__main__":

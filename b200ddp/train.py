@@ -199,7 +199,8 @@ def main(argv=None) -> int:
     dist.barrier()
 
     fault = None
-    if args.inject_fault:
+    if args.inject_fault and int(os.environ.get("TORCHELASTIC_RESTART_COUNT", "0")) == 0:
+        # first attempt only: a restarted worker group (launcher --max-restarts) must get through
         r, s = args.inject_fault.split(":")
         fault = (int(r), int(s))
 

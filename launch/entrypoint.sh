@@ -12,6 +12,8 @@
 # Additions:
 #   LAUNCHER=torchrun     use torchrun instead of b200ddp.launch
 #   single-box mode: REPLICAS=1 needs no discovery service; master is 127.0.0.1
+#   MAX_RESTARTS=N        (b200ddp.launch, single node) restart the worker group up to N times;
+#   RESTART_ARGS="..."    trainer arguments added on restarts, e.g. "--resume ck/latest_model.pt"
 set -euo pipefail
 
 say() { printf '[%s] %s\n' "$(date -u +%H:%M:%S)" "$*"; }
@@ -49,6 +51,10 @@ if [ "${launcher}" = "torchrun" ]; then
 fi
 
 say "Starting b200ddp.launch (static rendezvous, ${nproc} worker(s) on this node)"
+if [ -n "${MAX_RESTARTS:-}" ]; then
+    topology+=(--max-restarts="${MAX_RESTARTS}")
+    [ -z "${RESTART_ARGS:-}" ] || topology+=(--restart-args="${RESTART_ARGS}")
+fi
 if [ -n "${script}" ]; then
     # shellcheck disable=SC2086
     exec python -m b200ddp.launch "${topology[@]}" "${script}" ${SCRIPT_ARGS:-}

@@ -107,3 +107,36 @@ def test_supervisor_success(tmp_path):
                        cwd=ROOT, capture_output=True, text=True, timeout=60)
     assert r.returncode == 0
     assert "hello 0 2" in r.stdout and "hello 1 2" in r.stdout
+
+
+def test_max_restarts_relaunches_the_group_with_restart_args(tmp_path):
+    """torchrun-agent semantics the reference would get with --max-restarts: the whole group is
+    torn down and started again, TORCHELASTIC_RESTART_COUNT counts the attempt, and the extra
+    arguments (a --resume in practice) reach the script only on restarts."""
+    script = tmp_path / "flaky.py"
+    script.write_text(textwrap.dedent("""
+        import os, sys, time
+        attempt = int(os.environ["TORCHELASTIC_RESTART_COUNT"])
+        print("attempt %d rank %s port %s argv %s max %s" % (attempt, os.environ["RANK"], os.environ["MASTER_PORT"],
+              sys.argv[1:], os.environ["TORCHELASTIC_MAX_RESTARTS"]), flush=True)
+        if attempt == 0 and os.environ["RANK"] == "1":
+            time.sleep(0.2); sys.exit(9)
+        if attempt == 0:
+            time.sleep(60)
+    """))
+    base = [sys.executable, "-m", "b200ddp.launch", "--nproc-per-node=2", "--master-port=29871"]
+    r = subprocess.run(base + ["--max-restarts=1", "--restart-args=--resume ck.pt", str(script), "--epochs", "3"],
+                       cwd=ROOT, capture_output=True, text=True, timeout=90)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "restart 1/1" in r.stdout
+    assert "attempt 0 rank 0 port 29871 argv ['--epochs', '3'] max 1" in r.stdout
+    assert "attempt 1 rank 1 port 29872 argv ['--epochs', '3', '--resume', 'ck.pt'] max 1" in r.stdout
+    # default (the reference's configuration): no restart, the failure code comes back
+    r0 = subprocess.run(base + [str(script)], cwd=ROOT, capture_output=True, text=True, timeout=90)
+    assert r0.returncode == 9 and "attempt 1" not in r0.stdout
+
+
+def test_max_restarts_is_single_node_only(tmp_path):
+    r = subprocess.run([sys.executable, "-m", "b200ddp.launch", "--nnodes=2", "--max-restarts=1", "x.py"],
+                       cwd=ROOT, capture_output=True, text=True, timeout=60)
+    assert r.returncode == 1 and "--max-restarts needs --nnodes 1" in r.stdout

@@ -105,6 +105,24 @@ def test_fault_injection_tears_down_job(tmp_path):
     assert "exited with code 17" in r.stdout
 
 
+def test_fault_then_restart_resumes_from_the_last_checkpoint(tmp_path):
+    """SURVEY §4 fault tier: a rank dies mid-run, the launcher tears the group down, restarts it
+    with --resume on the latest checkpoint and the job completes."""
+    ck = tmp_path / "ck" / "latest_model.pt"
+    cmd = [sys.executable, "-m", "b200ddp.launch", "--nproc-per-node=2", f"--master-port={free_port()}",
+           "--max-restarts=1", f"--restart-args=--resume {ck} --resume-next-epoch",
+           "-m", "b200ddp.train", "--backend", "gloo", "--checkpoint-dir", str(tmp_path / "ck"),
+           "--epochs", "3", "--num-samples", "2000", "--inject-fault", "1:20"]     # 16 steps per epoch
+    env = {**os.environ, "CUDA_VISIBLE_DEVICES": ""}
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=300, env=env)
+    out = r.stdout + r.stderr
+    assert r.returncode == 0, out[-3000:]
+    assert "injected fault at step 20" in out and "restart 1/1" in out
+    assert re.search(r"Checkpoint loaded from .*latest_model\.pt", out)
+    assert out.count("Epoch 0 completed") == 1          # not re-run after the restart
+    assert "Epoch 2 completed" in out and ck.exists()
+
+
 def test_buffers_follow_rank0_every_training_forward(tmp_path):
     """module buffers (BatchNorm statistics) are broadcast from rank 0 in the
     constructor and before every training forward, through one flat buffer arena."""
