@@ -216,6 +216,9 @@ def main(argv=None) -> int:
         train_loss = train_epoch(engine, train_loader, device, epoch, rank,
                                  log_interval=args.log_interval, fault=fault,
                                  global_step=global_step)
+        if device.type == "cuda":
+            torch.cuda.synchronize(device)
+        train_time = time.time() - epoch_start
         global_step += len(train_loader)
 
         val_loss, val_accuracy = validate(engine, val_loader, device)
@@ -235,6 +238,9 @@ def main(argv=None) -> int:
         if rank == 0:
             logger.info(f"Epoch {epoch} completed in {epoch_time:.2f}s")
             logger.info(f"  Train Loss: {avg_train_loss:.4f}")
+            # extra line (not in the reference): end-to-end training throughput of this epoch
+            logger.info(f"  Train throughput: {len(train_sampler) * world_size / max(train_time, 1e-9):,.0f} "
+                        f"samples/s over {world_size} rank(s)")
             logger.info(
                 f"  Val Loss: {avg_val_loss:.4f}, Val Accuracy: {avg_val_accuracy:.2f}%"
             )

@@ -43,6 +43,7 @@ def test_log_lines_match_reference_format(run2):
         r"Epoch 1, Batch 10/16, Loss: \d+\.\d{4}",
         r"Epoch 1 completed in \d+\.\d\ds",
         r"  Train Loss: \d+\.\d{4}",
+        r"  Train throughput: [\d,]+ samples/s over 2 rank\(s\)",
         r"  Val Loss: \d+\.\d{4}, Val Accuracy: \d+\.\d\d%",
         r"Checkpoint saved to .*latest_model\.pt",
         r"Training completed in \d+\.\d\ds",
