@@ -88,3 +88,34 @@ def test_weight_gradient_plan():
     assert wgrad_plan(4096, 4096, 1024, False) == "plain"
     # SimpleNet-sized: short reduction, nothing to split
     assert wgrad_plan(256, 784, 64, True) == "direct" and wgrad_plan(256, 784, 64, False) == "plain"
+
+
+from hypothesis import given, settings, strategies as st
+
+
+@settings(max_examples=300, deadline=None)
+@given(M=st.integers(1, 20000), N=st.integers(1, 60000), K=st.integers(1, 20000),
+       d_fp32=st.booleans(), bias=st.booleans(), aux=st.booleans(), colsum=st.booleans(),
+       epilogue=st.sampled_from([B.EPI_NONE, B.EPI_RELU_DROPOUT, B.EPI_GELU]), split=st.booleans(),
+       b_mn=st.booleans(), sms=st.sampled_from([148, 132, 64]))
+def test_auto_selection_always_lands_on_a_kernel_that_supports_the_problem(M, N, K, d_fp32, bias, aux, colsum,
+                                                                           epilogue, split, b_mn, sms):
+    """Whatever the problem, the automatic choice is a supported tile, and the large-tile kernels
+    are only chosen for what they implement (bf16 output, light epilogue, no column sums, no
+    split-K, more than one M tile)."""
+    if split:   # split-K contract: plain fp32 output
+        d_fp32, bias, aux, colsum, epilogue = True, False, False, False, B.EPI_NONE
+    if b_mn and N < 64:
+        N = 64      # MN-major B needs a 64-wide tile
+    ldd = (N + 7) // 8 * 8
+    kernel, bn = B.gemm_plan(M, N, K, sms=sms, d_fp32=d_fp32, bias=bias, aux=aux and N % 8 == 0, colsum=colsum,
+                             epilogue=epilogue, split_k=int(split), b_mn_major=b_mn, ldd=ldd)
+    assert bn in (16, 32, 64, 128, 256)
+    if b_mn:
+        assert bn >= 64
+    if kernel in ("pair", "m256", "lean"):
+        assert not d_fp32 and not colsum and not split and epilogue != B.EPI_RELU_DROPOUT and bn >= 64
+    if kernel == "pair":
+        assert M > 128 and N > 64 and bn in (128, 256)
+    if kernel == "m256":
+        assert bn == 256 and M >= 512 and K >= 4096
