@@ -63,7 +63,39 @@ class RunnerDesc(C.Structure):
     ]
 
 
+class MlpDesc(C.Structure):
+    from .bindings_comm import Comm as _Comm
+    _fields_ = [
+        ("in_features", C.c_int), ("hidden", C.c_int), ("classes", C.c_int),
+        ("W1", C.c_void_p), ("W2", C.c_void_p), ("W3", C.c_void_p),
+        ("b1", C.c_void_p), ("b2", C.c_void_p), ("b3", C.c_void_p),
+        ("gW1", C.c_void_p), ("gb1", C.c_void_p), ("gW2", C.c_void_p), ("gb2", C.c_void_p),
+        ("gW3", C.c_void_p), ("gb3", C.c_void_p),
+        ("grad_parity_stride", C.c_int64),
+        ("scratch", C.c_void_p), ("loss_out", C.c_void_p), ("step_dev", C.c_void_p),
+        ("dropout_p1", C.c_float), ("dropout_p2", C.c_float), ("seed", C.c_uint64),
+        ("hp", OptHParams),
+        ("master", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+        ("shadow", C.c_void_p),
+        ("n_buckets", C.c_int),
+        ("bucket_start", C.c_int64 * 4), ("bucket_n", C.c_int64 * 4), ("bucket_algo", C.c_int * 4),
+        ("comm", C.POINTER(_Comm)), ("comm_copy", _Comm),
+    ]
+
+
 def declare(L: C.CDLL) -> None:
+    L.b200_mlp_scratch_bytes.restype = C.c_int64
+    L.b200_mlp_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(MlpDesc)]
+    L.b200_mlp_destroy.argtypes = [C.c_void_p]
+    L.b200_mlp_forward_backward.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    L.b200_mlp_train.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]
+    L.b200_mlp_host_init.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    L.b200_mlp_host_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_float),
+                                     C.POINTER(C.c_int), C.c_void_p]
+    L.b200_mlp_host_finish.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_void_p]
+    for name in ("b200_mlp_create", "b200_mlp_destroy", "b200_mlp_forward_backward", "b200_mlp_train",
+                 "b200_mlp_host_init", "b200_mlp_host_step", "b200_mlp_host_finish"):
+        getattr(L, name).restype = C.c_int
     L.b200_maxpool_fwd.argtypes = [C.c_void_p] * 3 + [C.c_int] * 8 + [C.c_void_p]
     L.b200_maxpool_bwd.argtypes = [C.c_void_p] * 3 + [C.c_int] * 8 + [C.c_void_p]
     L.b200_avgpool_fwd.argtypes = [C.c_void_p] * 2 + [C.c_int] * 3 + [C.c_void_p]

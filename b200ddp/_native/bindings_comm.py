@@ -12,7 +12,9 @@ class Comm(C.Structure):
                 ("grad", C.c_void_p * MAX_RANKS), ("push", C.c_void_p * MAX_RANKS),
                 ("flags", C.c_void_p * MAX_RANKS),
                 ("grad_mc", C.c_void_p), ("push_mc", C.c_void_p),
-                ("timeout_ms", C.c_int), ("max_blocks", C.c_int)]
+                ("timeout_ms", C.c_int), ("max_blocks", C.c_int),
+                ("master_peer", C.c_void_p * MAX_RANKS), ("f32_mask", C.c_void_p),
+                ("parity_stride", C.c_int64), ("no_exit_wait", C.c_int)]
 
 
 def declare(L: C.CDLL) -> None:

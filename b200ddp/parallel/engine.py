@@ -124,15 +124,36 @@ class DataParallel(nn.Module):
         if backend == "b200" and self.world_size > 1:
             from .symm import SymmetricArena
             self.symm = SymmetricArena(self.device, self.rank, self.world_size)
-        # fp32 compute: the two-shot kernel pushes updated fp32 parameters straight into
-        # every rank's master arena, so it is peer-mapped too.
-        self.master = self._alloc(total, torch.float32, peer=compute_dtype == torch.float32)
+        # The master arena is peer-mapped: with fp32 compute the sharded kernels push the updated
+        # fp32 parameters straight into every rank's master; with a bf16 shadow they push bf16 and,
+        # for the parameters forward reads in fp32 (biases, norm scales / shifts: `f32_mask`), the
+        # fp32 value as well — otherwise those would be current only on the shard owner.
+        self.master = self._alloc(total, torch.float32, peer=True)
         self.allow_two_shot = True
         self.shadow = None
         if compute_dtype != torch.float32:
             self.shadow = self._alloc(total, compute_dtype, peer=True)
-        # gradients are what peers read: they live in peer-mapped memory on b200
-        self.grad = self._alloc(total, self.wire_dtype, peer=True)
+        # Gradients are what peers read: they live in peer-mapped memory on b200.  The fused MLP
+        # step double-buffers them on step parity (two arenas back to back), which lets the
+        # one-shot all-reduce leave without an exit barrier (csrc/comm.cu).
+        self.grad_parity_stride = 0
+        if want_program and self.symm is not None:
+            both = self._alloc(2 * total, self.wire_dtype, peer=True)
+            self.grad = both[:total]
+            for attr in ("_b200_peers", "_b200_mc", "_b200_hdl"):
+                if hasattr(both, attr):
+                    setattr(self.grad, attr, getattr(both, attr))
+            self._grad_both = both
+            self.grad_parity_stride = total * both.element_size()
+        else:
+            self.grad = self._alloc(total, self.wire_dtype, peer=True)
+        self.f32_mask = None
+        if self.symm is not None and self.shadow is not None:
+            mask = torch.zeros((total + 7) // 8, dtype=torch.uint8)
+            for (name, p), slot in zip(params, self.layout.slots):
+                if p.dim() <= 1:
+                    mask[slot.offset // 8:(slot.offset + slot.numel + 7) // 8] = 1
+            self.f32_mask = mask.to(self.device)
         for (name, p), slot in zip(params, self.layout.slots):
             sl = slice(slot.offset, slot.offset + slot.numel)
             with torch.no_grad():
@@ -180,11 +201,12 @@ class DataParallel(nn.Module):
         for p, slot in zip(self._params, self.layout.slots):
             hook = self._make_hook(slot.bucket)
             p.register_post_accumulate_grad_hook(hook)
+            sl = slice(slot.offset, slot.offset + slot.numel)
+            p._b200_arena = self.grad[sl].view(slot.shape)
             if self.is_cuda:
                 # lets the native autograd ops write gradients straight into the arena
                 # (ops/functional.py) and signal the bucket themselves
-                sl = slice(slot.offset, slot.offset + slot.numel)
-                p._b200_grad = self.grad[sl].view(slot.shape)
+                p._b200_grad = p._b200_arena
                 p._b200_master = self.master[sl].view(slot.shape)
                 p._b200_ready = (lambda h=hook, q=p: h(q))
 
@@ -264,6 +286,28 @@ class DataParallel(nn.Module):
         if self._graph_ok:
             return self._graphed_step(data, target)
         return self._eager_step(data, target)
+
+    def train_steps(self, x_pool: torch.Tensor, y_pool: torch.Tensor, first: int, count: int) -> None:
+        """`count` optimisation steps over an on-device pool of batches (x_pool [P, B, ...],
+        y_pool [P, B]); step i uses batch (first + i) % P.  With the fused MLP session this is ONE
+        native call that issues two launches per step (no Python, no graph replay in the loop);
+        other models loop over ``train_step``.  The loss of the last step is ``last_loss()``."""
+        self.check_graphs_current()
+        if self.program is not None and count > 0:
+            loss = self.program.train_many(x_pool, y_pool, first, count)
+            if loss is not None:
+                self._last_loss = loss
+            self.optimizer.step_count += count
+            self._step_index += count
+            return
+        P = x_pool.shape[0]
+        for i in range(count):
+            self._last_loss = self.train_step(x_pool[(first + i) % P], y_pool[(first + i) % P])
+
+    def last_loss(self) -> torch.Tensor:
+        if self.program is not None and self.program.fused is not None and self.program._last_fused:
+            return self.program.fused.loss[0].clone()
+        return self._last_loss
 
     def check_graphs_current(self) -> None:
         """Captured steps bake lr / betas / eps / weight decay into kernel arguments: when the
@@ -382,6 +426,12 @@ class DataParallel(nn.Module):
         def hook(param):
             if not self._in_backward:
                 return
+            g = param.grad
+            if g is not None and g.data_ptr() != param._b200_arena.data_ptr():
+                # autograd produced a fresh tensor (the wire dtype differs from the parameter's):
+                # cast it into the arena slice the reduction reads
+                param._b200_arena.copy_(g)
+                param.grad = None
             self._pending[bucket_index] -= 1
             if self._pending[bucket_index] == 0 and self.overlap:
                 self._launch_ready()

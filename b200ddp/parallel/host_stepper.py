@@ -97,6 +97,8 @@ class HostStepper:
             raise ValueError("HostStepper.step wants contiguous pinned host tensors")
         eng = self.engine
         eng.check_graphs_current()       # hyper-parameters changed: graphs (and runners) are rebuilt
+        if eng.program is not None and eng.program._fused_ok(hx, hy):
+            return self._fused_step(hx, hy)
         runner = self._runner_for(hx, hy)
         if runner is None:   # engine still warming up for this shape: ordinary path
             prev = self._take_previous()
@@ -123,11 +125,42 @@ class HostStepper:
             return float(self._prev.value)
         return prev
 
+    FUSED = -1   # `_live` value while the fused MLP session has a step in flight
+
+    def _fused_step(self, hx: torch.Tensor, hy: torch.Tensor) -> Optional[float]:
+        """Fused two-launch MLP step (csrc/mlp_fused.cu): the session copies the pinned batch into
+        its device ring on a copy stream, launches the step kernel (which stores the loss into
+        mapped pinned memory itself) and the update, and hands back the previous step's loss."""
+        eng = self.engine
+        fs = eng.program.fused
+        L = nat.lib()
+        if not fs.host_ready:
+            nat.check(L.b200_mlp_host_init(fs.handle, eng.program.fused.MAX_BATCH, self.slots), "b200_mlp_host_init")
+            fs.host_ready = True
+        prev = None if self._live == self.FUSED else self._take_previous()
+        same = self._live == self.FUSED
+        eng.program._leave_gemm_path()
+        x = hx.reshape(hx.shape[0], -1)
+        nat.check(L.b200_mlp_host_step(fs.handle, x.data_ptr(), hy.data_ptr(), x.shape[0], C.byref(self._prev),
+                                       C.byref(self._valid), nat.stream_ptr(self.device)), "b200_mlp_host_step")
+        self._live = self.FUSED
+        eng.optimizer.step_count += 1
+        eng._step_index += 1
+        if same and self._valid.value:
+            return float(self._prev.value)
+        return prev
+
     def _take_previous(self) -> Optional[float]:
         """Loss of the last submitted step, whichever path it took; clears the pending state."""
         if self._carry is not None:
             prev, self._carry = self._carry, None
             return prev
+        if self._live == self.FUSED:
+            fs = self.engine.program.fused
+            nat.check(nat.lib().b200_mlp_host_finish(fs.handle, C.byref(self._prev), C.byref(self._valid),
+                                                     nat.stream_ptr(self.device)), "b200_mlp_host_finish")
+            self._live = None
+            return float(self._prev.value) if self._valid.value else None
         if self._live is not None:
             nat.check(nat.lib().b200_runner_finish(self._live, C.byref(self._prev), C.byref(self._valid)),
                       "b200_runner_finish")

@@ -23,12 +23,119 @@ from the stored activation (H > 0 <=> kept and positive).
 """
 from __future__ import annotations
 
-from typing import Dict, Tuple
+import ctypes as C
+import os
+from typing import Dict, Optional, Tuple
 
 import torch
 
 from .. import _native as nat
 from .._native import bindings as B
+
+
+class FusedSession:
+    """Native session of the fused step (``csrc/mlp_fused.cu``): ONE 8-CTA-cluster kernel for
+    forward + cross-entropy + backward, then the fused all-reduce + optimizer kernel — two
+    launches per step, issued from C without a CUDA graph.  Built for the reference's model
+    class (ref ``train.py:32-50``): two hidden layers of 256, at most 16 classes, at most 1024
+    inputs, batches of at most 64; everything else runs the GEMM-per-layer schedule below."""
+
+    MAX_BATCH = 64
+
+    @staticmethod
+    def supports(prog: "MLPProgram") -> bool:
+        L = prog.layers
+        if os.environ.get("B200DDP_NO_FUSED_MLP") or len(L) != 3:
+            return False
+        return (L[0]["n_out"] == 256 and L[1]["n_in"] == 256 and L[1]["n_out"] == 256
+                and L[2]["n_in"] == 256 and L[2]["n_out"] <= 16
+                and 64 <= L[0]["n_in"] <= 1024 and L[0]["n_in"] % 8 == 0)
+
+    def __init__(self, prog: "MLPProgram"):
+        eng = prog.engine
+        self.prog, self.engine, self.device = prog, eng, prog.device
+        self.L = nat.lib()
+        self.in_features = prog.layers[0]["n_in"]
+        self.scratch = torch.empty(int(self.L.b200_mlp_scratch_bytes()), dtype=torch.uint8, device=self.device)
+        self.loss = torch.zeros(2, dtype=torch.float32, device=self.device)
+        self.handle: Optional[int] = None
+        self.host_ready = False
+        self._build()
+
+    def _build(self) -> None:
+        eng, prog, opt = self.engine, self.prog, self.engine.optimizer
+        d = B.MlpDesc()
+        d.in_features, d.hidden, d.classes = self.in_features, 256, prog.layers[2]["n_out"]
+        (d.W1, d.W2, d.W3) = (l["w"].data_ptr() for l in prog.layers)
+        (d.b1, d.b2, d.b3) = (l["b"].data_ptr() for l in prog.layers)
+        (d.gW1, d.gW2, d.gW3) = (l["gw"].data_ptr() for l in prog.layers)
+        (d.gb1, d.gb2, d.gb3) = (l["gb"].data_ptr() for l in prog.layers)
+        d.grad_parity_stride = eng.grad_parity_stride
+        d.scratch, d.loss_out = self.scratch.data_ptr(), self.loss.data_ptr()
+        d.step_dev = opt.step_dev.data_ptr()
+        d.dropout_p1, d.dropout_p2 = prog.layers[0]["p"], prog.layers[1]["p"]
+        d.seed = prog.seed
+        d.hp = B.make_hparams(opt, 1.0 / eng.world_size)
+        d.master, d.grad = opt.master.data_ptr(), eng.grad.data_ptr()
+        d.exp_avg = opt.exp_avg.data_ptr()
+        d.exp_avg_sq = opt.exp_avg_sq.data_ptr() if opt.kind != "sgd" else None
+        d.shadow = opt.shadow.data_ptr()
+        buckets = eng.layout.buckets
+        if len(buckets) > len(d.bucket_start):
+            raise RuntimeError("too many buckets for the fused MLP session")
+        d.n_buckets = len(buckets)
+        comm = None
+        if eng.world_size > 1:
+            symm = eng.symm
+            algos = [symm.pick_algo(eng, b) for b in buckets]
+            symm.vec_elems = 4
+            symm.two_shot_buckets.update(b.index for b, al in zip(buckets, algos) if al >= 1)
+            comm = symm.comm(eng.grad, eng.shadow, master=eng.master, f32_mask=eng.f32_mask,
+                             parity_stride=eng.grad_parity_stride,
+                             no_exit_wait=eng.grad_parity_stride > 0)
+            d.comm = C.pointer(comm)
+        else:
+            algos = [0] * len(buckets)
+        for k, b in enumerate(buckets):
+            d.bucket_start[k], d.bucket_n[k], d.bucket_algo[k] = b.start, b.numel, algos[k]
+        self.algos = algos
+        h = C.c_void_p()
+        nat.check(self.L.b200_mlp_create(C.byref(h), C.byref(d)), "b200_mlp_create")
+        self.handle = h.value
+        self._keep = (d, comm)
+
+    def rebuild(self) -> None:
+        """Hyper-parameters are baked into the session: drop it and build a new one."""
+        self.close()
+        self.host_ready = False
+        self._build()
+
+    def close(self) -> None:
+        if self.handle is not None:
+            torch.cuda.synchronize(self.device)
+            self.L.b200_mlp_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001 - interpreter shutdown
+            pass
+
+    # ------------------------------------------------------------------ stepping
+    def forward_backward(self, x: torch.Tensor, y: torch.Tensor, train: bool,
+                         logits_out: Optional[torch.Tensor] = None) -> None:
+        nat.check(self.L.b200_mlp_forward_backward(
+            self.handle, x.data_ptr(), y.data_ptr(), x.shape[0], int(train),
+            logits_out.data_ptr() if logits_out is not None else None, nat.stream_ptr(self.device)),
+            "b200_mlp_forward_backward")
+
+    def train(self, x_pool: torch.Tensor, y_pool: torch.Tensor, first: int, count: int) -> None:
+        """`count` steps over the device-resident pool x_pool [P, bsz, in] / y_pool [P, bsz]."""
+        nat.check(self.L.b200_mlp_train(
+            self.handle, x_pool.data_ptr(), y_pool.data_ptr(), x_pool.shape[-2],
+            x_pool.shape[0] if x_pool.dim() == 3 else 1, first, count, nat.stream_ptr(self.device)),
+            "b200_mlp_train")
 
 
 class _Buffers:
@@ -82,16 +189,60 @@ class MLPProgram:
         self._bufs: Dict[int, _Buffers] = {}
         self._side = torch.cuda.Stream(self.device)
         self.launches_per_step = 0
+        # the fused two-launch step when the model is the reference's shape class
+        self.fused: Optional[FusedSession] = FusedSession(self) if FusedSession.supports(self) else None
+        self._last_fused = False
+        if self.fused is not None:
+            self.launches_per_step = 1 + len(engine.layout.buckets)
 
     def on_params_changed(self) -> None:
         pass  # weights are read in place from the arenas; nothing is cached
 
     def invalidate(self) -> None:
-        """Drops the captured graphs (they bake the optimizer hyper-parameters into kernel
-        arguments); the next step re-captures."""
+        """Drops the captured graphs and the native session (both bake the optimizer
+        hyper-parameters into kernel arguments); the next step rebuilds."""
         for b in self._bufs.values():
             b.train_graph = None
             b.eval_graph = None
+        if self.fused is not None:
+            self.fused.rebuild()
+
+    def _fused_ok(self, data: torch.Tensor, target: torch.Tensor) -> bool:
+        return (self.fused is not None and data.shape[0] <= FusedSession.MAX_BATCH
+                and data.dtype == torch.float32 and target.dtype == torch.int64)
+
+    @staticmethod
+    def _flat(data: torch.Tensor, target: torch.Tensor):
+        x = data.reshape(data.shape[0], -1)
+        if not x.is_contiguous():
+            x = x.contiguous()
+        return x, target.contiguous()
+
+    def train_many(self, x_pool: torch.Tensor, y_pool: torch.Tensor, first: int, count: int):
+        """`count` optimisation steps over an on-device pool of batches ([P, bsz, in], [P, bsz]):
+        step i uses batch (first + i) % P.  One native call, two launches per step."""
+        if not self._fused_ok(x_pool[0], y_pool[0]) or not x_pool.is_contiguous() or not y_pool.is_contiguous():
+            loss = None
+            for i in range(count):
+                k = (first + i) % x_pool.shape[0]
+                loss = self.train_step(x_pool[k], y_pool[k])
+            return loss
+        self._leave_gemm_path()
+        self.fused.train(x_pool.reshape(x_pool.shape[0], x_pool.shape[1], -1), y_pool, first, count)
+        return None
+
+    def _leave_gemm_path(self) -> None:
+        self._last_fused = True
+
+    def _enter_gemm_path(self) -> None:
+        """The fused session's one-shot all-reduce leaves without an exit barrier (its gradients
+        are double-buffered); the GEMM schedule writes buffer 0 every step, so a switch between
+        the two needs the peers to have finished reading first."""
+        if self._last_fused and self.engine.world_size > 1 and self.engine.grad_parity_stride:
+            import torch.distributed as dist
+            torch.cuda.synchronize(self.device)
+            dist.barrier()
+        self._last_fused = False
 
     # ------------------------------------------------------------------ schedule
     def _forward(self, bufs: _Buffers, train: bool) -> None:
@@ -183,6 +334,12 @@ class MLPProgram:
                       bufs.zero_train if train else bufs.zero_eval)
 
     def train_step(self, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        if self._fused_ok(data, target):
+            x, y = self._flat(data, target)
+            self._leave_gemm_path()
+            self.fused.train(x, y, 0, 1)
+            return self.fused.loss[0].clone()
+        self._enter_gemm_path()
         bufs = self._get(int(data.shape[0]))
         self._stage(bufs, data, target)
         if bufs.train_graph is None:
@@ -191,6 +348,11 @@ class MLPProgram:
         return bufs.loss[0].clone()
 
     def eval_step(self, data: torch.Tensor, target: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        if self._fused_ok(data, target):
+            x, y = self._flat(data, target)
+            self.fused.forward_backward(x, y, train=False)
+            out = self.fused.loss.clone()
+            return out[0], out[1]
         bufs = self._get(int(data.shape[0]))
         self._stage(bufs, data, target, train=False)
         if bufs.eval_graph is None:
@@ -201,6 +363,11 @@ class MLPProgram:
 
     def logits(self, data: torch.Tensor) -> torch.Tensor:
         """Eval-mode logits [B, classes] fp32 (uncaptured; for tests and ad-hoc inference)."""
+        if self._fused_ok(data, torch.empty(0, dtype=torch.int64)):
+            x, y = self._flat(data, torch.zeros(data.shape[0], dtype=torch.int64, device=self.device))
+            out = torch.empty(x.shape[0], self.dims[-1], dtype=torch.float32, device=self.device)
+            self.fused.forward_backward(x, y, train=False, logits_out=out)
+            return out
         bufs = self._get(int(data.shape[0]))
         self._stage(bufs, data, torch.zeros(data.shape[0], dtype=torch.int64, device=self.device),
                     train=False)

@@ -125,7 +125,12 @@ class SymmetricArena:
         t._b200_peers = peers  # type: ignore[attr-defined]
         return t
 
-    def comm(self, grad: torch.Tensor, push: Optional[torch.Tensor] = None) -> Comm:
+    def comm(self, grad: torch.Tensor, push: Optional[torch.Tensor] = None, *,
+             master: Optional[torch.Tensor] = None, f32_mask: Optional[torch.Tensor] = None,
+             parity_stride: int = 0, no_exit_wait: bool = False) -> Comm:
+        """Kernel-side view of the symmetric arenas.  `master` + `f32_mask`: the sharded kernels
+        also push the fp32 master of the marked parameters (biases, norm scales) to every rank.
+        `parity_stride` / `no_exit_wait`: double-buffered gradients (include/b200ddp.h)."""
         c = Comm()
         c.rank, c.world = self.rank, self.world
         for j in range(self.world):
@@ -136,7 +141,27 @@ class SymmetricArena:
         c.push_mc = (getattr(push, "_b200_mc", 0) or None) if push is not None else None
         c.timeout_ms = self.timeout_ms
         c.max_blocks = 0
+        if f32_mask is not None and master is not None and hasattr(master, "_b200_peers"):
+            for j in range(self.world):
+                c.master_peer[j] = master._b200_peers[j]
+            c.f32_mask = f32_mask.data_ptr()
+        c.parity_stride = parity_stride
+        c.no_exit_wait = int(no_exit_wait)
         return c
+
+    def pick_algo(self, engine, b) -> int:
+        """0 one-shot, 1 two-shot, 2 NVLS for bucket `b` (identical on every rank)."""
+        push = engine.shadow if engine.shadow is not None else engine.master
+        can_push = hasattr(push, "_b200_peers")
+        esize = engine.grad.element_size()
+        algo = 1 if (can_push and engine.allow_two_shot
+                     and b.numel * esize * (self.world - 1) > ONE_SHOT_MAX_BYTES) else 0
+        if (algo == 1 and self.world > 2 and getattr(engine.grad, "_b200_mc", 0)
+                and getattr(push, "_b200_mc", 0)):
+            # in-switch reduction + broadcast; measured faster than P2P two-shot at 8 ranks for
+            # every size, slower at 2 ranks (no traffic saved, multimem overhead)
+            algo = 2
+        return algo
 
     # ------------------------------------------------------------------ engine hooks
     def shard_ranges(self, b) -> List[tuple]:
@@ -158,21 +183,16 @@ class SymmetricArena:
         push = engine.shadow if engine.shadow is not None else engine.master
         can_push = hasattr(push, "_b200_peers")
         wire_bf16 = engine.grad.dtype == torch.bfloat16
-        esize = 2 if wire_bf16 else 4
-        algo = 1 if (can_push and engine.allow_two_shot
-                     and b.numel * esize * (self.world - 1) > ONE_SHOT_MAX_BYTES) else 0
-        if (algo == 1 and self.world > 2 and getattr(engine.grad, "_b200_mc", 0)
-                and getattr(push, "_b200_mc", 0)):
-            # in-switch reduction + broadcast; measured faster than P2P two-shot at 8 ranks for
-            # every size, slower at 2 ranks (no traffic saved, multimem overhead)
-            algo = 2
+        algo = self.pick_algo(engine, b)
         self.vec_elems = 8 if wire_bf16 else 4  # one 16-byte vector of the wire dtype
         if algo >= 1:
             self.two_shot_buckets.add(b.index)
         key = (id(engine), can_push)
         c = self._comm_cache.get(key)
         if c is None:
-            c = self._comm_cache[key] = self.comm(engine.grad, push if can_push else None)
+            c = self._comm_cache[key] = self.comm(
+                engine.grad, push if can_push else None, master=engine.master,
+                f32_mask=engine.f32_mask if engine.shadow is not None else None)
         c.max_blocks = max_blocks
         hp = bindings.make_hparams(opt, scale)
         nat.check(self.L.b200_allreduce_optimizer(

@@ -60,7 +60,12 @@ _QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
 
 
 class ClockSampler:
-    """Samples ``nvidia-smi`` clocks/throttle reasons for one GPU in a thread."""
+    """Samples SM clocks / throttle reasons of one GPU: NVML polled from a thread when ``pynvml``
+    is importable (sub-millisecond period, and ``sample_now()`` for timed regions shorter than
+    any period), else ``nvidia-smi -lms`` in a child process."""
+
+    _REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+                ("sw_power_cap", 0x4))
 
     def __init__(self, index: int = 0, period_ms: int = 100):
         self.index = index
@@ -68,8 +73,57 @@ class ClockSampler:
         self.rows: List[List[str]] = []
         self._proc = None
         self._thread = None
+        self._nvml = None
+        self._handle = None
+        self._stop = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._handle = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(index))
+            self._nvml = pynvml
+        except Exception:  # noqa: BLE001 - no NVML on this box: nvidia-smi fallback
+            self._nvml = None
+
+    @staticmethod
+    def _physical_index(index: int) -> int:
+        import os
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [v.strip() for v in vis.split(",") if v.strip()]
+            if index < len(ids) and ids[index].isdigit():
+                return int(ids[index])
+        return index
+
+    def sample_now(self) -> None:
+        """One NVML reading, appended to the record (call while the GPU is busy)."""
+        nv = self._nvml
+        if nv is None:
+            return
+        try:
+            sm = nv.nvmlDeviceGetClockInfo(self._handle, nv.NVML_CLOCK_SM)
+            mx = nv.nvmlDeviceGetMaxClockInfo(self._handle, nv.NVML_CLOCK_SM)
+            try:
+                mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self._handle)
+            except Exception:  # noqa: BLE001 - older binding name
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._handle)
+            try:
+                power = nv.nvmlDeviceGetPowerUsage(self._handle) / 1000.0
+            except Exception:  # noqa: BLE001
+                power = 0.0
+            self.rows.append([str(sm), str(mx), f"{power:.1f}"] +
+                             ["Active" if mask & bit else "Not Active" for _, bit in self._REASONS])
+        except Exception:  # noqa: BLE001 - a failed reading is a missing sample, not an error
+            pass
 
     def start(self):
+        if self._nvml is not None:
+            def poll():
+                while not self._stop.is_set():
+                    self.sample_now()
+                    self._stop.wait(self.period_ms / 1000.0)
+            self._thread = threading.Thread(target=poll, daemon=True)
+            self._thread.start()
+            return self
         try:
             self._proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}", f"--query-gpu={_QUERY}",
@@ -90,6 +144,9 @@ class ClockSampler:
         return self
 
     def stop(self) -> Dict:
+        self._stop.set()
+        if self._nvml is not None and self._thread is not None:
+            self._thread.join(timeout=2)
         if self._proc is not None:
             self._proc.terminate()
             try:

@@ -16,11 +16,22 @@
 // The reduction order is fixed (rank 0..W-1), so every replica computes bit-
 // identical sums and replicas never drift.
 //
-// Synchronisation: two flag barriers per kernel over peer memory — "gradients
-// ready" before the first remote load and "reads/pushes done" before exit — using
-// monotonically increasing epochs (never reset, so no reset race), release
-// stores / acquire loads at .sys scope, and a bounded spin: a dead peer raises
-// a trap on the survivors instead of wedging seven GPUs.
+// Synchronisation: flag barriers over peer memory with monotonically increasing
+// epochs (never reset, so no reset race), release stores / acquire loads at .sys
+// scope, and a bounded spin: a dead peer raises a trap on the survivors instead of
+// wedging seven GPUs.
+//   entry  "my gradients are ready": one release store per peer, then every block
+//          polls the local copies of the peers' flags (relaxed loads; the last one
+//          is an acquire load).  No stand-alone fence: the gradients were written by
+//          earlier kernels of the stream and are already at the point of coherence.
+//   exit   "I am done reading / my pushes have landed": only where a peer could
+//          otherwise be overtaken — kernels that write peer memory (two-shot, NVLS)
+//          and single-buffered one-shot.  One .sys fence per block drains that
+//          block's remote stores, the last block publishes and waits.
+//   When the producer double-buffers the gradient arena on step parity
+//   (B200_COMM_NO_EXIT_WAIT), one-shot needs no exit barrier at all: a peer can only
+//   overwrite buffer t%2 in step t+2, after its step t+1 kernel saw OUR step t+1
+//   entry flag, which we store after this kernel's reads have completed.
 //
 //   NVLS      (algo 2, when the arenas are bound to an NVSwitch multicast object)  same
 //             sharding as two-shot, but the reduce-scatter is ONE multimem.ld_reduce per
@@ -52,6 +63,10 @@ struct CommArgs {
     uint32_t* flags[MAX_RANKS];   // peer-mapped flag blocks
     const void* grad_mc;          // NVLS: multicast address of the gradient arenas (or null)
     void* push_mc;                // NVLS: multicast address of the parameter arenas (or null)
+    float* master_peer[MAX_RANKS];  // peer-mapped fp32 master arenas (masked fp32 push) or null
+    const uint8_t* f32_mask;      // one byte per 8 elements: non-zero = also push the fp32 master
+    int64_t parity_stride;        // bytes between the two gradient buffers (0 = single-buffered)
+    int no_exit_wait;             // one-shot on double-buffered gradients: skip the exit barrier
     uint64_t timeout_ns;
 };
 
@@ -63,17 +78,26 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
     asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+// volatile + "memory": the loads must stay behind the entry barrier that makes the peers'
+// gradients valid (a pure asm could legally be hoisted above it).
 __device__ __forceinline__ uint4 ld_peer_16(const void* p) {
     uint4 v;
     asm volatile("ld.global.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
                  : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                 : "l"(p));
+                 : "l"(p)
+                 : "memory");
     return v;
 }
 
-// Polls with relaxed loads (cheap: the flag lives in local memory) and fences once on
-// success; bounded so a dead peer traps instead of hanging the GPU.
+// Polls with relaxed loads (cheap: the flag lives in local memory), then takes the value once
+// more with an acquire load — epochs only grow, so it passes — which orders everything after it
+// behind the peer's release store.  Bounded so a dead peer traps instead of hanging the GPU.
 __device__ __forceinline__ void spin_until(const uint32_t* flag, uint32_t epoch, uint64_t timeout_ns,
                                            int who) {
     if ((int32_t)(ld_relaxed_sys(flag) - epoch) < 0) {
@@ -86,7 +110,7 @@ __device__ __forceinline__ void spin_until(const uint32_t* flag, uint32_t epoch,
             }
         }
     }
-    fence_acq_rel_sys();
+    (void)ld_acquire_sys(flag);
 }
 
 // All blocks: wait until every rank has published `epoch` in our ready flags.
@@ -101,11 +125,14 @@ __device__ __forceinline__ void begin_barrier(const CommArgs& a, uint32_t epoch)
     __syncthreads();
 }
 
-// The last block to finish tells every rank we are done reading/pushing, waits
-// for the same from everyone, then advances the local epoch.  One thread per block
-// fences after the CTA barrier (cumulative over the block's remote stores).
+// Exit.  Every block takes a ticket; the last one advances the local epoch (and the optimizer's
+// device step counter).  With WAIT it first tells every rank "I am done" and waits for the same
+// from everyone.  REMOTE_WRITES: one thread per block drains the block's stores to peer memory
+// with a .sys fence (cumulative over the CTA barrier in front of it) before taking the ticket,
+// so the last block's release store publishes all of them.
 template <bool REMOTE_WRITES>
-__device__ __forceinline__ void end_barrier(const CommArgs& a, uint32_t epoch, int* step_dev, int new_step) {
+__device__ __forceinline__ void end_barrier(const CommArgs& a, uint32_t epoch, int* step_dev, int new_step,
+                                            bool wait) {
     __shared__ int s_last;
     __syncthreads();
     uint32_t* mine = a.flags[a.rank];
@@ -113,20 +140,21 @@ __device__ __forceinline__ void end_barrier(const CommArgs& a, uint32_t epoch, i
         if (REMOTE_WRITES) fence_acq_rel_sys(); else __threadfence();
         const unsigned t = atomicAdd(mine + F_TICKET, 1u);
         s_last = (t == gridDim.x - 1);
+        if (s_last) __threadfence();   // acquire side of the ticket chain
     }
     __syncthreads();
     if (!s_last) return;
-    if (threadIdx.x < a.world) {
-        if (REMOTE_WRITES) fence_acq_rel_sys();
-        st_release_sys(a.flags[threadIdx.x] + F_DONE + a.rank, epoch);
-        spin_until(mine + F_DONE + threadIdx.x, epoch, a.timeout_ns, threadIdx.x);
+    if (wait) {
+        if (threadIdx.x < a.world) {
+            st_release_sys(a.flags[threadIdx.x] + F_DONE + a.rank, epoch);
+            spin_until(mine + F_DONE + threadIdx.x, epoch, a.timeout_ns, threadIdx.x);
+        }
+        __syncthreads();
     }
-    __syncthreads();
     if (threadIdx.x == 0) {
         mine[F_TICKET] = 0;
         mine[F_EPOCH] = epoch;
         if (step_dev) step_dev[0] = new_step;
-        __threadfence();
     }
 }
 
@@ -150,13 +178,15 @@ __device__ __forceinline__ void unpack(const uint4& raw, float (&f)[Vec<BF16>::N
 }
 
 // Fixed-order (rank 0..W-1) fp32 sum of vector i across all ranks' arenas.
+// `poff` is the byte offset of the gradient buffer in use (step parity; 0 when single-buffered).
 template <bool BF16>
-__device__ __forceinline__ void reduce_vec(const CommArgs& a, int64_t i, float (&s)[Vec<BF16>::N]) {
+__device__ __forceinline__ void reduce_vec(const CommArgs& a, int64_t poff, int64_t i, float (&s)[Vec<BF16>::N]) {
     constexpr int N = Vec<BF16>::N;
     uint4 raw[MAX_RANKS];
 #pragma unroll
     for (int j = 0; j < MAX_RANKS; ++j)
-        if (j < a.world) raw[j] = ld_peer_16(reinterpret_cast<const uint4*>(a.grad[j]) + i);  // all in flight
+        if (j < a.world)   // all in flight
+            raw[j] = ld_peer_16(reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(a.grad[j]) + poff) + i);
     unpack<BF16>(raw[0], s);
 #pragma unroll
     for (int j = 1; j < MAX_RANKS; ++j)
@@ -229,13 +259,16 @@ __global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
     begin_barrier(a, epoch);  // includes __syncthreads
     const OptScalars s = sc;
 
+    // gradient buffer of this step: the producer alternates between two on step parity
+    const int64_t poff = ((s.t - 1) & 1) ? a.parity_stride : 0;
+    const void* grad_mc = reinterpret_cast<const char*>(a.grad_mc) + poff;
     int64_t lo, hi;
     my_range<ALGO>(a, start / N, (start + n) / N, lo, hi);
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
         float g[N];
-        if (ALGO == 2) reduce_vec_mc<BF16>(a.grad_mc, i, g);
-        else reduce_vec<BF16>(a, i, g);
+        if (ALGO == 2) reduce_vec_mc<BF16>(grad_mc, i, g);
+        else reduce_vec<BF16>(a, poff, i, g);
         float pp[N], mm[N], vv[N];
 #pragma unroll
         for (int q = 0; q < N / 4; ++q) {
@@ -293,8 +326,22 @@ __global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
                             make_float4(pp[4 * q], pp[4 * q + 1], pp[4 * q + 2], pp[4 * q + 3]);
                 }
         }
+        // Sharded update with a bf16 push: the fp32 master is current only on the shard owner.
+        // Parameters that forward reads in fp32 (biases, norm scales / shifts) are marked in
+        // f32_mask; their fp32 values go to every rank's master as well, so all replicas compute
+        // with the same numbers (they are a fraction of a percent of the bytes).
+        if (ALGO >= 1 && PUSH_BF16 && a.f32_mask && a.f32_mask[(i * N) >> 3]) {
+#pragma unroll
+            for (int j = 0; j < MAX_RANKS; ++j)
+                if (j < a.world && j != a.rank) {
+#pragma unroll
+                    for (int q = 0; q < N / 4; ++q)
+                        reinterpret_cast<float4*>(a.master_peer[j])[i * (N / 4) + q] =
+                            make_float4(pp[4 * q], pp[4 * q + 1], pp[4 * q + 2], pp[4 * q + 3]);
+                }
+        }
     }
-    end_barrier<ALGO >= 1>(a, epoch, advance ? step_dev : nullptr, s.t);
+    end_barrier<ALGO >= 1>(a, epoch, advance ? step_dev : nullptr, s.t, ALGO >= 1 || !a.no_exit_wait);
 }
 
 // Plain all-reduce (sum * scale), for the bandwidth sweep and generic use.
@@ -311,7 +358,7 @@ __global__ void __launch_bounds__(256) allreduce_kernel(const CommArgs a, int64_
     for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
         float g[N];
         if (ALGO == 2) reduce_vec_mc<BF16>(a.grad_mc, i, g);
-        else reduce_vec<BF16>(a, i, g);
+        else reduce_vec<BF16>(a, 0, i, g);
         uint4 o;
         if constexpr (BF16) {
             o = make_uint4(pack_bf16(g[0] * scale, g[1] * scale), pack_bf16(g[2] * scale, g[3] * scale),
@@ -328,7 +375,7 @@ __global__ void __launch_bounds__(256) allreduce_kernel(const CommArgs a, int64_
                 if (j < a.world) reinterpret_cast<uint4*>(const_cast<void*>(a.grad[j]))[i] = o;
         }
     }
-    end_barrier<ALGO >= 1>(a, epoch, nullptr, 0);
+    end_barrier<ALGO >= 1>(a, epoch, nullptr, 0, true);
 }
 
 static int fill_args(const b200_comm* c, CommArgs* a) {
@@ -344,6 +391,17 @@ static int fill_args(const b200_comm* c, CommArgs* a) {
     }
     a->grad_mc = c->grad_mc;
     a->push_mc = c->push_mc;
+    a->f32_mask = (const uint8_t*)c->f32_mask;
+    for (int j = 0; j < MAX_RANKS; ++j) {
+        a->master_peer[j] = (j < c->world && c->f32_mask) ? (float*)c->master_peer[j] : nullptr;
+        if (j < c->world && c->f32_mask)
+            B200_REQUIRE(a->master_peer[j], "comm: f32_mask needs the peer-mapped master of rank %d", j);
+    }
+    a->parity_stride = c->parity_stride;
+    a->no_exit_wait = c->no_exit_wait;
+    B200_REQUIRE(c->parity_stride >= 0 && (c->parity_stride % 16) == 0, "comm: parity_stride must be a multiple of 16");
+    B200_REQUIRE(!c->no_exit_wait || c->parity_stride > 0,
+                 "comm: no_exit_wait is only safe on a double-buffered gradient arena (parity_stride > 0)");
     a->timeout_ns = c->timeout_ms > 0 ? (uint64_t)c->timeout_ms * 1000000ull : 30000000000ull;
     return 0;
 }

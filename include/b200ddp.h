@@ -284,6 +284,17 @@ typedef struct {
     void* push_mc;               /* NVLS multicast address of all parameter arenas, or null */
     int timeout_ms;              /* spin bound before the kernel traps; 0 = 30 s */
     int max_blocks;              /* 0 = default */
+    /* Sharded algorithms (1, 2) with a bf16 push keep the fp32 master current only on the shard
+     * owner.  f32_mask (device, one byte per 8 arena elements) marks the parameters whose fp32
+     * value forward reads (biases, norm scales/shifts): for those the kernel also stores the fp32
+     * master into every rank's master_peer[] arena.  Null = no such parameters. */
+    void* master_peer[B200_MAX_RANKS];
+    const void* f32_mask;
+    /* Double-buffered gradients: the producer of step t (1-based) writes the arena at byte offset
+     * ((t-1)&1) * parity_stride and the kernel reads there.  0 = single buffer.  With two buffers a
+     * one-shot kernel (algo 0) needs no exit barrier: set no_exit_wait. */
+    int64_t parity_stride;
+    int no_exit_wait;
 } b200_comm;
 #define B200_COMM_FLAG_WORDS (2 * B200_MAX_RANKS + 2)
 
@@ -310,6 +321,55 @@ int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200_opt_hparam
  * all-reduce sweep of BASELINE.json. */
 int b200_allreduce(const b200_comm* c, int algo, int64_t start, int64_t n, int is_bf16, void* out,
                    float scale, void* stream);
+
+/* ---------------------------------------------------------------- fused MLP training step
+ * The reference's model (ref train.py:32-50: 784-256-256-10 with ReLU + dropout) and its step
+ * (ref train.py:135-139: zero_grad, forward, criterion, backward, optimizer.step) as TWO launches:
+ * one 8-CTA-cluster kernel for forward + cross-entropy + backward (csrc/mlp_fused.cu: tcgen05 MMAs
+ * on TMA-loaded weight tiles, activations kept transposed in shared memory, split-K partials through
+ * an L2-resident scratch ordered by hardware cluster barriers) and the fused all-reduce + optimizer
+ * kernel.  Shapes: hidden width 256 (two hidden layers), in_features a multiple of 8 up to 1024,
+ * up to 16 classes, batch up to 64 per call; other MLPs run the GEMM-per-layer program.
+ * The session object owns the TMA descriptors and, for the end-to-end path, a device input ring and
+ * a mapped pinned loss ring (allocated by b200_mlp_create / b200_mlp_host_init, nothing afterwards). */
+#define B200_MLP_MAX_BUCKETS 4
+typedef struct {
+    int in_features, hidden, classes;
+    const void *W1, *W2, *W3;          /* bf16 [hidden,in], [hidden,hidden], [classes,hidden] */
+    const float *b1, *b2, *b3;         /* fp32 */
+    float *gW1, *gb1, *gW2, *gb2, *gW3, *gb3;   /* fp32 gradient arena slices (buffer 0) */
+    int64_t grad_parity_stride;        /* bytes to gradient buffer 1; step t (1-based) writes buffer (t-1)&1 */
+    void* scratch;                     /* b200_mlp_scratch_bytes() bytes, any contents */
+    float* loss_out;                   /* [2]: mean loss, number of correct rows */
+    int* step_dev;                     /* optimizer step counter {t, ticket} (dropout stream, parity) */
+    float dropout_p1, dropout_p2;
+    uint64_t seed;
+    /* the update chained after the backward by b200_mlp_train / b200_mlp_host_step */
+    b200_opt_hparams hp;
+    float *master, *grad, *exp_avg, *exp_avg_sq;   /* arena bases */
+    void* shadow;                      /* bf16 parameter arena base */
+    int n_buckets;
+    int64_t bucket_start[B200_MLP_MAX_BUCKETS], bucket_n[B200_MLP_MAX_BUCKETS];
+    int bucket_algo[B200_MLP_MAX_BUCKETS];
+    const b200_comm* comm;             /* null: single GPU (flat optimizer kernel) */
+    b200_comm comm_copy;               /* filled by b200_mlp_create */
+} b200_mlp_desc;
+int64_t b200_mlp_scratch_bytes(void);
+int b200_mlp_create(void** session, const b200_mlp_desc* d);
+int b200_mlp_destroy(void* session);
+/* forward (+ backward when train) on device inputs x fp32 [bsz,in], y int64 [bsz]; no update.
+ * logits_out: optional fp32 [bsz, classes]. */
+int b200_mlp_forward_backward(void* session, const float* x, const int64_t* y, int bsz, int train,
+                              float* logits_out, void* stream);
+/* `count` full training steps over a device-resident pool of batches (x_base [pool,bsz,in],
+ * y_base [pool,bsz]); step i uses batch (first + i) % pool. */
+int b200_mlp_train(void* session, const float* x_base, const int64_t* y_base, int bsz, int64_t pool,
+                   int64_t first, int64_t count, void* stream);
+/* end-to-end path (ref train.py:133,141): pinned host batch in, previous step's loss out */
+int b200_mlp_host_init(void* session, int bsz, int slots);
+int b200_mlp_host_step(void* session, const void* host_x, const void* host_y, int bsz, float* prev_loss,
+                       int* prev_valid, void* stream);
+int b200_mlp_host_finish(void* session, float* last_loss, int* valid, void* stream);
 
 /* ---------------------------------------------------------------- pooling (NHWC bf16, C % 8 == 0)
  * BASELINE.json config 3 (ResNet-50); no counterpart in the reference (its baseline runs ATen's

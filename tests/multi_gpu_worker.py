@@ -119,26 +119,69 @@ def check_fused_optimizer(rank, world, dev, compute_dtype, two_shot, kind):
         f"{str(compute_dtype).split('.')[-1]} matches NCCL + torch-op update; replicas identical")
 
 
-def check_program(rank, world, dev):
-    symm_mod.ONE_SHOT_MAX_BYTES = 2 << 20
+def check_program(rank, world, dev, sharded, fused=True):
+    """The SimpleNet step program at world > 1.  `sharded` forces the two-shot / NVLS kernels
+    (whose fp32 master lives on the shard owner); otherwise the size rule decides.  Replicas must
+    compute with identical numbers EVERY step, biases included, without consolidate_state()."""
+    symm_mod.ONE_SHOT_MAX_BYTES = 0 if sharded else 2 << 20
+    if not fused:
+        os.environ["B200DDP_NO_FUSED_MLP"] = "1"
+    else:
+        os.environ.pop("B200DDP_NO_FUSED_MLP", None)
     torch.manual_seed(100 + rank)  # different init per rank: ctor broadcast must fix it
     eng = DataParallel(SimpleNet().to(dev), backend="b200", compute_dtype=torch.bfloat16, lr=1e-3)
-    assert eng.program is not None
+    os.environ.pop("B200DDP_NO_FUSED_MLP", None)
+    assert eng.program is not None and (eng.program.fused is not None) == fused
     torch.manual_seed(200 + rank)
     x = torch.randn(64, 784, device=dev); y = torch.randint(0, 10, (64,), device=dev)
-    losses = [eng.train_step(x, y) for _ in range(40)]
+    torch.manual_seed(4242)
+    xc = torch.randn(64, 784, device=dev)          # the same probe batch on every rank
+    losses = []
+    for step in range(40):
+        losses.append(eng.train_step(x, y))
+        if step in (0, 1, 7, 39):
+            # ADVICE r1: biases read by forward must be current on every rank after every step
+            lg = eng.program.logits(xc)
+            allg = [torch.empty_like(lg) for _ in range(world)]
+            dist.all_gather(allg, lg)
+            assert all(torch.equal(allg[0], t) for t in allg), f"replica logits differ after step {step + 1}"
+            for lay in eng.program.layers:
+                bs = [torch.empty_like(lay["b"]) for _ in range(world)]
+                dist.all_gather(bs, lay["b"].contiguous())
+                assert all(torch.equal(bs[0], t) for t in bs), f"fp32 biases differ after step {step + 1}"
     torch.cuda.synchronize()
     l0, l1 = losses[0].item(), losses[-1].item()
     assert l1 < 0.6 * l0, (l0, l1)
     gs = [torch.empty_like(eng.shadow) for _ in range(world)]
     dist.all_gather(gs, eng.shadow)
     assert all(torch.equal(gs[0], t) for t in gs), "bf16 replicas diverged under the step program"
+    algos = eng.program.fused.algos if fused else None
     eng.consolidate_state()  # two-shot/NVLS buckets keep the fp32 master on the shard owner
     got = [torch.empty_like(eng.master) for _ in range(world)]
     dist.all_gather(got, eng.master)
     assert all(torch.equal(got[0], t) for t in got), "replicas diverged under the step program"
     assert eng.optimizer.step_dev[0].item() == 40
-    log(f"fused step program at world {world}: loss {l0:.3f} -> {l1:.3f}, replicas bit-identical")
+    log(f"{'fused cluster-kernel' if fused else 'GEMM-per-layer'} step program at world {world} "
+        f"({'sharded' if sharded else 'size rule'}; algos {algos}): loss {l0:.3f} -> {l1:.3f}, "
+        f"replicas bit-identical every step")
+
+
+def check_program_pool(rank, world, dev):
+    """engine.train_steps (one native call, two launches per step) == the same steps one by one."""
+    symm_mod.ONE_SHOT_MAX_BYTES = 2 << 20
+    torch.manual_seed(300)
+    net = SimpleNet().to(dev)
+    a = DataParallel(copy.deepcopy(net), backend="b200", compute_dtype=torch.bfloat16, lr=1e-3)
+    b = DataParallel(copy.deepcopy(net), backend="b200", compute_dtype=torch.bfloat16, lr=1e-3)
+    torch.manual_seed(400 + rank)
+    xs = torch.randn(6, 64, 784, device=dev); ys = torch.randint(0, 10, (6, 64), device=dev)
+    a.train_steps(xs, ys, 0, 50)
+    for i in range(50):
+        b.train_step(xs[i % 6], ys[i % 6])
+    torch.cuda.synchronize()
+    assert torch.equal(a.shadow, b.shadow), rel(a.shadow, b.shadow)
+    assert a.optimizer.step_count == 50 and a.optimizer.step_dev[0].item() == 50
+    log("train_steps over a device pool == 50 single steps (bit-identical), back-to-back no-exit-wait kernels")
 
 
 def check_autograd_overlap(rank, world, dev):
@@ -171,11 +214,14 @@ def main():
     arena = SymmetricArena(dev, rank, world)
     log(f"world {world}: NVLS multicast memory {'available' if arena.nvls else 'unavailable: ' + getattr(arena, '_nvls_error', 'disabled')}")
     check_plain_allreduce(arena, rank, world, dev)
-    for kind in ("adam", "sgd"):
+    for kind in ("adam", "adamw", "sgd"):
         for dtype in (torch.float32, torch.bfloat16):
             for two_shot in (False, True):
                 check_fused_optimizer(rank, world, dev, dtype, two_shot, kind)
-    check_program(rank, world, dev)
+    for sharded in (False, True):
+        check_program(rank, world, dev, sharded, fused=True)
+    check_program(rank, world, dev, True, fused=False)
+    check_program_pool(rank, world, dev)
     check_autograd_overlap(rank, world, dev)
     dist.barrier()
     log("MULTI_GPU_OK")
