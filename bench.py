@@ -87,7 +87,7 @@ def timed(fn_run, steps: int, warmup: int, device, sample_clocks: bool, fn_end=N
     the steps left pending, still inside the timed region.  Returns (ms total max-over-ranks,
     clocks dict).  Clocks: NVML is polled every 2 ms from the start of the warm-up (the GPU is
     already under load) and read once more the moment the timed steps have been submitted, so
-    even a 20-step region (< 1 ms) has a reading taken while it runs."""
+    even a 20-step region (< 1 ms) has a reading taken while (or right after) it runs."""
     from b200ddp.utils.profiling import ClockSampler
     sampler = ClockSampler(index=device.index or 0, period_ms=2).start() if sample_clocks else None
     fn_run(0, warmup)
@@ -99,11 +99,9 @@ def timed(fn_run, steps: int, warmup: int, device, sample_clocks: bool, fn_end=N
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     fn_run(warmup, steps)
-    if sampler:
-        sampler.sample_now()
     if fn_end is not None:
         fn_end()
-    e1.record()
+    e1.record()               # enqueued before any NVML call: a reading costs the host milliseconds
     if sampler:
         sampler.sample_now()
     torch.cuda.synchronize()

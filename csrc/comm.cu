@@ -44,6 +44,8 @@
 #include "common.cuh"
 #include "optim_update.cuh"
 
+#include <cstdlib>
+
 void b200_count_launch(int n);
 
 namespace b200 {
@@ -251,6 +253,10 @@ __global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
     int step_host, int advance) {
     constexpr int N = Vec<BF16>::N;
     __shared__ OptScalars sc;
+    // Programmatic dependent launch (no-ops on an ordinary launch): become resident while the
+    // backward kernel is still running, start when it completes.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const uint32_t epoch = *(volatile uint32_t*)(a.flags[a.rank] + F_EPOCH) + 1u;
     if (threadIdx.x == 0) {
         const int t = step_dev ? (*(volatile int*)step_dev + 1) : step_host;
@@ -446,11 +452,11 @@ extern "C" int b200_symm_free(void* ptr) {
 }
 
 // ------------------------------------------------------------------ collectives
-extern "C" int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200_opt_hparams* hp,
-                                        int64_t start, int64_t n, int grad_is_bf16, float* master,
-                                        float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
-                                        int push_is_bf16, int* step_dev, int step_host, int advance,
-                                        void* stream) {
+static int allreduce_optimizer_impl(const b200_comm* c, int algo, const b200_opt_hparams* hp,
+                                    int64_t start, int64_t n, int grad_is_bf16, float* master,
+                                    float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
+                                    int push_is_bf16, int* step_dev, int step_host, int advance,
+                                    void* stream, bool pdl) {
     using namespace b200;
     CommArgs a;
     int rc = fill_args(c, &a);
@@ -464,11 +470,20 @@ extern "C" int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200
     const int64_t nv = n / (grad_is_bf16 ? 8 : 4);
     const int64_t vecs = (algo >= 1 ? (nv + c->world - 1) / c->world : nv);
     const int blocks = grid_for(vecs, c->max_blocks > 0 ? c->max_blocks : 296);
-    cudaStream_t s = (cudaStream_t)stream;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)blocks);
+    cfg.blockDim = dim3(256);
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    const b200_opt_hparams h = *hp;
+    __nv_bfloat16* sh = (__nv_bfloat16*)shadow_bf16;
 #define GO(BF, AL, PB)                                                                             \
-    allreduce_optimizer_kernel<BF, AL, PB><<<blocks, 256, 0, s>>>(                                 \
-        a, *hp, start, n, master, exp_avg, exp_avg_sq, (__nv_bfloat16*)shadow_bf16, step_dev,      \
-        step_host, advance)
+    B200_CUDA_OK(cudaLaunchKernelEx(&cfg, allreduce_optimizer_kernel<BF, AL, PB>, a, h, start, n,  \
+                                    master, exp_avg, exp_avg_sq, sh, step_dev, step_host, advance))
     if (algo == 0) { if (grad_is_bf16) GO(true, 0, false); else GO(false, 0, false); }
     else if (algo == 2) {
         if (push_is_bf16) { if (grad_is_bf16) GO(true, 2, true); else GO(false, 2, true); }
@@ -478,8 +493,26 @@ extern "C" int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200
     else { if (grad_is_bf16) GO(true, 1, false); else GO(false, 1, false); }
 #undef GO
     b200_count_launch(1);
-    B200_CUDA_OK(cudaGetLastError());
     return 0;
+}
+
+extern "C" int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200_opt_hparams* hp,
+                                        int64_t start, int64_t n, int grad_is_bf16, float* master,
+                                        float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
+                                        int push_is_bf16, int* step_dev, int step_host, int advance,
+                                        void* stream) {
+    return allreduce_optimizer_impl(c, algo, hp, start, n, grad_is_bf16, master, exp_avg, exp_avg_sq, shadow_bf16,
+                                    push_is_bf16, step_dev, step_host, advance, stream, false);
+}
+
+// Launched with programmatic stream serialization (used behind the fused MLP step kernel).
+int b200_allreduce_optimizer_pdl(const b200_comm* c, int algo, const b200_opt_hparams* hp, int64_t start, int64_t n,
+                                 int grad_is_bf16, float* master, float* exp_avg, float* exp_avg_sq,
+                                 void* shadow_bf16, int push_is_bf16, int* step_dev, int step_host, int advance,
+                                 void* stream) {
+    static const bool pdl = getenv("B200DDP_NO_PDL") == nullptr;
+    return allreduce_optimizer_impl(c, algo, hp, start, n, grad_is_bf16, master, exp_avg, exp_avg_sq, shadow_bf16,
+                                    push_is_bf16, step_dev, step_host, advance, stream, pdl);
 }
 
 extern "C" int b200_allreduce(const b200_comm* c, int algo, int64_t start, int64_t n, int is_bf16,

@@ -8,6 +8,8 @@
 #include "common.cuh"
 #include "optim_update.cuh"
 
+#include <cstdlib>
+
 void b200_count_launch(int n);
 
 namespace b200 {
@@ -18,6 +20,10 @@ __global__ void __launch_bounds__(256) optimizer_kernel(
     float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, int64_t n, int* step_dev,
     int step_host, int advance) {
     __shared__ OptScalars sc;
+    // Programmatic dependent launch (no-ops on an ordinary launch): let the next kernel's
+    // prologue start, then wait for the producer of the gradients.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     if (threadIdx.x == 0) {
         const int t = step_dev ? (*(volatile int*)step_dev + 1) : step_host;
         sc = make_opt_scalars(hp, t);
@@ -81,10 +87,10 @@ __global__ void __launch_bounds__(256) optimizer_kernel(
 
 }  // namespace b200
 
-extern "C" int b200_optimizer_step(const b200_opt_hparams* hp, float* master, const void* grad,
-                                   int grad_is_bf16, float* exp_avg, float* exp_avg_sq,
-                                   void* shadow_bf16, int64_t n, int* step_dev, int step_host,
-                                   int advance, void* stream) {
+static int optimizer_step_impl(const b200_opt_hparams* hp, float* master, const void* grad,
+                               int grad_is_bf16, float* exp_avg, float* exp_avg_sq,
+                               void* shadow_bf16, int64_t n, int* step_dev, int step_host,
+                               int advance, void* stream, bool pdl) {
     B200_REQUIRE(hp && master && grad && exp_avg, "optimizer_step: null pointer");
     B200_REQUIRE(hp->kind >= 0 && hp->kind <= 2, "optimizer_step: unknown kind %d", hp->kind);
     B200_REQUIRE(hp->kind == 2 || exp_avg_sq, "optimizer_step: Adam needs exp_avg_sq");
@@ -99,16 +105,41 @@ extern "C" int b200_optimizer_step(const b200_opt_hparams* hp, float* master, co
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int64_t want = (n / 4 + 255) / 256;
     int blocks = (int)(want < 1 ? 1 : (want > (int64_t)sms * 8 ? (int64_t)sms * 8 : want));
-    cudaStream_t s = (cudaStream_t)stream;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)blocks);
+    cfg.blockDim = dim3(256);
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    const b200_opt_hparams h = *hp;
+    __nv_bfloat16* sh = (__nv_bfloat16*)shadow_bf16;
     if (grad_is_bf16)
-        b200::optimizer_kernel<true><<<blocks, 256, 0, s>>>(
-            *hp, master, grad, exp_avg, exp_avg_sq, (__nv_bfloat16*)shadow_bf16, n, step_dev,
-            step_host, advance);
+        B200_CUDA_OK(cudaLaunchKernelEx(&cfg, b200::optimizer_kernel<true>, h, master, grad, exp_avg, exp_avg_sq, sh, n,
+                                        step_dev, step_host, advance));
     else
-        b200::optimizer_kernel<false><<<blocks, 256, 0, s>>>(
-            *hp, master, grad, exp_avg, exp_avg_sq, (__nv_bfloat16*)shadow_bf16, n, step_dev,
-            step_host, advance);
+        B200_CUDA_OK(cudaLaunchKernelEx(&cfg, b200::optimizer_kernel<false>, h, master, grad, exp_avg, exp_avg_sq, sh, n,
+                                        step_dev, step_host, advance));
     b200_count_launch(1);
-    B200_CUDA_OK(cudaGetLastError());
     return 0;
+}
+
+extern "C" int b200_optimizer_step(const b200_opt_hparams* hp, float* master, const void* grad,
+                                   int grad_is_bf16, float* exp_avg, float* exp_avg_sq,
+                                   void* shadow_bf16, int64_t n, int* step_dev, int step_host,
+                                   int advance, void* stream) {
+    return optimizer_step_impl(hp, master, grad, grad_is_bf16, exp_avg, exp_avg_sq, shadow_bf16, n, step_dev,
+                               step_host, advance, stream, false);
+}
+
+// Launched with programmatic stream serialization: the kernel's blocks become resident while the
+// producer of the gradients is still running and start the moment it completes (csrc/mlp_fused.cu).
+int b200_optimizer_step_pdl(const b200_opt_hparams* hp, float* master, const void* grad, int grad_is_bf16,
+                            float* exp_avg, float* exp_avg_sq, void* shadow_bf16, int64_t n, int* step_dev,
+                            int step_host, int advance, void* stream) {
+    static const bool pdl = getenv("B200DDP_NO_PDL") == nullptr;
+    return optimizer_step_impl(hp, master, grad, grad_is_bf16, exp_avg, exp_avg_sq, shadow_bf16, n, step_dev,
+                               step_host, advance, stream, pdl);
 }

@@ -444,20 +444,13 @@ def test_fused_mlp_step_matches_gemm_program(monkeypatch, bsz):
     # eval path and logits of the fused forward-only kernel vs fp32 torch on the bf16 weights
     loss_e, correct = fused.eval_step(x, y)
     logits = fused.program.logits(x)
-    W = [fused.shadow[s.offset:s.offset + s.numel].view(s.shape).float() for s in fused.layout.slots if len(s.shape) == 2]
-    bvec = [fused.master[s.offset:s.offset + s.numel] for s in fused.layout.slots if len(s.shape) == 1]
-    by_out = {w.shape[0]: w for w in W}
-    W1 = [w for w in W if w.shape[1] == 784][0]
-    W3 = [w for w in W if w.shape[0] == 10][0]
-    W2 = [w for w in W if w.shape == (256, 256)][0]
-    b1 = [v for v in bvec if v.numel() == 256]
-    # layout order is gradient-ready order: identify biases by matching against the module
-    mod = fused.module
+    slot = {s.name: s for s in fused.layout.slots}
+    W1, W2, W3 = (fused.shadow[slot[n].offset:slot[n].offset + slot[n].numel].view(slot[n].shape).float()
+                  for n in ("layers.0.weight", "layers.3.weight", "layers.6.weight"))
+    m1, m2, m3 = (fused.master[slot[n].offset:slot[n].offset + slot[n].numel]
+                  for n in ("layers.0.bias", "layers.3.bias", "layers.6.bias"))
     xr = x.to(torch.bfloat16).float()
     r = lambda t: t.to(torch.bfloat16).float()
-    m1, m2, m3 = (fused.master[s.offset:s.offset + s.numel] for s in
-                  (next(s for s in fused.layout.slots if s.name == n) for n in
-                   ("layers.0.bias", "layers.3.bias", "layers.6.bias")))
     h1 = r(torch.relu(xr @ W1.t() + m1))
     h2 = r(torch.relu(h1 @ W2.t() + m2))
     want = h2 @ W3.t() + m3
@@ -478,11 +471,13 @@ def test_fused_mlp_dropout_is_a_mask_with_the_right_rate(monkeypatch):
     assert fs is not None
     x = torch.randn(64, 784, device=dev)
     y = torch.randint(0, 10, (64,), device=dev)
-    off = (12 * 256 * 64 + 2 * 16 * 64) * 4     # h1 after activation, bf16 [256][64] (b200_mlp_scratch layout)
+    # h1 after activation as the kernel keeps it for the backward gate: bf16, [batch group of 8][feature][8]
+    off = (12 * 256 * 64 + 2 * 16 * 64) * 4
     def h1_after(train):
         fs.forward_backward(x, y, train=train)
         torch.cuda.synchronize()
-        return fs.scratch[off:off + 256 * 64 * 2].view(torch.bfloat16).view(256, 64).float().clone()
+        raw = fs.scratch[off:off + 256 * 64 * 2].view(torch.bfloat16).view(8, 256, 8)
+        return raw.permute(1, 0, 2).reshape(256, 64).float().clone()
     kept = h1_after(True)
     W1 = eng.program.layers[0]["w"].float(); b1 = eng.program.layers[0]["b"]
     full = torch.relu(x.to(torch.bfloat16).float() @ W1.t() + b1).t()          # [256, 64] without dropout
@@ -695,10 +690,14 @@ def test_host_stepper_matches_train_step(model):
     assert stepper.finish() is None               # nothing pending any more
     want = [b.train_step(hx[i].to(dev), hy[i].to(dev)).item() for i in range(steps)]
     assert len(got) == steps and a.optimizer.step_count == b.optimizer.step_count == steps
-    assert len(stepper._runners) == 1             # the native path was taken
+    if model == "simplenet":                      # the native path was taken: fused two-launch session ...
+        assert a.program.fused is not None and a.program.fused.host_ready and not stepper._runners
+    else:                                         # ... or the graph runner
+        assert len(stepper._runners) == 1
     for g, w in zip(got, want):
         assert abs(g - w) < 2e-2 * max(1.0, abs(w)), (got, want)
-    assert rel_err(a.master, b.master) < 2e-3
+    # (split-K / bias-gradient atomics make two GPT-2 runs differ in the last bits; 12 Adam steps amplify it)
+    assert rel_err(a.master, b.master) < 4e-3
     stepper.close()
 
 
