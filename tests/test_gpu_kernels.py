@@ -733,7 +733,11 @@ def test_hyperparameter_change_recaptures_the_step(model):
     for _ in range(4):
         stepper.step(hx, hy)
     assert stepper.finish() is not None
-    assert not torch.equal(eng.master, before) and len(stepper._runners) == 1
+    assert not torch.equal(eng.master, before)
+    if model == "simplenet":      # fused session (rebuilt on the lr change) or the graph runner took the steps
+        assert eng.program.fused.host_ready and not stepper._runners
+    else:
+        assert len(stepper._runners) == 1
     eng.optimizer.set_lr(0.0)
     before = eng.master.clone()
     for _ in range(4 if model == "gpt2" else 2):     # gpt2: two eager warm-up steps, capture, replay
