@@ -250,7 +250,7 @@ template <bool BF16, int ALGO, bool PUSH_BF16>
 __global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
     const CommArgs a, b200_opt_hparams hp, int64_t start, int64_t n, float* __restrict__ master,
     float* __restrict__ m, float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, int* step_dev,
-    int step_host, int advance) {
+    int step_host, int advance, const OptScalars* __restrict__ scalars) {
     constexpr int N = Vec<BF16>::N;
     __shared__ OptScalars sc;
     // Programmatic dependent launch (no-ops on an ordinary launch): become resident while the
@@ -258,9 +258,15 @@ __global__ void __launch_bounds__(256) allreduce_optimizer_kernel(
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const uint32_t epoch = *(volatile uint32_t*)(a.flags[a.rank] + F_EPOCH) + 1u;
+    // thread 0 also publishes the "ready" flag: with precomputed `scalars` (csrc/mlp_fused.cu) the
+    // two double-precision pow() of make_opt_scalars no longer sit in front of the barrier
     if (threadIdx.x == 0) {
-        const int t = step_dev ? (*(volatile int*)step_dev + 1) : step_host;
-        sc = make_opt_scalars(hp, t);
+        if (scalars) {
+            sc = *scalars;
+        } else {
+            const int t = step_dev ? (*(volatile int*)step_dev + 1) : step_host;
+            sc = make_opt_scalars(hp, t);
+        }
     }
     begin_barrier(a, epoch);  // includes __syncthreads
     const OptScalars s = sc;
@@ -456,7 +462,7 @@ static int allreduce_optimizer_impl(const b200_comm* c, int algo, const b200_opt
                                     int64_t start, int64_t n, int grad_is_bf16, float* master,
                                     float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
                                     int push_is_bf16, int* step_dev, int step_host, int advance,
-                                    void* stream, bool pdl) {
+                                    void* stream, bool pdl, const void* scalars = nullptr) {
     using namespace b200;
     CommArgs a;
     int rc = fill_args(c, &a);
@@ -483,7 +489,8 @@ static int allreduce_optimizer_impl(const b200_comm* c, int algo, const b200_opt
     __nv_bfloat16* sh = (__nv_bfloat16*)shadow_bf16;
 #define GO(BF, AL, PB)                                                                             \
     B200_CUDA_OK(cudaLaunchKernelEx(&cfg, allreduce_optimizer_kernel<BF, AL, PB>, a, h, start, n,  \
-                                    master, exp_avg, exp_avg_sq, sh, step_dev, step_host, advance))
+                                    master, exp_avg, exp_avg_sq, sh, step_dev, step_host, advance,  \
+                                    (const OptScalars*)scalars))
     if (algo == 0) { if (grad_is_bf16) GO(true, 0, false); else GO(false, 0, false); }
     else if (algo == 2) {
         if (push_is_bf16) { if (grad_is_bf16) GO(true, 2, true); else GO(false, 2, true); }
@@ -509,10 +516,10 @@ extern "C" int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200
 int b200_allreduce_optimizer_pdl(const b200_comm* c, int algo, const b200_opt_hparams* hp, int64_t start, int64_t n,
                                  int grad_is_bf16, float* master, float* exp_avg, float* exp_avg_sq,
                                  void* shadow_bf16, int push_is_bf16, int* step_dev, int step_host, int advance,
-                                 void* stream) {
+                                 const void* scalars, void* stream) {
     static const bool pdl = getenv("B200DDP_NO_PDL") == nullptr;
     return allreduce_optimizer_impl(c, algo, hp, start, n, grad_is_bf16, master, exp_avg, exp_avg_sq, shadow_bf16,
-                                    push_is_bf16, step_dev, step_host, advance, stream, pdl);
+                                    push_is_bf16, step_dev, step_host, advance, stream, pdl, scalars);
 }
 
 extern "C" int b200_allreduce(const b200_comm* c, int algo, int64_t start, int64_t n, int is_bf16,

@@ -18,15 +18,22 @@ template <bool GRAD_BF16>
 __global__ void __launch_bounds__(256) optimizer_kernel(
     b200_opt_hparams hp, float* __restrict__ p, const void* __restrict__ g_, float* __restrict__ m,
     float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, int64_t n, int* step_dev,
-    int step_host, int advance) {
+    int step_host, int advance, const OptScalars* __restrict__ scalars) {
     __shared__ OptScalars sc;
     // Programmatic dependent launch (no-ops on an ordinary launch): let the next kernel's
     // prologue start, then wait for the producer of the gradients.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    // `scalars`: bias corrections etc. of this step, precomputed by the producer kernel
+    // (csrc/mlp_fused.cu) — make_opt_scalars runs two double-precision pow(): microseconds of
+    // serial latency in front of every block's first load when done here.
     if (threadIdx.x == 0) {
-        const int t = step_dev ? (*(volatile int*)step_dev + 1) : step_host;
-        sc = make_opt_scalars(hp, t);
+        if (scalars) {
+            sc = *scalars;
+        } else {
+            const int t = step_dev ? (*(volatile int*)step_dev + 1) : step_host;
+            sc = make_opt_scalars(hp, t);
+        }
     }
     __syncthreads();
     const OptScalars s = sc;
@@ -90,7 +97,7 @@ __global__ void __launch_bounds__(256) optimizer_kernel(
 static int optimizer_step_impl(const b200_opt_hparams* hp, float* master, const void* grad,
                                int grad_is_bf16, float* exp_avg, float* exp_avg_sq,
                                void* shadow_bf16, int64_t n, int* step_dev, int step_host,
-                               int advance, void* stream, bool pdl) {
+                               int advance, void* stream, bool pdl, const void* scalars = nullptr) {
     B200_REQUIRE(hp && master && grad && exp_avg, "optimizer_step: null pointer");
     B200_REQUIRE(hp->kind >= 0 && hp->kind <= 2, "optimizer_step: unknown kind %d", hp->kind);
     B200_REQUIRE(hp->kind == 2 || exp_avg_sq, "optimizer_step: Adam needs exp_avg_sq");
@@ -118,10 +125,10 @@ static int optimizer_step_impl(const b200_opt_hparams* hp, float* master, const 
     __nv_bfloat16* sh = (__nv_bfloat16*)shadow_bf16;
     if (grad_is_bf16)
         B200_CUDA_OK(cudaLaunchKernelEx(&cfg, b200::optimizer_kernel<true>, h, master, grad, exp_avg, exp_avg_sq, sh, n,
-                                        step_dev, step_host, advance));
+                                        step_dev, step_host, advance, (const b200::OptScalars*)scalars));
     else
         B200_CUDA_OK(cudaLaunchKernelEx(&cfg, b200::optimizer_kernel<false>, h, master, grad, exp_avg, exp_avg_sq, sh, n,
-                                        step_dev, step_host, advance));
+                                        step_dev, step_host, advance, (const b200::OptScalars*)scalars));
     b200_count_launch(1);
     return 0;
 }
@@ -136,10 +143,11 @@ extern "C" int b200_optimizer_step(const b200_opt_hparams* hp, float* master, co
 
 // Launched with programmatic stream serialization: the kernel's blocks become resident while the
 // producer of the gradients is still running and start the moment it completes (csrc/mlp_fused.cu).
+// `scalars` (device, b200::OptScalars of this step) may be null.
 int b200_optimizer_step_pdl(const b200_opt_hparams* hp, float* master, const void* grad, int grad_is_bf16,
                             float* exp_avg, float* exp_avg_sq, void* shadow_bf16, int64_t n, int* step_dev,
-                            int step_host, int advance, void* stream) {
+                            int step_host, int advance, const void* scalars, void* stream) {
     static const bool pdl = getenv("B200DDP_NO_PDL") == nullptr;
     return optimizer_step_impl(hp, master, grad, grad_is_bf16, exp_avg, exp_avg_sq, shadow_bf16, n, step_dev,
-                               step_host, advance, stream, pdl);
+                               step_host, advance, stream, pdl, scalars);
 }
