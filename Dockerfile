@@ -12,6 +12,7 @@ WORKDIR /workspace
 COPY b200ddp ./b200ddp
 COPY csrc ./csrc
 COPY include ./include
+COPY oracle ./oracle
 COPY launch/entrypoint.sh train.py __graft_entry__.py ./
 
 # Compile the sm_100a kernels in-tree (b200ddp/_native/libb200ddp.so).

@@ -10,7 +10,9 @@ Every matmul (qkv, attention projection, MLP up/down, LM head) runs on the
 tcgen05 GEMM with fused epilogues (bias, GELU + pre-activation save, residual
 add, GELU-backward gate); LayerNorm and the LM-head cross-entropy are our
 kernels; gradients are written into the engine's arena by the wgrad epilogues.
-The softmax(QK^T)V core uses torch SDPA in round 1 (see ops/functional.py).
+The softmax(QK^T)V core is the fused flash-style tcgen05 kernel pair of
+``csrc/flash_attention.cu`` (``B200DDP_ATTENTION=gemm|sdpa`` select the batched-GEMM path or torch's
+library kernel for comparison, see ops/functional.py).
 """
 from __future__ import annotations
 

@@ -41,6 +41,32 @@ def resolve_backend(backend: str) -> str:
     return backend
 
 
+def pick_engine_backend(backend: str, device) -> str:
+    """Gradient-path backend of the engine for ``--backend auto`` (collective: call on every rank
+    after ``setup_distributed``).  The ``b200`` backend maps every peer's arenas through CUDA IPC /
+    NVSwitch multicast, which exists inside ONE NVSwitch domain of at most 8 GPUs; the reference's
+    own deployment (``entrypoint.sh``: REPLICAS > 1 nodes, ref ``entrypoint.sh:33-39``) spans hosts.
+    There, or beyond 8 ranks, the engine falls back to NCCL all-reduce + the fused optimizer kernel."""
+    if backend != "auto":
+        return backend
+    if torch.device(device).type != "cuda":
+        return "gloo"
+    world_size = dist.get_world_size() if dist.is_initialized() else 1
+    if world_size == 1:
+        return "b200"
+    import socket
+    from .._native.bindings_comm import MAX_RANKS
+    hosts = [None] * world_size
+    dist.all_gather_object(hosts, socket.gethostname())
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", world_size))
+    one_box = len(set(hosts)) == 1 and local_world == world_size
+    if one_box and world_size <= MAX_RANKS:
+        return "b200"
+    why = (f"{len(set(hosts))} hosts" if not one_box else f"{world_size} ranks > {MAX_RANKS}")
+    get_logger("b200ddp").info(f"backend auto -> nccl ({why}: peer-mapped arenas need one NVSwitch domain)")
+    return "nccl"
+
+
 def setup_distributed(backend: str = "auto", timeout_s: int = 600) -> Tuple[int, int, int]:
     """Joins the env:// rendezvous.  Returns ``(rank, world_size, local_rank)``.
 

@@ -25,7 +25,7 @@ from .checkpoint import load_checkpoint, save_checkpoint
 from .cli import parse_args
 from .data import SyntheticDataset, create_data_loader
 from .parallel.engine import DataParallel
-from .parallel.process_group import cleanup_distributed, get_device, setup_distributed
+from .parallel.process_group import cleanup_distributed, get_device, pick_engine_backend, setup_distributed
 from .utils.logging import configure_logging, get_logger
 from .utils.profiling import nvtx_range
 
@@ -152,9 +152,10 @@ def main(argv=None) -> int:
     dtype = _DTYPES[args.dtype] if args.dtype else (
         torch.bfloat16 if device.type == "cuda" else torch.float32)
     wire = _DTYPES[args.wire_dtype] if args.wire_dtype else None
-    backend = args.backend
-    if backend == "auto":
-        backend = "b200" if device.type == "cuda" else "gloo"
+    backend = pick_engine_backend(args.backend, device)
+    if args.profile:      # NVTX ranges around every step phase (nsys / ncu --nvtx pick them up)
+        from .utils.profiling import enable_nvtx
+        enable_nvtx(True)
 
     model = build_model(args, device)
     engine = DataParallel(

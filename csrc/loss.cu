@@ -63,6 +63,13 @@ __global__ void __launch_bounds__(256) ce_kernel(const void* __restrict__ logits
     for (int64_t row = (int64_t)blockIdx.x * TEAMS + team; row < rows;
          row += (int64_t)gridDim.x * TEAMS) {
         const int64_t base = row * ld;
+        // Target logit first: dlogits may alias logits, and another warp of the team may already be
+        // writing this row's gradient when lane 0 gets to the loss term (every thread of the team
+        // passes the merge barrier below before the first write).  A target outside [0, classes)
+        // (e.g. an ignore index) reads nothing, adds no loss and gets no -1.
+        const int tgt_raw = (int)targets[row];
+        const bool tgt_ok = tgt_raw >= 0 && tgt_raw < classes;
+        const float x_tgt = tgt_ok ? ld_logit<BF16>(logits, base + tgt_raw) : 0.f;
         RowStat st{-INFINITY, 0.f, 0x7fffffff};
         for (int c = lane; c < classes; c += TEAM) {
             const float x = ld_logit<BF16>(logits, base + c);
@@ -90,12 +97,13 @@ __global__ void __launch_bounds__(256) ce_kernel(const void* __restrict__ logits
             for (int w = 1; w < 8; ++w) st = merge(st, s_stat[w]);
             __syncthreads();
         }
-        const int tgt = (int)targets[row];
+        const int tgt = tgt_ok ? tgt_raw : -1;
         const float lse = st.mx + __logf(st.sum);
-        if (lane == 0) {
-            acc_loss += lse - ld_logit<BF16>(logits, base + tgt);
+        if (lane == 0 && tgt_ok) {
+            acc_loss += lse - x_tgt;
             acc_ok += (st.arg == tgt) ? 1.f : 0.f;
         }
+        if (TEAM <= 32) __syncwarp();
         if (dlogits) {
             const float inv = 1.f / st.sum;
             for (int c = lane; c < classes; c += TEAM) {
@@ -166,9 +174,11 @@ __global__ void __launch_bounds__(256) ce_row_vec_kernel(const __nv_bfloat16* lo
     for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
         const __nv_bfloat16* src = logits + row * ld;
         const uint4* src4 = reinterpret_cast<const uint4*>(src);
-        const int tgt = (int)targets[row];
+        const int tgt_raw = (int)targets[row];
+        const bool tgt_ok = tgt_raw >= 0 && tgt_raw < classes;   // out of range (ignore index): no loss, no -1
+        const int tgt = tgt_ok ? tgt_raw : -1;
         // read before anything of this row is overwritten (dlogits may alias logits)
-        const float x_tgt = lane == 0 ? __bfloat162float(src[tgt]) : 0.f;
+        const float x_tgt = (lane == 0 && tgt_ok) ? __bfloat162float(src[tgt]) : 0.f;
         RowStat st{-INFINITY, 0.f, 0x7fffffff};
         for (int v = lane; v < nvec; v += 256) {
             float x[8];
@@ -201,7 +211,7 @@ __global__ void __launch_bounds__(256) ce_row_vec_kernel(const __nv_bfloat16* lo
 #pragma unroll
         for (int w = 1; w < 8; ++w) st = merge(st, s_stat[w]);
         __syncthreads();
-        if (lane == 0) {
+        if (lane == 0 && tgt_ok) {
             acc_loss += st.mx + __logf(st.sum) - x_tgt;
             acc_ok += (st.arg == tgt) ? 1.f : 0.f;
         }

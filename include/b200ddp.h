@@ -61,7 +61,9 @@ int b200_optimizer_step(const b200_opt_hparams* hp, float* master, const void* g
  * it at train.py:138; torch: log_softmax + nll_loss + their two backward ops.
  * logits [rows, ld] (bf16 when logits_bf16 else fp32), targets int64.
  * dlogits (same dtype/ld as logits, may alias logits, may be null) receives
- * (softmax - onehot) * grad_scale.  loss_out[0] = mean loss, loss_out[1] =
+ * (softmax - onehot) * grad_scale.  A target outside [0, classes) — e.g. an
+ * ignore index of -100 — is never dereferenced: its row adds no loss and gets
+ * plain softmax * grad_scale; the mean still divides by `rows`.  loss_out[0] = mean loss, loss_out[1] =
  * number of rows whose argmax equals the target (as float).  `scratch` holds
  * per-block partials and a ticket: b200_ce_scratch_bytes(rows) bytes, zeroed
  * once at allocation (the kernel leaves the ticket at zero). */
@@ -70,8 +72,11 @@ int b200_cross_entropy(const void* logits, int logits_bf16, int64_t ld, const in
                        int64_t rows, int classes, void* dlogits, float grad_scale, float* loss_out,
                        void* scratch, void* stream);
 
-/* Same computation and same results as b200_cross_entropy, for callers that
- * must not allocate.  (No counterpart in the reference: it has no native code
+/* Same inputs, outputs and results as b200_cross_entropy, for callers that
+ * must not allocate.  (The numbers agree within the tests' tolerance, the code
+ * that produces them can differ: for bf16 rows with more than 2048 classes
+ * b200_cross_entropy runs its vectorised row kernel, this entry always runs the
+ * generic team-per-row kernel.)  (No counterpart in the reference: it has no native code
  * and no allocation-free path; this exists for embedders of this library.)
  *
  * Meant for code that lives inside another component's memory budget — a plugin
@@ -91,7 +96,10 @@ int b200_cross_entropy(const void* logits, int logits_bf16, int64_t ld, const in
  *
  * The first call on each device looks the array's device address up
  * (cudaGetSymbolAddress, with that device current); make that first call
- * before starting any stream capture.
+ * before starting any stream capture.  The address is cached per device
+ * ordinal for the life of the process: after a cudaDeviceReset the cached
+ * value is stale, so a process that resets a device must not call this again
+ * on it.
  *
  * All calls on a device share the one array, and it keeps the previous call's
  * contents; each call re-zeroes the word that has to start at zero (an async

@@ -142,6 +142,34 @@ def test_cross_entropy_kernel(B, rows, classes, dtype):
     assert rel_err(dl, ref_in.grad) < tol
 
 
+@pytest.mark.parametrize("rows,classes,dtype", [(257, 10, torch.float32), (129, 1000, torch.bfloat16),
+                                                (33, 3000, torch.float32)])
+def test_cross_entropy_in_place_and_ignored_targets(B, rows, classes, dtype):
+    """dlogits aliasing logits on the generic kernel (warp- and block-per-row teams): the loss term
+    must be read before the row is overwritten.  Targets outside [0, classes) are never
+    dereferenced: no loss, plain softmax gradient, mean over all rows."""
+    torch.manual_seed(2)
+    dev = torch.device("cuda")
+    logits = (torch.randn(rows, classes, device=dev) * 3).to(dtype)
+    tgt = torch.randint(0, classes, (rows,), device=dev)
+    tgt[3], tgt[rows - 1] = -100, classes + 5
+    valid = (tgt >= 0) & (tgt < classes)
+    ref_in = logits.float().requires_grad_(True)
+    per_row = F.cross_entropy(ref_in[valid], tgt[valid], reduction="sum") / rows
+    sm = torch.softmax(logits.float(), 1)
+    want_grad = sm.clone()
+    want_grad[valid, tgt[valid]] -= 1.0
+    want_grad /= rows
+    want_ok = (logits.float().argmax(1)[valid] == tgt[valid]).sum().item()
+    work = logits.clone()
+    out = torch.zeros(2, device=dev)
+    B.cross_entropy(work, tgt, work, 1.0 / rows, out)        # in place
+    torch.cuda.synchronize()
+    assert abs(out[0].item() - per_row.item()) < 2e-4 * max(1.0, abs(per_row.item()))
+    assert out[1].item() == want_ok
+    assert rel_err(work, want_grad) < (1e-5 if dtype == torch.float32 else 1e-2)
+
+
 @pytest.mark.parametrize("rows,inplace", [(37, False), (700, True)])
 def test_cross_entropy_vectorised_rows(B, rows, inplace):
     """LM-head shape: 50257 classes in rows padded to 50264 (16-byte aligned) take the 16-byte
