@@ -84,6 +84,12 @@ class MlpDesc(C.Structure):
 
 
 def declare(L: C.CDLL) -> None:
+    L.b200_embedding_fwd.argtypes = [C.c_void_p] * 4 + [C.c_int64, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    L.b200_embedding_bwd.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int,
+                                     C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    L.b200_embedding_scratch_bytes.argtypes = [C.c_int64]
+    L.b200_embedding_scratch_bytes.restype = C.c_int64
+    L.b200_embedding_fwd.restype = L.b200_embedding_bwd.restype = C.c_int
     L.b200_mlp_scratch_bytes.restype = C.c_int64
     L.b200_mlp_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(MlpDesc)]
     L.b200_mlp_destroy.argtypes = [C.c_void_p]
@@ -216,6 +222,42 @@ def cross_entropy(logits: torch.Tensor, targets: torch.Tensor, dlogits: Optional
         targets.data_ptr(), logits.shape[0], logits.shape[1], _ptr(dlogits), grad_scale,
         loss_out.data_ptr(), ce_scratch(logits.device).data_ptr(), stream_ptr(logits.device)),
         "b200_cross_entropy")
+
+
+# ------------------------------------------------------------------ embedding
+_emb_scratch = {}
+
+
+def embedding_fwd(idx: torch.Tensor, wte: torch.Tensor, wpe: torch.Tensor) -> torch.Tensor:
+    """x[b, t] = wte[idx[b, t]] + wpe[t]  (bf16 tables, int64 ids [B, T])."""
+    assert idx.dtype == torch.int64 and idx.dim() == 2 and idx.is_contiguous()
+    assert wte.dtype == torch.bfloat16 and wpe.dtype == torch.bfloat16 and wte.is_contiguous() and wpe.is_contiguous()
+    Bsz, T = idx.shape
+    V, Cc = wte.shape
+    out = torch.empty(Bsz, T, Cc, dtype=torch.bfloat16, device=wte.device)
+    check(lib().b200_embedding_fwd(idx.data_ptr(), wte.data_ptr(), wpe.data_ptr(), out.data_ptr(), Bsz * T, T, Cc,
+                                   V, stream_ptr(wte.device)), "b200_embedding_fwd")
+    return out
+
+
+def embedding_bwd(idx: torch.Tensor, dx: torch.Tensor, g_wte: Optional[torch.Tensor],
+                  g_wpe: Optional[torch.Tensor], V: int) -> None:
+    """g_wte[v] += sum of dx over tokens with id v (deterministic); g_wpe[t] = sum_b dx[b, t]."""
+    Bsz, T = idx.shape
+    Cc = dx.shape[-1]
+    assert dx.dtype == torch.bfloat16 and dx.is_contiguous() and idx.is_contiguous()
+    for g in (g_wte, g_wpe):
+        assert g is None or (g.is_contiguous() and g.dtype in (torch.bfloat16, torch.float32))
+    key = (torch.device(dx.device).index, Bsz * T)
+    sc = _emb_scratch.get(key)
+    if sc is None:
+        sc = _emb_scratch[key] = torch.empty(int(lib().b200_embedding_scratch_bytes(Bsz * T)), dtype=torch.uint8,
+                                             device=dx.device)
+    check(lib().b200_embedding_bwd(
+        idx.data_ptr(), dx.data_ptr(), _ptr(g_wte), int(g_wte is not None and g_wte.dtype == torch.bfloat16),
+        _ptr(g_wpe), int(g_wpe is not None and g_wpe.dtype == torch.bfloat16), Bsz, T,
+        g_wpe.shape[0] if g_wpe is not None else T, Cc, V, sc.data_ptr(), stream_ptr(dx.device)),
+        "b200_embedding_bwd")
 
 
 # ------------------------------------------------------------------ GEMM

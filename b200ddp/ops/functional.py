@@ -369,27 +369,31 @@ def lm_head_cross_entropy(x, w, targets, signal_weight: bool = True):
 
 # ------------------------------------------------------------------ embedding (tied with the head)
 class _Embedding(torch.autograd.Function):
+    """Token + position embedding on our kernels (csrc/embedding.cu): a gather forward and a
+    deterministic (sorted, atomic-free) scatter-add backward that lands on top of the tied LM-head
+    gradient already in the arena."""
+
     @staticmethod
     def forward(ctx, idx, wte, wpe):
-        Bsz, T = idx.shape
-        x = wte[idx] + wpe[:T].unsqueeze(0)
+        idx = idx.contiguous()
+        x = _B().embedding_fwd(idx, wte, wpe)
         ctx.save_for_backward(idx)
         ctx.wte, ctx.wpe = wte, wpe
         return x
 
     @staticmethod
     def backward(ctx, dx):
+        B = _B()
         (idx,) = ctx.saved_tensors
         wte, wpe = ctx.wte, ctx.wpe
-        Bsz, T = idx.shape
-        Cc = dx.shape[-1]
+        V = wte.shape[0]
+        dx = dx.contiguous()
 
         def wte_grad(dst):  # accumulates on top of the LM-head contribution already in the arena
-            dst.index_add_(0, idx.reshape(-1), dx.reshape(-1, Cc).to(dst.dtype))
+            B.embedding_bwd(idx, dx, dst, None, V)
 
         def wpe_grad(dst):
-            dst.zero_()
-            dst[:T] = dx.float().sum(0).to(dst.dtype)
+            B.embedding_bwd(idx, dx, None, dst, V)
 
         owned = getattr(wte, "_b200_grad", None) is not None
         if owned:

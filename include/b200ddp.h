@@ -330,6 +330,21 @@ int b200_allreduce_optimizer(const b200_comm* c, int algo, const b200_opt_hparam
 int b200_allreduce(const b200_comm* c, int algo, int64_t start, int64_t n, int is_bf16, void* out,
                    float scale, void* stream);
 
+/* ---------------------------------------------------------------- embedding (GPT-2, BASELINE.json config 4)
+ * forward: out[b, t, :] = wte[idx[b, t], :] + wpe[t, :] (bf16, C % 8 == 0; ids are clamped to [0, V)).
+ * backward: g_wte[v, :] += sum of dx over the tokens with id v — on top of what is already there (the
+ * tied LM-head gradient) — and g_wpe[t, :] = sum_b dx[b, t, :] (rows T..wpe_rows-1 zeroed).  Either
+ * gradient pointer may be null; each is bf16 or fp32 per its flag.  Deterministic: ids are sorted
+ * on the device and every row is summed in position order, no atomics.  `scratch`:
+ * b200_embedding_scratch_bytes(B*T) bytes, any contents.
+ * ref: train.py:136,138 at GPT-2 scale; torch: aten::embedding / embedding_dense_backward. */
+int b200_embedding_fwd(const int64_t* idx, const void* wte, const void* wpe, void* out, int64_t tokens,
+                       int T, int C, int V, void* stream);
+int64_t b200_embedding_scratch_bytes(int64_t tokens);
+int b200_embedding_bwd(const int64_t* idx, const void* dx, void* g_wte, int g_wte_bf16, void* g_wpe,
+                       int g_wpe_bf16, int Bsz, int T, int wpe_rows, int C, int V, void* scratch,
+                       void* stream);
+
 /* ---------------------------------------------------------------- fused MLP training step
  * The reference's model (ref train.py:32-50: 784-256-256-10 with ReLU + dropout) and its step
  * (ref train.py:135-139: zero_grad, forward, criterion, backward, optimizer.step) as TWO launches:

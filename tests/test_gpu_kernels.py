@@ -683,6 +683,39 @@ def test_whole_step_cuda_graph_matches_eager(model):
         assert rel_err(bg.float(), be.float()) < 5e-2
 
 
+@pytest.mark.parametrize("Bsz,T,V,C,dst_dtype", [(8, 1024, 50257, 768, torch.bfloat16), (3, 37, 101, 64, torch.float32),
+                                                  (20, 1024, 512, 128, torch.float32)])
+def test_embedding_gather_and_deterministic_scatter_add(B, Bsz, T, V, C, dst_dtype):
+    """csrc/embedding.cu vs fp32 torch: gather + position add forward; the backward adds the token
+    gradients ON TOP of what the row already holds (tied LM head) in a fixed order — two runs are
+    bit-identical — and handles more tokens than one sort segment (20 x 1024 > 16384)."""
+    torch.manual_seed(9)
+    dev = torch.device("cuda")
+    wte = bf(torch.randn(V, C, device=dev))
+    wpe = bf(torch.randn(T + 5, C, device=dev))
+    idx = torch.randint(0, V, (Bsz, T), device=dev)
+    idx[0, :7] = 3                                  # a run of repeated ids
+    x = B.embedding_fwd(idx, wte, wpe)
+    want = wte.float()[idx] + wpe.float()[:T].unsqueeze(0)
+    assert torch.equal(x, bf(want))
+    dx = bf(torch.randn(Bsz, T, C, device=dev))
+    prior = torch.randn(V, C, device=dev).to(dst_dtype)
+    outs = []
+    for _ in range(2):
+        g_wte = prior.clone()
+        g_wpe = torch.full((T + 5, C), 7.0, device=dev).to(dst_dtype)
+        B.embedding_bwd(idx, dx, g_wte, None, V)
+        B.embedding_bwd(idx, dx, None, g_wpe, V)
+        outs.append((g_wte, g_wpe))
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    ref = prior.float().index_add(0, idx.reshape(-1), dx.float().reshape(-1, C))
+    tol = 1e-2 if dst_dtype == torch.bfloat16 else 1e-5
+    assert rel_err(outs[0][0], ref) < tol
+    assert rel_err(outs[0][1][:T], dx.float().sum(0)) < tol
+    assert torch.count_nonzero(outs[0][1][T:]) == 0
+
+
 @pytest.mark.parametrize("model", ["simplenet", "gpt2"])
 def test_host_stepper_matches_train_step(model):
     """The native end-to-end runner (pinned host batch in, float loss out, one C call per step)
