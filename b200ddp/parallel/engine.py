@@ -41,6 +41,7 @@ from .buckets import ArenaLayout, Bucket, MiB, build_layout
 from .process_group import world
 
 logger = get_logger("b200ddp")
+_SYMM_DTYPES = (torch.float32, torch.bfloat16, torch.int32, torch.uint8, torch.int64)
 
 
 def _native():
@@ -174,7 +175,9 @@ class DataParallel(nn.Module):
         for b in module.buffers():
             by_dtype.setdefault(b.dtype, []).append(b)
         for dtype, group in by_dtype.items():
-            flat = torch.zeros(sum(b.numel() for b in group), dtype=dtype, device=self.device)
+            # peer-mapped on the b200 backend: the per-forward broadcast (K4) is then one kernel of
+            # ours inside the step graph (multimem.st through the switch) instead of an NCCL call
+            flat = self._alloc(sum(b.numel() for b in group), dtype, peer=dtype in _SYMM_DTYPES)
             off = 0
             for b in group:
                 flat[off:off + b.numel()].copy_(b.detach().reshape(-1))
@@ -253,15 +256,25 @@ class DataParallel(nn.Module):
             self.shadow.copy_(self.master)
         self._sync_buffers()
 
+    @property
+    def _buffers_in_graph(self) -> bool:
+        """True when every buffer arena is peer-mapped: the K4 broadcast is then our kernel and is
+        captured with the step."""
+        return self.symm is not None and all(hasattr(f, "_b200_peers") for f in self._buffer_arenas)
+
     def _sync_buffers(self) -> None:
         if self.world_size == 1:
             return
         for flat in self._buffer_arenas:  # buffers are views of these (see __init__)
-            dist.broadcast(flat, src=0)
+            if self.symm is not None and hasattr(flat, "_b200_peers"):
+                self.symm.broadcast_(flat, root=0)
+            else:
+                dist.broadcast(flat, src=0)
 
     # ------------------------------------------------------------------ nn.Module
     def forward(self, *args, **kwargs):
-        if self.training and self.broadcast_buffers and torch.is_grad_enabled() and not self._capturing:
+        if self.training and self.broadcast_buffers and torch.is_grad_enabled() and (
+                not self._capturing or self._buffers_in_graph):
             self._sync_buffers()
         if self.compute_dtype != torch.float32:
             args = tuple(a.to(self.compute_dtype) if torch.is_tensor(a) and a.dtype == torch.float32
@@ -357,8 +370,8 @@ class DataParallel(nn.Module):
         if not self._dev_step_synced:   # eager steps advance the host counter only
             opt.step_dev[0] = opt.step_count
             self._dev_step_synced = True
-        if self.training and self.broadcast_buffers:
-            self._sync_buffers()   # SURVEY K4, outside the graph (NCCL plumbing)
+        if self.training and self.broadcast_buffers and not self._buffers_in_graph:
+            self._sync_buffers()   # SURVEY K4 over NCCL stays outside the graph; our kernel is captured in it
         st.x.copy_(data, non_blocking=True)
         st.y.copy_(target, non_blocking=True)
         st.graph.replay()

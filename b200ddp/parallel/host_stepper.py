@@ -113,8 +113,8 @@ class HostStepper:
             if not eng._dev_step_synced:     # eager steps advance the host counter only
                 opt.step_dev[0] = opt.step_count
                 eng._dev_step_synced = True
-            if eng.training and eng.broadcast_buffers:
-                eng._sync_buffers()          # SURVEY K4 (NCCL plumbing, outside the graph)
+            if eng.training and eng.broadcast_buffers and not eng._buffers_in_graph:
+                eng._sync_buffers()          # SURVEY K4 over NCCL (our broadcast kernel is inside the graph)
         same = self._live == runner
         nat.check(nat.lib().b200_runner_step(runner, hx.data_ptr(), hy.data_ptr(), C.byref(self._prev),
                                              C.byref(self._valid)), "b200_runner_step")

@@ -25,7 +25,7 @@ from .._native import bindings
 from .._native.bindings_comm import FLAG_WORDS, MAX_RANKS, Comm
 
 _DT = {torch.float32: ("<f4", 4), torch.bfloat16: ("<u2", 2), torch.int32: ("<i4", 4),
-       torch.uint8: ("|u1", 1)}
+       torch.uint8: ("|u1", 1), torch.int64: ("<i8", 8)}
 
 # One-shot makes every rank pull the whole bucket from its W-1 peers; it is used while that
 # remote traffic, bucket_bytes * (W - 1), stays at or below this many bytes (latency path).
@@ -47,9 +47,74 @@ def _wrap(ptr: int, n: int, dtype: torch.dtype, device: torch.device) -> torch.T
     return t.view(dtype) if t.dtype != dtype else t
 
 
+class _FdExchange:
+    """All-to-all hand-over of POSIX file descriptors between the ranks of one host: every rank
+    listens on an abstract AF_UNIX socket and passes descriptors with SCM_RIGHTS
+    (``socket.send_fds``).  Host plumbing only — what the descriptors stand for (VMM allocations,
+    the multicast object) is created and mapped by ``csrc/vmm.cu``."""
+
+    def __init__(self, rank: int, world: int, group=None):
+        import secrets
+        import socket
+        self.rank, self.world, self.group = rank, world, group
+        token = [secrets.token_hex(8) if rank == 0 else None]
+        dist.broadcast_object_list(token, src=0, group=group)
+        self.prefix = f"\0b200ddp-{token[0]}-"
+        self.server = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        self.server.bind(self.prefix + str(rank))
+        self.server.listen(world + 1)
+        self._barrier()
+
+    def _barrier(self) -> None:
+        got = [None] * self.world
+        dist.all_gather_object(got, self.rank, group=self.group)
+
+    def all_gather(self, fd: Optional[int]) -> List[Optional[int]]:
+        """Every rank offers one descriptor (or None); returns what each rank offered, as
+        descriptors valid in THIS process (own entry: the descriptor passed in)."""
+        import socket
+        import struct
+        clients = {}
+        for r in range(self.world):
+            if r == self.rank:
+                continue
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            c.connect(self.prefix + str(r))         # completes against the listener's backlog
+            c.sendall(struct.pack("i", self.rank))
+            clients[r] = c
+        for _ in range(self.world - 1):             # serve every peer's request for our descriptor
+            conn, _ = self.server.accept()
+            conn.recv(4, socket.MSG_WAITALL)
+            if fd is None:
+                conn.sendall(b"n")
+            else:
+                socket.send_fds(conn, [b"f"], [fd])
+            conn.close()
+        out: List[Optional[int]] = [None] * self.world
+        out[self.rank] = fd
+        for r, c in clients.items():
+            msg, fds, _, _ = socket.recv_fds(c, 1, 1)
+            out[r] = fds[0] if (msg == b"f" and fds) else None
+            c.close()
+        self._barrier()
+        return out
+
+    def close(self) -> None:
+        self.server.close()
+
+
 class SymmetricArena:
     """Collective allocator of peer-mapped buffers.  ``alloc`` must be called by every rank
-    with the same arguments in the same order."""
+    with the same arguments in the same order.
+
+    Two allocators, both in the native library:
+      vmm   ``cuMemCreate`` allocations exported as file descriptors, mapped by every peer, and bound
+            to one NVSwitch multicast object (``cuMulticastCreate`` / ``AddDevice`` / ``BindMem``):
+            every buffer then has per-peer addresses AND a multicast address for the NVLS kernels
+            (``csrc/vmm.cu``).  Default when the driver offers it.
+      ipc   ``cudaMalloc`` + CUDA IPC handles (``csrc/comm.cu``): peer addresses only.
+    ``B200DDP_SYMM=ipc`` forces the second, ``B200DDP_NVLS=0`` keeps VMM but skips multicast,
+    ``B200DDP_NVLS=1`` makes a missing multicast an error."""
 
     def __init__(self, device: torch.device, rank: int, world: int, group=None):
         if world > MAX_RANKS:
@@ -58,46 +123,128 @@ class SymmetricArena:
         self.rank, self.world, self.group = rank, world, group
         self.L = nat.lib()
         self._segments: List[Dict] = []
-        self.flags_local, self.flags_peers = self._alloc_raw(FLAG_WORDS * 4)
         self.timeout_ms = int(os.environ.get("B200DDP_PEER_TIMEOUT_MS", "30000"))
         self.two_shot_buckets = set()
         self.vec_elems = 4
         self._comm_cache: Dict = {}
-        # NVLS: allocate from multicast-capable memory when the fabric offers it.
-        # B200DDP_NVLS=0 disables, =1 requires, default (auto) falls back to CUDA IPC.
         self.nvls_mode = os.environ.get("B200DDP_NVLS", "auto")
         self.nvls = False
-        if self.nvls_mode != "0" and world > 1:
-            self.nvls = self._probe_multicast()
-            if self.nvls_mode == "1" and not self.nvls:
-                raise RuntimeError("B200DDP_NVLS=1 but NVSwitch multicast memory is unavailable")
+        self.vmm = False
+        self._fds: Optional[_FdExchange] = None
+        self._nvls_error = "disabled"
+        if world > 1 and os.environ.get("B200DDP_SYMM", "vmm") != "ipc":
+            self._probe_vmm()
+        if self.nvls_mode == "1" and world > 1 and not self.nvls:
+            raise RuntimeError(f"B200DDP_NVLS=1 but NVSwitch multicast memory is unavailable: {self._nvls_error}")
+        self.flags_local, self.flags_peers, _ = self._alloc_raw(FLAG_WORDS * 4, multicast=False)
 
-    # ------------------------------------------------------------------ multicast arena
-    def _probe_multicast(self) -> bool:
-        try:
-            t = self._alloc_mc(1024, torch.float32)
-            ok = bool(getattr(t, "_b200_mc", 0))
-        except Exception as e:  # no fabric / old driver / container without the capability
-            ok, self._nvls_error = False, repr(e)
+    # ------------------------------------------------------------------ VMM + multicast allocator
+    def _vote(self, ok: bool) -> bool:
         votes = [None] * self.world
-        dist.all_gather_object(votes, ok, group=self.group)
+        dist.all_gather_object(votes, bool(ok), group=self.group)
         return all(votes)
 
-    def _alloc_mc(self, n: int, dtype: torch.dtype) -> torch.Tensor:
-        """Multicast-capable symmetric allocation.  The VMM allocation, handle exchange and
-        multicast binding are torch's CUDASymmetricMemory (bootstrap plumbing); what runs on
-        the addresses it returns — multimem.ld_reduce / multimem.st — is ours (comm.cu)."""
-        import torch.distributed._symmetric_memory as sm
-        t = sm.empty(n, dtype=dtype, device=self.device)
-        hdl = sm.rendezvous(t, self.group if self.group is not None else dist.group.WORLD)
-        t.zero_()
-        t._b200_peers = [int(p) for p in hdl.buffer_ptrs]  # type: ignore[attr-defined]
-        t._b200_mc = int(hdl.multicast_ptr or 0)           # type: ignore[attr-defined]
-        t._b200_hdl = hdl                                   # keep the mapping alive
-        return t
+    def _probe_vmm(self) -> None:
+        """Decides, identically on every rank, whether the VMM allocator and the multicast object
+        work here (driver entry points, fd passing between the processes, the fabric)."""
+        sup = (C.c_int * 2)()
+        ok = self.L.b200_vmm_support(sup) == 0 and bool(sup[0])
+        if not self._vote(ok):
+            return
+        try:
+            self._fds = _FdExchange(self.rank, self.world, self.group)
+            err = None
+        except Exception as e:  # noqa: BLE001 - no AF_UNIX abstract sockets in this sandbox
+            err = repr(e)
+        if not self._vote(err is None):
+            self._fds = None
+            return
+        self.vmm = True
+        want_mc = self.nvls_mode != "0" and bool(sup[1])
+        if not self._vote(want_mc):
+            self._nvls_error = "device attribute MULTICAST_SUPPORTED is 0" if self.nvls_mode != "0" else "disabled"
+            return
+        try:                     # a small trial allocation: creation / binding can still be refused
+            self._alloc_vmm(4096, multicast=True, trial=True)
+            err = None
+        except Exception as e:  # noqa: BLE001
+            err = repr(e)
+        if self._vote(err is None):
+            self.nvls = True
+        else:
+            self._nvls_error = err or "refused on another rank"
 
-    def _alloc_raw(self, nbytes: int):
+    def _agree(self, rc: int, what: str) -> None:
+        """Collective error check: every rank raises when the step failed on ANY rank, so nobody
+        is left waiting in the next exchange."""
+        msg = None
+        if rc != 0:
+            e = self.L.b200_last_error()
+            msg = f"{what} failed on rank {self.rank} (code {rc}): {e.decode() if e else '?'}"
+        errs = [None] * self.world
+        dist.all_gather_object(errs, msg, group=self.group)
+        bad = [e for e in errs if e]
+        if bad:
+            raise RuntimeError(bad[0])
+
+    def _alloc_vmm(self, nbytes: int, multicast: bool, trial: bool = False):
+        L, W = self.L, self.world
+        padded = C.c_int64()
+        self._agree(L.b200_vmm_padded_size(nbytes, W if multicast else 1, C.byref(padded)), "b200_vmm_padded_size")
+        size = padded.value
+        mapping, ptr, fd = C.c_void_p(), C.c_void_p(), C.c_int(-1)
+        rc = L.b200_vmm_create(size, C.byref(mapping), C.byref(ptr))
+        if rc == 0:
+            rc = L.b200_vmm_export(mapping, C.byref(fd))
+        self._agree(rc, "b200_vmm_create/export")
+        fds = self._fds.all_gather(fd.value)
+        peers, maps, rc = [], [mapping], 0
+        for r in range(W):
+            if r == self.rank:
+                peers.append(ptr.value)
+                continue
+            pm, pp = C.c_void_p(), C.c_void_p()
+            if rc == 0:
+                rc = L.b200_vmm_import(fds[r], size, C.byref(pm), C.byref(pp))
+                maps.append(pm)
+            L.b200_close_fd(fds[r])
+            peers.append(pp.value)
+        L.b200_close_fd(fd.value)
+        self._agree(rc, "b200_vmm_import")
+        mc_ptr = 0
+        if multicast:
+            mc, mfd, rc = C.c_void_p(), None, 0
+            if self.rank == 0:
+                rc = L.b200_mc_create(size, W, C.byref(mc))
+                if rc == 0:
+                    f = C.c_int(-1)
+                    rc = L.b200_vmm_export(mc, C.byref(f))
+                    mfd = f.value if rc == 0 else None
+            self._agree(rc, "b200_mc_create")
+            got = self._fds.all_gather(mfd)
+            if self.rank != 0:
+                rc = L.b200_mc_import(got[0], size, C.byref(mc))
+            L.b200_close_fd(got[0])
+            if rc == 0:
+                rc = L.b200_mc_add_device(mc)
+            self._agree(rc, "b200_mc_import/add_device")     # also: every device added before anyone binds
+            p = C.c_void_p()
+            self._agree(L.b200_mc_bind_map(mc, mapping, C.byref(p)), "b200_mc_bind_map")
+            mc_ptr = p.value
+            maps.append(mc)
+        if trial:
+            torch.cuda.synchronize(self.device)
+            for m in reversed(maps):
+                L.b200_vmm_release(m)
+            return 0, [], 0
+        self._segments.append({"local": ptr.value, "peers": peers, "bytes": size, "mc": mc_ptr, "maps": maps})
+        return ptr.value, peers, mc_ptr
+
+    def _alloc_raw(self, nbytes: int, multicast: bool = True):
+        """(local pointer, per-rank pointers, multicast pointer or 0) of a zero-filled symmetric buffer."""
         nbytes = (nbytes + 255) // 256 * 256
+        if self.vmm:
+            return self._alloc_vmm(nbytes, multicast=multicast and self.nvls)
         ptr = C.c_void_p()
         handle = (C.c_char * 64)()
         nat.check(self.L.b200_symm_alloc(nbytes, C.byref(ptr), handle), "b200_symm_alloc")
@@ -112,17 +259,16 @@ class SymmetricArena:
                 buf = (C.c_char * 64).from_buffer_copy(h)
                 nat.check(self.L.b200_symm_open(buf, C.byref(p)), f"b200_symm_open(rank {r})")
                 peers.append(p.value)
-        self._segments.append({"local": ptr.value, "peers": peers, "bytes": nbytes})
-        return ptr.value, peers
+        self._segments.append({"local": ptr.value, "peers": peers, "bytes": nbytes, "mc": 0})
+        return ptr.value, peers, 0
 
     def alloc(self, n: int, dtype: torch.dtype) -> torch.Tensor:
-        if self.nvls:
-            torch.cuda.synchronize(self.device)
-            return self._alloc_mc(n, dtype)
         _, esize = _DT[dtype]
-        local, peers = self._alloc_raw(n * esize)
+        torch.cuda.synchronize(self.device)
+        local, peers, mc = self._alloc_raw(n * esize)
         t = _wrap(local, n, dtype, self.device)
         t._b200_peers = peers  # type: ignore[attr-defined]
+        t._b200_mc = mc        # type: ignore[attr-defined]
         return t
 
     def comm(self, grad: torch.Tensor, push: Optional[torch.Tensor] = None, *,
@@ -209,6 +355,17 @@ class SymmetricArena:
         for k, b in enumerate(engine.layout.buckets):
             self.launch_bucket(engine, b, scale, step_host=engine.optimizer.step_count,
                                device_step=device_step, advance=device_step and k == nb - 1)
+
+    def broadcast_(self, t: torch.Tensor, root: int = 0) -> None:
+        """Replicates rank `root`'s symmetric buffer `t` into every rank's copy: one kernel per
+        rank, multimem.st through the switch when `t` has a multicast mapping."""
+        key = ("bcast", t.data_ptr())
+        c = self._comm_cache.get(key)
+        if c is None:
+            c = self._comm_cache[key] = self.comm(t, t)
+        nbytes = (t.numel() * t.element_size() + 15) // 16 * 16     # allocations are padded to 256 bytes
+        nat.check(self.L.b200_broadcast(C.byref(c), root, 0, nbytes, nat.stream_ptr(self.device)),
+                  "b200_broadcast")
 
     def allreduce_(self, t: torch.Tensor, start: int, n: int, *, algo: int, scale: float = 1.0,
                    out: Optional[torch.Tensor] = None) -> None:

@@ -390,6 +390,30 @@ __global__ void __launch_bounds__(256) allreduce_kernel(const CommArgs a, int64_
     end_barrier<ALGO >= 1>(a, epoch, nullptr, 0, true);
 }
 
+// Rank `root` replicates [off, off + nvec) 16-byte vectors of its `push` arena into every rank's
+// (DDP's per-forward buffer broadcast, SURVEY K4: ref train.py:136 -> torch _sync_buffers).  Entry
+// barrier: nobody is still reading the old values; exit barrier: the new ones have landed.
+// One multimem.st per vector when the arena has a multicast mapping, else one store per peer.
+__global__ void __launch_bounds__(256) broadcast_kernel(const CommArgs a, int root, int64_t off, int64_t nvec) {
+    const uint32_t epoch = *(volatile uint32_t*)(a.flags[a.rank] + F_EPOCH) + 1u;
+    begin_barrier(a, epoch);
+    if (a.rank == root) {
+        const uint4* src = reinterpret_cast<const uint4*>(a.push[root]) + off;
+        const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+            const uint4 v = src[i];
+            if (a.push_mc) {
+                st_mc_16(reinterpret_cast<uint4*>(a.push_mc) + off + i, v);
+            } else {
+#pragma unroll
+                for (int j = 0; j < MAX_RANKS; ++j)
+                    if (j < a.world && j != root) (reinterpret_cast<uint4*>(a.push[j]) + off)[i] = v;
+            }
+        }
+    }
+    end_barrier<true>(a, epoch, nullptr, 0, true);
+}
+
 static int fill_args(const b200_comm* c, CommArgs* a) {
     B200_REQUIRE(c && c->world >= 1 && c->world <= MAX_RANKS, "comm: world size must be in [1, %d]", MAX_RANKS);
     B200_REQUIRE(c->rank >= 0 && c->rank < c->world, "comm: bad rank %d", c->rank);
@@ -545,6 +569,23 @@ extern "C" int b200_allreduce(const b200_comm* c, int algo, int64_t start, int64
         else if (algo == 1) allreduce_kernel<false, 1><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
         else allreduce_kernel<false, 2><<<blocks, 256, 0, s>>>(a, start, n, out, scale);
     }
+    b200_count_launch(1);
+    B200_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int b200_broadcast(const b200_comm* c, int root, int64_t offset_bytes, int64_t nbytes, void* stream) {
+    using namespace b200;
+    CommArgs a;
+    int rc = fill_args(c, &a);
+    if (rc) return rc;
+    B200_REQUIRE(root >= 0 && root < c->world, "broadcast: bad root %d", root);
+    B200_REQUIRE(offset_bytes >= 0 && nbytes > 0 && (offset_bytes % 16) == 0 && (nbytes % 16) == 0,
+                 "broadcast: offset and size must be multiples of 16 bytes");
+    for (int j = 0; j < c->world; ++j) B200_REQUIRE(a.push[j], "broadcast: missing arena pointer of rank %d", j);
+    const int64_t nvec = nbytes / 16;
+    const int blocks = c->rank == root ? grid_for(nvec, c->max_blocks > 0 ? c->max_blocks : 148) : 1;
+    broadcast_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(a, root, offset_bytes / 16, nvec);
     b200_count_launch(1);
     B200_CUDA_OK(cudaGetLastError());
     return 0;

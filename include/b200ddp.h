@@ -394,6 +394,29 @@ int b200_mlp_host_step(void* session, const void* host_x, const void* host_y, in
                        int* prev_valid, void* stream);
 int b200_mlp_host_finish(void* session, float* last_loss, int* valid, void* stream);
 
+/* Broadcast of [offset_bytes, offset_bytes + nbytes) of rank `root`'s c->push arena into every
+ * rank's (multiples of 16 bytes).  One kernel on every rank with an entry and an exit flag barrier;
+ * capturable like the other collectives.  ref: train.py:136 (DDP forward -> _sync_buffers, the
+ * per-forward broadcast of module buffers). */
+int b200_broadcast(const b200_comm* c, int root, int64_t offset_bytes, int64_t nbytes, void* stream);
+
+/* ---------------------------------------------------------------- symmetric memory, VMM flavour
+ * cuMemCreate allocations shared as POSIX file descriptors and the NVLS multicast object bound over
+ * them (csrc/vmm.cu).  The caller moves the descriptors between processes (SCM_RIGHTS).  All sizes
+ * are the padded size from b200_vmm_padded_size, identical on every rank.  These calls allocate.
+ * ref: what c10d provides behind train.py:71,233; torch: CUDASymmetricMemory. */
+int b200_vmm_support(int* out2);                       /* out[0]: fd-shareable VMM, out[1]: multicast */
+int b200_vmm_padded_size(int64_t bytes, int ranks, int64_t* out);
+int b200_vmm_create(int64_t bytes, void** mapping, void** ptr);
+int b200_vmm_export(void* mapping, int* fd);
+int b200_vmm_import(int fd, int64_t bytes, void** mapping, void** ptr);
+int b200_vmm_release(void* mapping);
+int b200_mc_create(int64_t bytes, int ranks, void** mapping);
+int b200_mc_import(int fd, int64_t bytes, void** mapping);
+int b200_mc_add_device(void* mc);
+int b200_mc_bind_map(void* mc, void* local_mapping, void** mc_ptr);
+int b200_close_fd(int fd);
+
 /* ---------------------------------------------------------------- pooling (NHWC bf16, C % 8 == 0)
  * BASELINE.json config 3 (ResNet-50); no counterpart in the reference (its baseline runs ATen's
  * pooling kernels).  idx: one byte per output element, the winning tap r*S + s (first maximum in

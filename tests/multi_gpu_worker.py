@@ -184,6 +184,52 @@ def check_program_pool(rank, world, dev):
     log("train_steps over a device pool == 50 single steps (bit-identical), back-to-back no-exit-wait kernels")
 
 
+def check_buffer_broadcast(rank, world, dev):
+    """K4: module buffers follow rank 0 before every training forward — our broadcast kernel on the
+    peer-mapped buffer arenas (captured in the step graph), no NCCL call on the step."""
+    import torch.nn as nn
+
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.fc = nn.Linear(32, 16)
+            self.bn = nn.BatchNorm1d(16)
+            self.out = nn.Linear(16, 4)
+
+        def forward(self, x):
+            return self.out(torch.relu(self.bn(self.fc(x))))
+
+    torch.manual_seed(7)
+    eng = DataParallel(Net().to(dev), backend="b200", compute_dtype=torch.float32, use_program=False)
+    assert eng._buffers_in_graph and len(eng._buffer_arenas) == 2      # fp32 statistics + int64 counter
+    for step in range(6):       # 2 eager steps, then the captured step is replayed
+        torch.manual_seed(1000 * rank + step)     # different data per rank -> different local statistics
+        x = torch.randn(24, 32, device=dev) * (1 + rank); y = torch.randint(0, 4, (24,), device=dev)
+        # what rank 0 holds BEFORE the step is what every rank must normalise with during it
+        eng.train_step(x, y)
+        torch.cuda.synchronize()
+    assert len(eng._step_graphs) == 1
+    # after a step every rank holds "rank 0's pre-step buffers updated with ITS OWN batch": they differ ...
+    rm = eng.module.bn.running_mean.clone()
+    allm = [torch.empty_like(rm) for _ in range(world)]
+    dist.all_gather(allm, rm)
+    assert not torch.equal(allm[0], allm[-1])
+    # ... and the next forward starts from rank 0's again
+    eng._sync_buffers()
+    torch.cuda.synchronize()
+    rm = eng.module.bn.running_mean.clone()
+    nb = eng.module.bn.num_batches_tracked.clone()
+    dist.all_gather(allm, rm)
+    assert all(torch.equal(allm[0], t) for t in allm)
+    alln = [torch.empty_like(nb) for _ in range(world)]
+    dist.all_gather(alln, nb)
+    assert all(torch.equal(alln[0], t) for t in alln) and int(nb) == 6
+    got = [torch.empty_like(eng.master) for _ in range(world)]
+    dist.all_gather(got, eng.master)
+    assert all(torch.equal(got[0], t) for t in got), "replicas diverged with broadcast buffers"
+    log("module buffers (fp32 statistics, int64 counter) broadcast from rank 0 by our kernel inside the step graph")
+
+
 def check_autograd_overlap(rank, world, dev):
     """Generic autograd path with bucket hooks on the b200 backend vs the nccl backend."""
     symm_mod.ONE_SHOT_MAX_BYTES = 64 * 1024  # mix of one-shot and two-shot buckets
@@ -212,7 +258,8 @@ def main():
     dev = torch.device("cuda", local)
     assert nat.available()
     arena = SymmetricArena(dev, rank, world)
-    log(f"world {world}: NVLS multicast memory {'available' if arena.nvls else 'unavailable: ' + getattr(arena, '_nvls_error', 'disabled')}")
+    log(f"world {world}: symmetric allocator {'own VMM (cuMemCreate + fd exchange)' if arena.vmm else 'cudaMalloc + CUDA IPC'}; "
+        f"NVLS multicast memory {'available (own cuMulticast object)' if arena.nvls else 'unavailable: ' + getattr(arena, '_nvls_error', 'disabled')}")
     check_plain_allreduce(arena, rank, world, dev)
     for kind in ("adam", "adamw", "sgd"):
         for dtype in (torch.float32, torch.bfloat16):
@@ -222,6 +269,7 @@ def main():
         check_program(rank, world, dev, sharded, fused=True)
     check_program(rank, world, dev, True, fused=False)
     check_program_pool(rank, world, dev)
+    check_buffer_broadcast(rank, world, dev)
     check_autograd_overlap(rank, world, dev)
     dist.barrier()
     log("MULTI_GPU_OK")
