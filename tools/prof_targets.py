@@ -45,5 +45,24 @@ elif what == "step":
     x = torch.randn(64, 784, device=dev); y = torch.randint(0, 10, (64,), device=dev)
     for _ in range(12):
         eng.train_step(x, y)
+elif what == "mlpstep":
+    from b200ddp import DataParallel, SimpleNet
+    eng = DataParallel(SimpleNet().to(dev), backend="b200", compute_dtype=torch.bfloat16)
+    xs = torch.randn(8, 64, 784, device=dev); ys = torch.randint(0, 10, (8, 64), device=dev)
+    eng.train_steps(xs, ys, 0, 24)
+elif what in ("gpt2step", "rn50step"):
+    from b200ddp import DataParallel
+    torch.manual_seed(0)
+    if what == "rn50step":
+        from b200ddp.models.resnet50 import resnet50
+        net = resnet50().to(dev)
+        x = torch.randn(32, 3, 224, 224, device=dev); y = torch.randint(0, 1000, (32,), device=dev)
+    else:
+        from b200ddp.models.gpt2 import GPT2
+        net = GPT2().to(dev)
+        t = torch.randint(0, 50257, (8, 1025), device=dev); x, y = t[:, :-1].contiguous(), t[:, 1:].contiguous()
+    eng = DataParallel(net, optimizer="adamw", lr=3e-4, backend="b200", compute_dtype=torch.bfloat16, step_graph=False)
+    for _ in range(2):
+        eng.train_step(x, y)
 torch.cuda.synchronize()
 print("OK", what)
