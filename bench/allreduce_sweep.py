@@ -9,11 +9,16 @@ and the fused two-shot all-reduce + 1/W + Adam + bf16 parameter push.  Device-ti
 with CUDA events, max over ranks, buffers rotated so consecutive iterations touch
 different memory (a set larger than L2 for the small sizes).
 
-Reported per row: time, algorithm bandwidth S/t, bus bandwidth S/t * 2(W-1)/W, and the
-fraction of the NVLink roofline t_roof = 2 S (W-1)/W / 770 GB/s (measured peer-copy
-bandwidth per direction, B200_PROFILING.md).  For the fused kernel the roofline is
-max(link time, HBM time) with link bytes S_grad (W-1)/W in + S_param (W-1)/W out per rank
-and HBM 28 B/param / W (sharded optimizer) over the measured copy bandwidth.
+Reported per row: time, bus bandwidth S/t * 2(W-1)/W, and the fraction of the NVLink roofline,
+each algorithm against ITS OWN per-direction link bytes:
+    two-shot (P2P)   2 S (W-1)/W
+    NVLS             S (1 + 1/W)          (one switch-reduced pull of the shard, one multicast push)
+Every fraction is quoted twice: against the measured peer-copy rate (770 GB/s per direction,
+B200_PROFILING.md) and against the nominal NVLink 5 rate (900 GB/s, BASELINE.json).  For the
+fused kernel the roofline is max(link time, HBM time): link bytes per direction are
+max(out, in) with, for P2P two-shot, S_grad (W-1)/W pulled + S_param (W-1)/W pushed, and for NVLS
+out = S_grad (W-1)/W + S_param / W, in = S_grad / W + S_param (W-1)/W; HBM is 28 B/param / W
+(sharded optimizer) over the measured copy bandwidth.
 """
 from __future__ import annotations
 
@@ -28,7 +33,8 @@ import torch.distributed as dist
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-LINK_GBS = 770.0
+LINK_GBS = 770.0        # measured peer copy, per direction
+LINK_NOMINAL_GBS = 900.0
 
 
 def main():
@@ -124,26 +130,43 @@ def main():
             del master, m, v
 
         f = (world - 1) / world
-        roof_ar = 2 * nbytes * f / (LINK_GBS * 1e9) * 1e3          # ms, two-shot traffic per direction
-        roof_fused = max((nbytes * f + n * 2 * f) / (LINK_GBS * 1e9), (n / world) * 28 / (hbm * 1e9)) * 1e3
+        nvls_fused = arena.nvls and world > 2
+        bytes_two = 2 * nbytes * f                       # per direction, P2P two-shot
+        bytes_nvls = nbytes * (1 + 1 / world)            # per direction, NVLS
+        sp = n * 2                                       # bf16 parameters pushed by the fused kernel
+        if nvls_fused:
+            bytes_fused = max(nbytes * f + sp / world, nbytes / world + sp * f)
+        else:
+            bytes_fused = nbytes * f + sp * f
+        hbm_ms = (n / world) * 28 / (hbm * 1e9) * 1e3
+
+        def frac(link_bytes, t_ms, gbs, floor_ms=0.0):
+            return max(link_bytes / (gbs * 1e9) * 1e3, floor_ms) / t_ms if t_ms else None
+
         row = {"bytes": nbytes, "dtype": args.dtype, "world": world,
                "nccl_ms": t_nccl, "oneshot_ms": t_one, "twoshot_ms": t_two, "nvls_ms": t_nvls,
                "nvls_busbw_gbs": (nbytes * 2 * f / t_nvls / 1e6) if t_nvls else None,
-               "fused_adam_ms": t_fused, "fused_algo": "nvls" if (arena.nvls and world > 2) else "two-shot",
+               "fused_adam_ms": t_fused, "fused_algo": "nvls" if nvls_fused else "two-shot",
                "nccl_busbw_gbs": nbytes * 2 * f / t_nccl / 1e6,
                "twoshot_busbw_gbs": nbytes * 2 * f / t_two / 1e6,
                "oneshot_busbw_gbs": (nbytes * 2 * f / t_one / 1e6) if t_one else None,
-               "twoshot_roofline_frac": roof_ar / t_two,
-               "nccl_roofline_frac": roof_ar / t_nccl,
-               "fused_roofline_frac": (roof_fused / t_fused) if t_fused else None}
+               "twoshot_roofline_frac": frac(bytes_two, t_two, LINK_GBS),
+               "twoshot_roofline_frac_nominal": frac(bytes_two, t_two, LINK_NOMINAL_GBS),
+               "nvls_roofline_frac": frac(bytes_nvls, t_nvls, LINK_GBS),
+               "nvls_roofline_frac_nominal": frac(bytes_nvls, t_nvls, LINK_NOMINAL_GBS),
+               "nccl_roofline_frac": frac(bytes_two, t_nccl, LINK_GBS),
+               "fused_roofline_frac": frac(bytes_fused, t_fused, LINK_GBS, hbm_ms),
+               "fused_roofline_frac_nominal": frac(bytes_fused, t_fused, LINK_NOMINAL_GBS, hbm_ms)}
         rows.append(row)
         if rank == 0:
             one = f"{t_one * 1e3:9.1f}" if t_one else "        -"
-            fu = f"{t_fused * 1e3:9.1f} ({row['fused_roofline_frac']:.2f})" if t_fused else "        -"
-            nv = f"{t_nvls * 1e3:9.1f} ({row['nvls_busbw_gbs']:6.1f} GB/s)" if t_nvls else "        -"
+            fu = (f"{t_fused * 1e3:9.1f} ({row['fused_roofline_frac']:.2f} / {row['fused_roofline_frac_nominal']:.2f})"
+                  if t_fused else "        -")
+            nv = (f"{t_nvls * 1e3:9.1f} ({row['nvls_roofline_frac']:.2f} / {row['nvls_roofline_frac_nominal']:.2f} of its roofline)"
+                  if t_nvls else "        -")
             print(f"{nbytes:>11d} B  nccl {t_nccl * 1e3:9.1f} us  one-shot {one} us  two-shot "
                   f"{t_two * 1e3:9.1f} us ({row['twoshot_busbw_gbs']:6.1f} GB/s bus, "
-                  f"{row['twoshot_roofline_frac']:.2f} of link roofline)  nvls {nv} us  "
+                  f"{row['twoshot_roofline_frac']:.2f} / {row['twoshot_roofline_frac_nominal']:.2f} of link roofline @770/@900)  nvls {nv} us  "
                   f"fused+adam[{row['fused_algo']}] {fu} us", flush=True)
         del buf, out, nccl_bufs
         torch.cuda.empty_cache()
