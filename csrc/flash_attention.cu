@@ -18,6 +18,8 @@
 // tensor map (no head split copies).
 #include "common.cuh"
 
+#include <cstdlib>
+
 void b200_count_launch(int n);
 
 namespace b200 {
@@ -249,6 +251,280 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaParam
     if (warp == 4) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 256);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Forward, second version (default).  ncu of the kernel above: tensor pipe 13 % active, a third of
+// all stall samples in mbarrier spins — S, softmax, PV and the fold of O form ONE serial chain per
+// CTA, and two co-resident CTAs are all the overlap there is.  Here a CTA owns TWO 128-query tiles
+// that ping-pong on the tensor core:
+//
+//   warps 0-3 / 4-7   softmax of tile 0 / tile 1, one query row per thread.  ONE pass over S
+//                     (128 fp32 in registers): row max, then P = exp2(s*c - m) as bf16 into the
+//                     tile's swizzled P buffer.  O is never folded in registers: it accumulates in
+//                     TMEM across KV blocks, and is rescaled there (tcgen05.ld / st) only when a
+//                     row's maximum grew by more than 2^8 since the value m the probabilities are
+//                     expressed in — after the first blocks that is rare, and until then P <= 256
+//                     is harmless in bf16 / fp32 (the final 1/l undoes it).
+//   warp 8            MMA issuer: ... PV_0(i), S_0(i+1), PV_1(i), S_1(i+1) ...  — while one tile's
+//                     softmax runs, the other tile's products occupy the tensor core.
+//   warp 9            TMA producer: both Q tiles once, K/V blocks through a 2-stage ring; every
+//                     K/V tile feeds four products (two tiles x {S, PV}).
+//
+// TMEM: S0 128 + S1 128 + O0 64 + O1 64 = 384 of 512 columns.  Shared memory: Q 2 x 16 KB,
+// K/V 2 x 2 x 16 KB, P 2 x 32 KB = 160 KB: one CTA per SM, heaviest tile pairs first.
+constexpr int FA2_THREADS = 320;
+constexpr uint32_t FA2_SMEM = FA_TILE_BYTES * (2 + 2 + 2) + 2 * 2 * FA_TILE_BYTES /*P0, P1*/ + 256;
+
+__device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+        "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]),
+        "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]),
+        "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x8(uint32_t taddr, const uint32_t (&v)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(v[0]),
+                 "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x8(uint32_t taddr, uint32_t (&v)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+__global__ void __launch_bounds__(FA2_THREADS, 1)
+flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaParams p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if (threadIdx.x == 0 && (smem_u32(smem) & 1023u) != 0) __trap();
+    uint8_t* s_q = smem;                           // 2 tiles
+    uint8_t* s_k = s_q + 2 * FA_TILE_BYTES;        // 2 stages
+    uint8_t* s_v = s_k + 2 * FA_TILE_BYTES;        // 2 stages
+    uint8_t* s_p = s_v + 2 * FA_TILE_BYTES;        // 2 tiles x 32 KB
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_p + 4 * FA_TILE_BYTES);
+    uint64_t* q_full = bars;          // 1
+    uint64_t* k_full = bars + 1;      // 2
+    uint64_t* v_full = bars + 3;      // 2
+    uint64_t* kv_empty = bars + 5;    // 2
+    uint64_t* s_full = bars + 7;      // 2 (per tile)
+    uint64_t* p_full = bars + 9;      // 2 (per tile, 128 arrivals)
+    uint64_t* o_full = bars + 11;     // 2 (per tile)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nq = p.T / FA_BLOCK;                 // 128-query tiles in the sequence
+    const int npairs = (nq + 1) / 2;
+    const int u = npairs - 1 - (int)blockIdx.x;    // heaviest pairs first
+    const int h = blockIdx.y, b = blockIdx.z;
+    // tile t covers query tile 2u + t and walks KV blocks 0 .. 2u + t; tile 1 may not exist (odd nq)
+    const int steps0 = 2 * u + 1;
+    const int steps1 = (2 * u + 1 < nq) ? 2 * u + 2 : 0;
+    const int nblocks = steps1 ? steps1 : steps0;
+
+    if (warp == 8 && lane == 0) {
+        tma_prefetch_desc(&tma_qkv);
+        mbar_init(q_full, 1);
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&k_full[s], 1); mbar_init(&v_full[s], 1); mbar_init(&kv_empty[s], 1);
+            mbar_init(&s_full[s], 1); mbar_init(&p_full[s], FA_BLOCK); mbar_init(&o_full[s], 1);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 8) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    if (warp == 9) {
+        // ===================== TMA producer =====================
+        if (elect_one()) {
+            mbar_arrive_expect_tx(q_full, (steps1 ? 2u : 1u) * FA_TILE_BYTES);
+            tma_load_4d(s_q, &tma_qkv, q_full, 0, 0 * p.H + h, (2 * u) * FA_BLOCK, b);
+            if (steps1) tma_load_4d(s_q + FA_TILE_BYTES, &tma_qkv, q_full, 0, 0 * p.H + h, (2 * u + 1) * FA_BLOCK, b);
+        }
+        __syncwarp();
+        for (int j = 0; j < nblocks; ++j) {
+            const int st = j & 1;
+            if (j >= 2) mbar_wait(&kv_empty[st], (uint32_t)(((j >> 1) - 1) & 1));
+            if (elect_one()) {
+                mbar_arrive_expect_tx(&k_full[st], FA_TILE_BYTES);
+                tma_load_4d(s_k + st * FA_TILE_BYTES, &tma_qkv, &k_full[st], 0, 1 * p.H + h, j * FA_BLOCK, b);
+                mbar_arrive_expect_tx(&v_full[st], FA_TILE_BYTES);
+                tma_load_4d(s_v + st * FA_TILE_BYTES, &tma_qkv, &v_full[st], 0, 2 * p.H + h, j * FA_BLOCK, b);
+            }
+            __syncwarp();
+        }
+    } else if (warp == 8) {
+        // ===================== MMA issuer =====================
+        const uint32_t idesc_s = fa_idesc(128, false), idesc_o = fa_idesc(64, true);
+        const uint64_t dq0 = umma_smem_desc(smem_u32(s_q), 16, 1024);
+        const uint64_t dk0 = umma_smem_desc(smem_u32(s_k), 16, 1024);
+        const uint64_t dp0 = umma_smem_desc(smem_u32(s_p), 16, 1024);
+        const uint64_t dv0 = umma_smem_desc(smem_u32(s_v), 8192, 1024);
+        auto issue_s = [&](int t, int j) {      // S_t = Q_t K_j^T
+            const int st = j & 1;
+            mbar_wait(&k_full[st], (uint32_t)((j >> 1) & 1));
+            tc_fence_after();
+            if (elect_one()) {
+                const uint64_t dq = dq0 + (uint64_t)(t * (FA_TILE_BYTES >> 4)), dk = dk0 + (uint64_t)(st * (FA_TILE_BYTES >> 4));
+#pragma unroll
+                for (int k = 0; k < FA_D / 16; ++k)
+                    umma_bf16(tmem_base + t * 128, dq + (uint64_t)(2 * k), dk + (uint64_t)(2 * k), idesc_s, k != 0 ? 1u : 0u);
+                umma_commit(&s_full[t]);
+            }
+            __syncwarp();
+        };
+        auto issue_pv = [&](int t, int i, bool last_user) {   // O_t (+)= P_t V_i
+            const int st = i & 1;
+            mbar_wait(&p_full[t], (uint32_t)(i & 1));
+            tc_fence_after();
+            mbar_wait(&v_full[st], (uint32_t)((i >> 1) & 1));
+            tc_fence_after();
+            if (elect_one()) {
+                const uint64_t dp = dp0 + (uint64_t)(t * 2 * (FA_TILE_BYTES >> 4)), dv = dv0 + (uint64_t)(st * (FA_TILE_BYTES >> 4));
+#pragma unroll
+                for (int kk = 0; kk < FA_BLOCK / 16; ++kk)
+                    umma_bf16(tmem_base + 256 + t * 64, dp + (uint64_t)((kk >> 2) * (FA_TILE_BYTES >> 4) + (kk & 3) * 2),
+                              dv + (uint64_t)(kk * 128), idesc_o, (i > 0 || kk != 0) ? 1u : 0u);
+                umma_commit(&o_full[t]);
+                if (last_user) umma_commit(&kv_empty[st]);
+            }
+            __syncwarp();
+        };
+        mbar_wait(q_full, 0);
+        issue_s(0, 0);
+        if (steps1) issue_s(1, 0);
+        for (int i = 0; i < nblocks; ++i) {
+            // KV block i is last used by tile 1's PV when tile 1 exists (it always walks at least as far)
+            if (i < steps0) {
+                issue_pv(0, i, steps1 == 0);
+                if (i + 1 < steps0) issue_s(0, i + 1);
+            }
+            if (i < steps1) {
+                issue_pv(1, i, true);
+                if (i + 1 < steps1) issue_s(1, i + 1);
+            }
+        }
+    } else {
+        // ===================== softmax warps: tile t = warp / 4, thread r owns one query row =====================
+        const int t = warp >> 2;
+        const int r = threadIdx.x & 127;
+        const int steps = t ? steps1 : steps0;
+        const int qi = 2 * u + t;
+        const uint32_t lane_addr = ((uint32_t)((warp & 3) * 32)) << 16;
+        const uint32_t tmem_s = tmem_base + t * 128 + lane_addr, tmem_o = tmem_base + 256 + t * 64 + lane_addr;
+        uint8_t* my_p = s_p + t * 2 * FA_TILE_BYTES;
+        float m = -INFINITY, l = 0.f;    // m: the maximum the stored probabilities (and O, l) are relative to
+        for (int i = 0; i < steps; ++i) {
+            const bool diag = (i == qi);
+            mbar_wait(&s_full[t], (uint32_t)(i & 1));
+            tc_fence_after();
+            uint32_t v0[32], v1[32], v2[32], v3[32];
+            tmem_ld_32x32(tmem_s, v0);
+            tmem_ld_32x32(tmem_s + 32, v1);
+            tmem_ld_32x32(tmem_s + 64, v2);
+            tmem_ld_32x32(tmem_s + 96, v3);
+            tmem_ld_wait();
+            float mx = -INFINITY;
+#pragma unroll
+            for (int c = 0; c < 32; ++c) {
+                if (!diag || c <= r) mx = fmaxf(mx, __uint_as_float(v0[c]));
+                if (!diag || 32 + c <= r) mx = fmaxf(mx, __uint_as_float(v1[c]));
+                if (!diag || 64 + c <= r) mx = fmaxf(mx, __uint_as_float(v2[c]));
+                if (!diag || 96 + c <= r) mx = fmaxf(mx, __uint_as_float(v3[c]));
+            }
+            const float m_new = fmaxf(m, mx * p.scale_log2e);
+            if (i > 0) {
+                // P_t of the previous block has been read (and O_t updated) once PV_t(i-1) retired
+                mbar_wait(&o_full[t], (uint32_t)((i - 1) & 1));
+                tc_fence_after();
+                const bool grow = m_new - m > 8.f;
+                if (__any_sync(0xffffffffu, grow)) {      // warp-uniform: TMEM ld / st are warp-collective
+                    const float m_next = grow ? m_new : m;
+                    const float alpha = fa_exp2(m - m_next);
+                    // rare path, eight columns at a time: the 128 scores stay in registers meanwhile
+#pragma unroll 1
+                    for (int c = 0; c < FA_D / 8; ++c) {
+                        uint32_t o[8];
+                        tmem_ld_32x8(tmem_o + c * 8, o);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * alpha);
+                        tmem_st_32x8(tmem_o + c * 8, o);
+                    }
+                    tmem_st_wait();
+                    l *= alpha;
+                    m = m_next;
+                }
+            } else {
+                m = m_new;
+            }
+            float psum = 0.f;
+            // eight probabilities at a time (16 bytes of bf16): the 128 scores already fill the register file
+            auto emit = [&](const uint32_t (&v)[32], int c32) {
+                uint8_t* blk = my_p + (c32 >> 1) * FA_TILE_BYTES + r * 128;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    float pv[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const float x = fa_exp2(__uint_as_float(v[8 * q + e]) * p.scale_log2e - m);
+                        pv[e] = (!diag || c32 * 32 + 8 * q + e <= r) ? x : 0.f;
+                        psum += pv[e];
+                    }
+                    const int vec = (c32 & 1) * 4 + q;
+                    *reinterpret_cast<uint4*>(blk + ((vec ^ (r & 7)) << 4)) =
+                        make_uint4(pack_bf16(pv[0], pv[1]), pack_bf16(pv[2], pv[3]), pack_bf16(pv[4], pv[5]), pack_bf16(pv[6], pv[7]));
+                }
+            };
+            emit(v0, 0); emit(v1, 1); emit(v2, 2); emit(v3, 3);
+            l += psum;
+            fence_proxy_async();
+            tc_fence_before();
+            mbar_arrive(&p_full[t]);
+        }
+        if (steps > 0) {
+            mbar_wait(&o_full[t], (uint32_t)((steps - 1) & 1));
+            tc_fence_after();
+            const float inv = 1.f / l;
+            __nv_bfloat16* dst = p.out + ((int64_t)b * p.T + qi * FA_BLOCK + r) * ((int64_t)p.H * FA_D) + (int64_t)h * FA_D;
+#pragma unroll
+            for (int c = 0; c < FA_D / 32; ++c) {
+                uint32_t o[32];
+                tmem_ld_32x32(tmem_o + c * 32, o);
+                tmem_ld_wait();
+#pragma unroll
+                for (int d = 0; d < 32; d += 8) {
+                    uint4 w;
+                    w.x = pack_bf16(__uint_as_float(o[d]) * inv, __uint_as_float(o[d + 1]) * inv);
+                    w.y = pack_bf16(__uint_as_float(o[d + 2]) * inv, __uint_as_float(o[d + 3]) * inv);
+                    w.z = pack_bf16(__uint_as_float(o[d + 4]) * inv, __uint_as_float(o[d + 5]) * inv);
+                    w.w = pack_bf16(__uint_as_float(o[d + 6]) * inv, __uint_as_float(o[d + 7]) * inv);
+                    *reinterpret_cast<uint4*>(dst + c * 32 + d) = w;
+                }
+            }
+            p.lse[((int64_t)b * p.H + h) * p.T + qi * FA_BLOCK + r] = (m + log2f(l)) * 0.6931471805599453f;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
     }
 }
 
@@ -584,6 +860,8 @@ int b200_flash_init() {
                                       (int)b200::FA_SMEM));
     B200_CUDA_OK(cudaFuncSetAttribute(b200::flash_attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)b200::FAB_SMEM));
+    B200_CUDA_OK(cudaFuncSetAttribute(b200::flash_attn_fwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)b200::FA2_SMEM));
     return 0;
 }
 
@@ -600,8 +878,14 @@ extern "C" int b200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B
     CUtensorMap map;
     if (int rc = fa_make_map(&map, qkv, B, T, H, 3)) return rc;
     FaParams p{B, T, H, (__nv_bfloat16*)out, lse, 1.4426950408889634f / sqrtf((float)D)};
-    dim3 grid((unsigned)(T / FA_BLOCK), (unsigned)H, (unsigned)B);
-    flash_attn_fwd_kernel<<<grid, FA_THREADS, FA_SMEM, (cudaStream_t)stream>>>(map, p);
+    static const bool v1 = getenv("B200DDP_FLASH_FWD_V1") != nullptr;    // the one-tile-per-CTA kernel, for comparison
+    if (v1) {
+        dim3 grid((unsigned)(T / FA_BLOCK), (unsigned)H, (unsigned)B);
+        flash_attn_fwd_kernel<<<grid, FA_THREADS, FA_SMEM, (cudaStream_t)stream>>>(map, p);
+    } else {
+        dim3 grid((unsigned)((T / FA_BLOCK + 1) / 2), (unsigned)H, (unsigned)B);
+        flash_attn_fwd2_kernel<<<grid, FA2_THREADS, FA2_SMEM, (cudaStream_t)stream>>>(map, p);
+    }
     b200_count_launch(1);
     B200_CUDA_OK(cudaGetLastError());
     return 0;
