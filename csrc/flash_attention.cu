@@ -19,6 +19,7 @@
 #include "common.cuh"
 
 #include <cstdlib>
+#include <type_traits>
 
 void b200_count_launch(int n);
 
@@ -43,6 +44,25 @@ __device__ __forceinline__ float fa_exp2(float x) {   // MUFU ex2; inputs are <=
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+
+// exp2 on the FMA pipe.  ncu of the forward: the XU pipe (MUFU) is the busiest unit by far (51 % of
+// its peak over the whole launch, FMA 8 %) — on B200 the softmax of a 128 x 128 score tile is bound by
+// MUFU.EX2, not by the tensor core.  So a share of the exponentials is computed arithmetically:
+// round-to-nearest split x = n + f with the 1.5 * 2^23 trick, 2^f on [-0.5, 0.5] by a cubic
+// (max relative error 1.0e-4, far below bf16's 3.9e-3), 2^n by adding n to the exponent field.
+__device__ __forceinline__ float fa_exp2_poly(float x) {
+    x = fmaxf(x, -125.f);
+    const float t = x + 12582912.f;
+    const float f = x - (t - 12582912.f);
+    float pl = fmaf(f, 0.05592203512787819f, 0.24264007806777954f);
+    pl = fmaf(pl, f, 0.6931210160255432f);
+    pl = fmaf(pl, f, 0.9999244809150696f);
+    return __int_as_float(__float_as_int(pl) + (__float_as_int(t) << 23));
+}
+// of every 8 consecutive probabilities, this many take the polynomial, the rest MUFU
+#ifndef FA_POLY_OF_8
+#define FA_POLY_OF_8 4
+#endif
 
 __device__ __forceinline__ uint32_t fa_idesc(int n, bool b_mn) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(b_mn ? 1 : 0) << 16) | ((uint32_t)(n >> 3) << 17) |
@@ -439,12 +459,18 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
             tmem_ld_32x32(tmem_s + 96, v3);
             tmem_ld_wait();
             float mx = -INFINITY;
+            if (!diag) {     // 29 of 36 steps: no masking arithmetic at all
 #pragma unroll
-            for (int c = 0; c < 32; ++c) {
-                if (!diag || c <= r) mx = fmaxf(mx, __uint_as_float(v0[c]));
-                if (!diag || 32 + c <= r) mx = fmaxf(mx, __uint_as_float(v1[c]));
-                if (!diag || 64 + c <= r) mx = fmaxf(mx, __uint_as_float(v2[c]));
-                if (!diag || 96 + c <= r) mx = fmaxf(mx, __uint_as_float(v3[c]));
+                for (int c = 0; c < 32; ++c)
+                    mx = fmaxf(fmaxf(mx, __uint_as_float(v0[c])), fmaxf(__uint_as_float(v1[c]), fmaxf(__uint_as_float(v2[c]), __uint_as_float(v3[c]))));
+            } else {
+#pragma unroll
+                for (int c = 0; c < 32; ++c) {
+                    if (c <= r) mx = fmaxf(mx, __uint_as_float(v0[c]));
+                    if (32 + c <= r) mx = fmaxf(mx, __uint_as_float(v1[c]));
+                    if (64 + c <= r) mx = fmaxf(mx, __uint_as_float(v2[c]));
+                    if (96 + c <= r) mx = fmaxf(mx, __uint_as_float(v3[c]));
+                }
             }
             const float m_new = fmaxf(m, mx * p.scale_log2e);
             if (i > 0) {
@@ -474,15 +500,17 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
             }
             float psum = 0.f;
             // eight probabilities at a time (16 bytes of bf16): the 128 scores already fill the register file
-            auto emit = [&](const uint32_t (&v)[32], int c32) {
+            auto emit = [&](const uint32_t (&v)[32], int c32, auto is_diag) {
+                constexpr bool DIAG = decltype(is_diag)::value;
                 uint8_t* blk = my_p + (c32 >> 1) * FA_TILE_BYTES + r * 128;
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     float pv[8];
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
-                        const float x = fa_exp2(__uint_as_float(v[8 * q + e]) * p.scale_log2e - m);
-                        pv[e] = (!diag || c32 * 32 + 8 * q + e <= r) ? x : 0.f;
+                        const float arg = fmaf(__uint_as_float(v[8 * q + e]), p.scale_log2e, -m);
+                        const float x = (e < FA_POLY_OF_8) ? fa_exp2_poly(arg) : fa_exp2(arg);
+                        pv[e] = (!DIAG || c32 * 32 + 8 * q + e <= r) ? x : 0.f;
                         psum += pv[e];
                     }
                     const int vec = (c32 & 1) * 4 + q;
@@ -490,7 +518,11 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
                         make_uint4(pack_bf16(pv[0], pv[1]), pack_bf16(pv[2], pv[3]), pack_bf16(pv[4], pv[5]), pack_bf16(pv[6], pv[7]));
                 }
             };
-            emit(v0, 0); emit(v1, 1); emit(v2, 2); emit(v3, 3);
+            if (diag) {
+                emit(v0, 0, std::true_type{}); emit(v1, 1, std::true_type{}); emit(v2, 2, std::true_type{}); emit(v3, 3, std::true_type{});
+            } else {
+                emit(v0, 0, std::false_type{}); emit(v1, 1, std::false_type{}); emit(v2, 2, std::false_type{}); emit(v3, 3, std::false_type{});
+            }
             l += psum;
             fence_proxy_async();
             tc_fence_before();
