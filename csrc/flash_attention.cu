@@ -37,6 +37,7 @@ struct FaParams {
     __nv_bfloat16* out;  // [B, T, H*D]
     float* lse;          // [B, H, T]
     float scale_log2e;   // (1/sqrt(D)) * log2(e)
+    int trace;
 };
 
 __device__ __forceinline__ float fa_exp2(float x) {   // MUFU ex2; inputs are <= 0 here
@@ -59,9 +60,15 @@ __device__ __forceinline__ float fa_exp2_poly(float x) {
     pl = fmaf(pl, f, 0.9999244809150696f);
     return __int_as_float(__float_as_int(pl) + (__float_as_int(t) << 23));
 }
-// of every 8 consecutive probabilities, this many take the polynomial, the rest MUFU
+__device__ __forceinline__ float fa_max3(float a, float b, float c) {
+    float r;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+// of every 8 consecutive probabilities, this many take the polynomial, the rest MUFU (the two
+// pipes then finish together: XU 16 cycles per warp instruction, ~12 FMA/ALU cycles per polynomial)
 #ifndef FA_POLY_OF_8
-#define FA_POLY_OF_8 4
+#define FA_POLY_OF_8 3
 #endif
 
 __device__ __forceinline__ uint32_t fa_idesc(int n, bool b_mn) {
@@ -295,7 +302,11 @@ flash_attn_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaParam
 // TMEM: S0 128 + S1 128 + O0 64 + O1 64 = 384 of 512 columns.  Shared memory: Q 2 x 16 KB,
 // K/V 2 x 2 x 16 KB, P 2 x 32 KB = 160 KB: one CTA per SM, heaviest tile pairs first.
 constexpr int FA2_THREADS = 320;
-constexpr uint32_t FA2_SMEM = FA_TILE_BYTES * (2 + 2 + 2) + 2 * 2 * FA_TILE_BYTES /*P0, P1*/ + 256;
+// step timeline of one softmax thread (block 0,0,0; tile 0) for tuning: B200DDP_FA_TRACE=1
+__device__ long long g_fa_trace[16 * 8];
+#define FA_TRACE(i, k) do { if (p.trace && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (i) < 16) g_fa_trace[(i) * 8 + (k)] = clock64(); } while (0)
+constexpr int FA2_STAGES = 3;   // K/V ring: S(i+1) is issued while the softmax of block i runs, so block i+2 must be in flight
+constexpr uint32_t FA2_SMEM = FA_TILE_BYTES * (2 + 2 * FA2_STAGES) + 2 * 2 * FA_TILE_BYTES /*P0, P1*/ + 256;
 
 __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&v)[32]) {
     asm volatile(
@@ -326,24 +337,27 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
     extern __shared__ __align__(1024) uint8_t smem[];
     if (threadIdx.x == 0 && (smem_u32(smem) & 1023u) != 0) __trap();
     uint8_t* s_q = smem;                           // 2 tiles
-    uint8_t* s_k = s_q + 2 * FA_TILE_BYTES;        // 2 stages
-    uint8_t* s_v = s_k + 2 * FA_TILE_BYTES;        // 2 stages
-    uint8_t* s_p = s_v + 2 * FA_TILE_BYTES;        // 2 tiles x 32 KB
+    uint8_t* s_k = s_q + 2 * FA_TILE_BYTES;              // FA2_STAGES stages
+    uint8_t* s_v = s_k + FA2_STAGES * FA_TILE_BYTES;     // FA2_STAGES stages
+    uint8_t* s_p = s_v + FA2_STAGES * FA_TILE_BYTES;     // 2 tiles x 32 KB
     uint64_t* bars = reinterpret_cast<uint64_t*>(s_p + 4 * FA_TILE_BYTES);
     uint64_t* q_full = bars;          // 1
-    uint64_t* k_full = bars + 1;      // 2
-    uint64_t* v_full = bars + 3;      // 2
-    uint64_t* kv_empty = bars + 5;    // 2
-    uint64_t* s_full = bars + 7;      // 2 (per tile)
-    uint64_t* p_full = bars + 9;      // 2 (per tile, 128 arrivals)
-    uint64_t* o_full = bars + 11;     // 2 (per tile)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+    uint64_t* k_full = bars + 1;      // 3
+    uint64_t* v_full = bars + 4;      // 3
+    uint64_t* kv_empty = bars + 7;    // 3
+    uint64_t* s_full = bars + 10;     // 2 (per tile)
+    uint64_t* p_full = bars + 12;     // 2 (per tile, 128 arrivals)
+    uint64_t* o_full = bars + 14;     // 2 (per tile)
+    uint64_t* s_free = bars + 16;     // 2 (per tile, 128 arrivals): the scores are in registers, S may be overwritten
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 18);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nq = p.T / FA_BLOCK;                 // 128-query tiles in the sequence
     const int npairs = (nq + 1) / 2;
-    const int u = npairs - 1 - (int)blockIdx.x;    // heaviest pairs first
-    const int h = blockIdx.y, b = blockIdx.z;
+    // the pair index is the SLOWEST grid axis: every heaviest pair (4u + 3 tile steps) is scheduled
+    // before the first lighter one, so the tail of the launch is made of short CTAs
+    const int u = npairs - 1 - (int)blockIdx.z;
+    const int h = blockIdx.x, b = blockIdx.y;
     // tile t covers query tile 2u + t and walks KV blocks 0 .. 2u + t; tile 1 may not exist (odd nq)
     const int steps0 = 2 * u + 1;
     const int steps1 = (2 * u + 1 < nq) ? 2 * u + 2 : 0;
@@ -352,9 +366,9 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
     if (warp == 8 && lane == 0) {
         tma_prefetch_desc(&tma_qkv);
         mbar_init(q_full, 1);
+        for (int s = 0; s < FA2_STAGES; ++s) { mbar_init(&k_full[s], 1); mbar_init(&v_full[s], 1); mbar_init(&kv_empty[s], 1); }
         for (int s = 0; s < 2; ++s) {
-            mbar_init(&k_full[s], 1); mbar_init(&v_full[s], 1); mbar_init(&kv_empty[s], 1);
-            mbar_init(&s_full[s], 1); mbar_init(&p_full[s], FA_BLOCK); mbar_init(&o_full[s], 1);
+            mbar_init(&s_full[s], 1); mbar_init(&p_full[s], FA_BLOCK); mbar_init(&o_full[s], 1); mbar_init(&s_free[s], FA_BLOCK);
         }
         fence_mbar_init();
     }
@@ -377,8 +391,8 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
         }
         __syncwarp();
         for (int j = 0; j < nblocks; ++j) {
-            const int st = j & 1;
-            if (j >= 2) mbar_wait(&kv_empty[st], (uint32_t)(((j >> 1) - 1) & 1));
+            const int st = j % FA2_STAGES;
+            if (j >= FA2_STAGES) mbar_wait(&kv_empty[st], (uint32_t)((j / FA2_STAGES - 1) & 1));
             if (elect_one()) {
                 mbar_arrive_expect_tx(&k_full[st], FA_TILE_BYTES);
                 tma_load_4d(s_k + st * FA_TILE_BYTES, &tma_qkv, &k_full[st], 0, 1 * p.H + h, j * FA_BLOCK, b);
@@ -395,8 +409,8 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
         const uint64_t dp0 = umma_smem_desc(smem_u32(s_p), 16, 1024);
         const uint64_t dv0 = umma_smem_desc(smem_u32(s_v), 8192, 1024);
         auto issue_s = [&](int t, int j) {      // S_t = Q_t K_j^T
-            const int st = j & 1;
-            mbar_wait(&k_full[st], (uint32_t)((j >> 1) & 1));
+            const int st = j % FA2_STAGES;
+            mbar_wait(&k_full[st], (uint32_t)((j / FA2_STAGES) & 1));
             tc_fence_after();
             if (elect_one()) {
                 const uint64_t dq = dq0 + (uint64_t)(t * (FA_TILE_BYTES >> 4)), dk = dk0 + (uint64_t)(st * (FA_TILE_BYTES >> 4));
@@ -408,10 +422,10 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
             __syncwarp();
         };
         auto issue_pv = [&](int t, int i, bool last_user) {   // O_t (+)= P_t V_i
-            const int st = i & 1;
+            const int st = i % FA2_STAGES;
             mbar_wait(&p_full[t], (uint32_t)(i & 1));
             tc_fence_after();
-            mbar_wait(&v_full[st], (uint32_t)((i >> 1) & 1));
+            mbar_wait(&v_full[st], (uint32_t)((i / FA2_STAGES) & 1));
             tc_fence_after();
             if (elect_one()) {
                 const uint64_t dp = dp0 + (uint64_t)(t * 2 * (FA_TILE_BYTES >> 4)), dv = dv0 + (uint64_t)(st * (FA_TILE_BYTES >> 4));
@@ -428,15 +442,13 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
         issue_s(0, 0);
         if (steps1) issue_s(1, 0);
         for (int i = 0; i < nblocks; ++i) {
+            // next scores first: S_t is free as soon as its softmax warps hold block i in registers
+            // (a few hundred cycles into their step), so S_t(i+1) is ready long before they finish
+            if (i + 1 < steps0) { mbar_wait(&s_free[0], (uint32_t)(i & 1)); tc_fence_after(); issue_s(0, i + 1); }
+            if (i + 1 < steps1) { mbar_wait(&s_free[1], (uint32_t)(i & 1)); tc_fence_after(); issue_s(1, i + 1); }
             // KV block i is last used by tile 1's PV when tile 1 exists (it always walks at least as far)
-            if (i < steps0) {
-                issue_pv(0, i, steps1 == 0);
-                if (i + 1 < steps0) issue_s(0, i + 1);
-            }
-            if (i < steps1) {
-                issue_pv(1, i, true);
-                if (i + 1 < steps1) issue_s(1, i + 1);
-            }
+            if (i < steps0) issue_pv(0, i, steps1 == 0);
+            if (i < steps1) issue_pv(1, i, true);
         }
     } else {
         // ===================== softmax warps: tile t = warp / 4, thread r owns one query row =====================
@@ -450,19 +462,28 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
         float m = -INFINITY, l = 0.f;    // m: the maximum the stored probabilities (and O, l) are relative to
         for (int i = 0; i < steps; ++i) {
             const bool diag = (i == qi);
+            FA_TRACE(i, 0);
             mbar_wait(&s_full[t], (uint32_t)(i & 1));
             tc_fence_after();
+            FA_TRACE(i, 1);
             uint32_t v0[32], v1[32], v2[32], v3[32];
             tmem_ld_32x32(tmem_s, v0);
             tmem_ld_32x32(tmem_s + 32, v1);
             tmem_ld_32x32(tmem_s + 64, v2);
             tmem_ld_32x32(tmem_s + 96, v3);
             tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(&s_free[t]);
+            FA_TRACE(i, 2);
             float mx = -INFINITY;
             if (!diag) {     // 29 of 36 steps: no masking arithmetic at all
 #pragma unroll
-                for (int c = 0; c < 32; ++c)
-                    mx = fmaxf(fmaxf(mx, __uint_as_float(v0[c])), fmaxf(__uint_as_float(v1[c]), fmaxf(__uint_as_float(v2[c]), __uint_as_float(v3[c]))));
+                for (int c = 0; c < 32; c += 2) {      // FMNMX3: two new values per instruction
+                    mx = fa_max3(mx, __uint_as_float(v0[c]), __uint_as_float(v0[c + 1]));
+                    mx = fa_max3(mx, __uint_as_float(v1[c]), __uint_as_float(v1[c + 1]));
+                    mx = fa_max3(mx, __uint_as_float(v2[c]), __uint_as_float(v2[c + 1]));
+                    mx = fa_max3(mx, __uint_as_float(v3[c]), __uint_as_float(v3[c + 1]));
+                }
             } else {
 #pragma unroll
                 for (int c = 0; c < 32; ++c) {
@@ -473,10 +494,12 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
                 }
             }
             const float m_new = fmaxf(m, mx * p.scale_log2e);
+            FA_TRACE(i, 3);
             if (i > 0) {
                 // P_t of the previous block has been read (and O_t updated) once PV_t(i-1) retired
                 mbar_wait(&o_full[t], (uint32_t)((i - 1) & 1));
                 tc_fence_after();
+                FA_TRACE(i, 4);
                 const bool grow = m_new - m > 8.f;
                 if (__any_sync(0xffffffffu, grow)) {      // warp-uniform: TMEM ld / st are warp-collective
                     const float m_next = grow ? m_new : m;
@@ -524,9 +547,11 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
                 emit(v0, 0, std::false_type{}); emit(v1, 1, std::false_type{}); emit(v2, 2, std::false_type{}); emit(v3, 3, std::false_type{});
             }
             l += psum;
+            FA_TRACE(i, 5);
             fence_proxy_async();
             tc_fence_before();
             mbar_arrive(&p_full[t]);
+            FA_TRACE(i, 6);
         }
         if (steps > 0) {
             mbar_wait(&o_full[t], (uint32_t)((steps - 1) & 1));
@@ -897,6 +922,12 @@ int b200_flash_init() {
     return 0;
 }
 
+extern "C" int b200_flash_debug_trace(long long* out) {
+    B200_CUDA_OK(cudaDeviceSynchronize());
+    B200_CUDA_OK(cudaMemcpyFromSymbol(out, b200::g_fa_trace, sizeof(long long) * 128));
+    return 0;
+}
+
 extern "C" int b200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D,
                                    void* stream) {
     using namespace b200;
@@ -909,13 +940,14 @@ extern "C" int b200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B
     if (inited) return inited;
     CUtensorMap map;
     if (int rc = fa_make_map(&map, qkv, B, T, H, 3)) return rc;
-    FaParams p{B, T, H, (__nv_bfloat16*)out, lse, 1.4426950408889634f / sqrtf((float)D)};
+    static const int trace = getenv("B200DDP_FA_TRACE") != nullptr;
+    FaParams p{B, T, H, (__nv_bfloat16*)out, lse, 1.4426950408889634f / sqrtf((float)D), trace};
     static const bool v1 = getenv("B200DDP_FLASH_FWD_V1") != nullptr;    // the one-tile-per-CTA kernel, for comparison
     if (v1) {
         dim3 grid((unsigned)(T / FA_BLOCK), (unsigned)H, (unsigned)B);
         flash_attn_fwd_kernel<<<grid, FA_THREADS, FA_SMEM, (cudaStream_t)stream>>>(map, p);
     } else {
-        dim3 grid((unsigned)((T / FA_BLOCK + 1) / 2), (unsigned)H, (unsigned)B);
+        dim3 grid((unsigned)H, (unsigned)B, (unsigned)((T / FA_BLOCK + 1) / 2));
         flash_attn_fwd2_kernel<<<grid, FA2_THREADS, FA2_SMEM, (cudaStream_t)stream>>>(map, p);
     }
     b200_count_launch(1);

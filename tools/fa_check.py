@@ -11,3 +11,14 @@ with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for _ in range(5): Fn.flash_attention_forward(qkv, 12)
     torch.cuda.synchronize()
 print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=5, max_name_column_width=60))
+
+if os.environ.get("B200DDP_FA_TRACE"):
+    import ctypes as C
+    from b200ddp import _native as nat
+    buf = (C.c_longlong * 128)()
+    nat.lib().b200_flash_debug_trace.argtypes = [C.c_void_p]
+    nat.check(nat.lib().b200_flash_debug_trace(buf), "trace")
+    print("step: wait S | tmem ld | max | wait O(i-1) | exp+store | arrive   (cycles; block 0 = heaviest pair, tile 0, thread 0)")
+    for i in range(7):
+        r = [buf[i * 8 + k] for k in range(7)]
+        print(i, [r[k + 1] - r[k] if r[k + 1] and r[k] else None for k in range(6)], "step total", (buf[(i + 1) * 8] - r[0]) if buf[(i + 1) * 8] else None)
