@@ -616,7 +616,12 @@ __device__ __forceinline__ uint32_t fab_idesc(int n, bool a_mn, bool b_mn) {
            ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 }
 
-__global__ void __launch_bounds__(FA_THREADS, 1)
+// 8 softmax warps: TWO threads per query row (64 key columns each; warps w and w + 4 share TMEM
+// lanes), warp 8 issues TMA and MMA.  lse and delta come from memory, so the two halves of a row
+// never talk to each other; with two warps per scheduler the exp2 / dS arithmetic of one hides
+// the latencies of the other (one warp per scheduler was the round-1 diagnosis).
+constexpr int FAB_THREADS = 288;
+__global__ void __launch_bounds__(FAB_THREADS, 1)
 flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_constant__ CUtensorMap tma_do,
                       const FaBwdParams p) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -632,30 +637,30 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
     uint64_t* qdo_full = bars + 1;    // 2
     uint64_t* qdo_empty = bars + 3;   // 2
     uint64_t* sdp_full = bars + 5;    // 1
-    uint64_t* pds_full = bars + 6;    // 1 (128 arrivals)
+    uint64_t* pds_full = bars + 6;    // 1 (256 arrivals)
     uint64_t* dq_full = bars + 7;     // 1
     uint64_t* dkv_full = bars + 8;    // 1
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nq = p.T / FA_BLOCK;
-    const int kj = blockIdx.x;                 // key block; block 0 has the most query blocks
-    const int h = blockIdx.y, b = blockIdx.z;
+    const int kj = blockIdx.z;                 // key block on the slowest grid axis: block 0 (most query blocks) first
+    const int h = blockIdx.x, b = blockIdx.y;
     const int niter = nq - kj;
     const int k0 = kj * FA_BLOCK;
 
-    if (warp == 4 && lane == 0) {
+    if (warp == 8 && lane == 0) {
         tma_prefetch_desc(&tma_qkv);
         tma_prefetch_desc(&tma_do);
         mbar_init(kv_full, 1);
         for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
         mbar_init(sdp_full, 1);
-        mbar_init(pds_full, FA_BLOCK);
+        mbar_init(pds_full, 2 * FA_BLOCK);
         mbar_init(dq_full, 1);
         mbar_init(dkv_full, 1);
         fence_mbar_init();
     }
-    if (warp == 4) {
+    if (warp == 8) {
         tmem_alloc(tmem_slot, 512);
         tmem_relinquish();
     }
@@ -666,7 +671,7 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
     const uint32_t t_s = tmem_base, t_dp = tmem_base + 128, t_dv = tmem_base + 256, t_dk = tmem_base + 320,
                    t_dq = tmem_base + 384;
 
-    if (warp == 4) {
+    if (warp == 8) {
         // whole warp walks the loop, one elected lane issues (see the forward kernel)
         auto load_qdo = [&](int it) {
             const int st = it & 1, i = kj + it;
@@ -740,8 +745,9 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
             }
         }
     } else {
-        const int r = threadIdx.x;
-        const uint32_t lane_addr = ((uint32_t)(warp * 32)) << 16;
+        const int r = threadIdx.x & 127;          // query row inside the block
+        const int half = threadIdx.x >> 7;        // key columns [64 half, 64 half + 64)
+        const uint32_t lane_addr = ((uint32_t)((warp & 3) * 32)) << 16;
         const int64_t bh = (int64_t)b * p.H + h;
         for (int it = 0; it < niter; ++it) {
             const int i = kj + it;
@@ -751,48 +757,48 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
             const float dlt = p.delta[qrow];
             mbar_wait(sdp_full, (uint32_t)(it & 1));
             tc_fence_after();
-#pragma unroll 1
-            for (int c = 0; c < FA_BLOCK / 32; ++c) {
+            auto chunk = [&](int c, auto is_diag) {
+                constexpr bool DIAG = decltype(is_diag)::value;
                 uint32_t vs[32], vd[32];
                 tmem_ld_32x32(t_s + lane_addr + c * 32, vs);
                 tmem_ld_32x32(t_dp + lane_addr + c * 32, vd);
                 tmem_ld_wait();
-                float pv[32], dv[32];
-#pragma unroll
-                for (int e = 0; e < 32; ++e) {
-                    const float pe = fa_exp2(__uint_as_float(vs[e]) * p.scale_log2e - lse2);
-                    const bool ok = !diag || c * 32 + e <= r;   // key column <= query row
-                    pv[e] = ok ? pe : 0.f;
-                    dv[e] = ok ? pe * (__uint_as_float(vd[e]) - dlt) * p.scale : 0.f;
-                }
                 uint8_t* bp = s_p + (c >> 1) * FA_TILE_BYTES + r * 128;
                 uint8_t* bd = s_ds + (c >> 1) * FA_TILE_BYTES + r * 128;
 #pragma unroll
                 for (int t = 0; t < 4; ++t) {
+                    float pv[8], dv[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const float arg = fmaf(__uint_as_float(vs[8 * t + e]), p.scale_log2e, -lse2);
+                        const float pe = (e < FA_POLY_OF_8) ? fa_exp2_poly(arg) : fa_exp2(arg);
+                        const bool ok = !DIAG || c * 32 + 8 * t + e <= r;   // key column <= query row
+                        pv[e] = ok ? pe : 0.f;
+                        dv[e] = ok ? pe * (__uint_as_float(vd[8 * t + e]) - dlt) * p.scale : 0.f;
+                    }
                     const int off = (((c & 1) * 4 + t) ^ (r & 7)) << 4;
                     *reinterpret_cast<uint4*>(bp + off) =
-                        make_uint4(pack_bf16(pv[8 * t], pv[8 * t + 1]), pack_bf16(pv[8 * t + 2], pv[8 * t + 3]),
-                                   pack_bf16(pv[8 * t + 4], pv[8 * t + 5]), pack_bf16(pv[8 * t + 6], pv[8 * t + 7]));
+                        make_uint4(pack_bf16(pv[0], pv[1]), pack_bf16(pv[2], pv[3]), pack_bf16(pv[4], pv[5]), pack_bf16(pv[6], pv[7]));
                     *reinterpret_cast<uint4*>(bd + off) =
-                        make_uint4(pack_bf16(dv[8 * t], dv[8 * t + 1]), pack_bf16(dv[8 * t + 2], dv[8 * t + 3]),
-                                   pack_bf16(dv[8 * t + 4], dv[8 * t + 5]), pack_bf16(dv[8 * t + 6], dv[8 * t + 7]));
+                        make_uint4(pack_bf16(dv[0], dv[1]), pack_bf16(dv[2], dv[3]), pack_bf16(dv[4], dv[5]), pack_bf16(dv[6], dv[7]));
                 }
-            }
+            };
+            if (diag) { chunk(2 * half, std::true_type{}); chunk(2 * half + 1, std::true_type{}); }
+            else { chunk(2 * half, std::false_type{}); chunk(2 * half + 1, std::false_type{}); }
             fence_proxy_async();
             tc_fence_before();
             mbar_arrive(pds_full);
             // dQ_i partial -> fp32 accumulator (other key blocks add to the same rows)
             mbar_wait(dq_full, (uint32_t)(it & 1));
             tc_fence_after();
-            float* dq = p.dq_acc + qrow * FA_D;
-#pragma unroll
-            for (int c = 0; c < FA_D / 32; ++c) {
+            float* dq = p.dq_acc + qrow * FA_D + half * 32;
+            {
                 uint32_t v[32];
-                tmem_ld_32x32(t_dq + lane_addr + c * 32, v);
+                tmem_ld_32x32(t_dq + lane_addr + half * 32, v);
                 tmem_ld_wait();
 #pragma unroll
                 for (int e = 0; e < 32; e += 4)
-                    atomicAdd(reinterpret_cast<float4*>(dq + c * 32 + e),
+                    atomicAdd(reinterpret_cast<float4*>(dq + e),
                               make_float4(__uint_as_float(v[e]), __uint_as_float(v[e + 1]), __uint_as_float(v[e + 2]),
                                           __uint_as_float(v[e + 3])));
             }
@@ -806,27 +812,24 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
         __nv_bfloat16* dv_dst = p.dqkv + (row3 + 2) * ((int64_t)p.H * FA_D) + (int64_t)h * FA_D;
 #pragma unroll
         for (int which = 0; which < 2; ++which) {
-            const uint32_t taddr = (which == 0 ? t_dk : t_dv) + lane_addr;
-            __nv_bfloat16* dst = which == 0 ? dk_dst : dv_dst;
+            const uint32_t taddr = (which == 0 ? t_dk : t_dv) + lane_addr + half * 32;
+            __nv_bfloat16* dst = (which == 0 ? dk_dst : dv_dst) + half * 32;
+            uint32_t v[32];
+            tmem_ld_32x32(taddr, v);
+            tmem_ld_wait();
 #pragma unroll
-            for (int c = 0; c < FA_D / 32; ++c) {
-                uint32_t v[32];
-                tmem_ld_32x32(taddr + c * 32, v);
-                tmem_ld_wait();
-#pragma unroll
-                for (int e = 0; e < 32; e += 8)
-                    *reinterpret_cast<uint4*>(dst + c * 32 + e) = make_uint4(
-                        pack_bf16(__uint_as_float(v[e]), __uint_as_float(v[e + 1])),
-                        pack_bf16(__uint_as_float(v[e + 2]), __uint_as_float(v[e + 3])),
-                        pack_bf16(__uint_as_float(v[e + 4]), __uint_as_float(v[e + 5])),
-                        pack_bf16(__uint_as_float(v[e + 6]), __uint_as_float(v[e + 7])));
-            }
+            for (int e = 0; e < 32; e += 8)
+                *reinterpret_cast<uint4*>(dst + e) = make_uint4(
+                    pack_bf16(__uint_as_float(v[e]), __uint_as_float(v[e + 1])),
+                    pack_bf16(__uint_as_float(v[e + 2]), __uint_as_float(v[e + 3])),
+                    pack_bf16(__uint_as_float(v[e + 4]), __uint_as_float(v[e + 5])),
+                    pack_bf16(__uint_as_float(v[e + 6]), __uint_as_float(v[e + 7])));
         }
     }
 
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) {
+    if (warp == 8) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
     }
@@ -981,8 +984,8 @@ extern "C" int b200_flash_attn_bwd(const void* qkv, const void* out, const void*
     fa_delta_kernel<<<blocks, 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, B, T, H);
     const float scale = 1.f / sqrtf((float)D);
     FaBwdParams p{B, T, H, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, scale, scale * 1.4426950408889634f};
-    dim3 grid((unsigned)(T / FA_BLOCK), (unsigned)H, (unsigned)B);
-    flash_attn_bwd_kernel<<<grid, FA_THREADS, FAB_SMEM, s>>>(map_qkv, map_do, p);
+    dim3 grid((unsigned)H, (unsigned)B, (unsigned)(T / FA_BLOCK));
+    flash_attn_bwd_kernel<<<grid, FAB_THREADS, FAB_SMEM, s>>>(map_qkv, map_do, p);
     fa_dq_convert_kernel<<<148 * 8, 256, 0, s>>>(dq_acc, (__nv_bfloat16*)dqkv, B, T, H);
     b200_count_launch(3);
     B200_CUDA_OK(cudaGetLastError());
