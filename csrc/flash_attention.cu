@@ -600,7 +600,8 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
 //     dV_j += P^T dO_i        dK_j += dS^T Q_i                     -> TMEM (accumulate over i)
 //     dQ_i partial = dS K_j                                        -> TMEM -> fp32 vector atomics
 // TMEM: S 128 + dP 128 + dV 64 + dK 64 + dQ 64 = 448 of 512 columns.
-constexpr uint32_t FAB_SMEM = FA_TILE_BYTES * (2 + 4) + 4 * FA_TILE_BYTES /*P, dS*/ + 256;
+constexpr uint32_t FAB_DQ_BYTES = FA_BLOCK * FA_D * 4;   // fp32 dQ tile staged for the bulk reduce-add
+constexpr uint32_t FAB_SMEM = FA_TILE_BYTES * (2 + 4) + 4 * FA_TILE_BYTES /*P, dS*/ + FAB_DQ_BYTES + 256;
 
 struct FaBwdParams {
     int B, T, H;
@@ -609,6 +610,7 @@ struct FaBwdParams {
     float* dq_acc;        // [B, H, T, D] fp32, zeroed
     __nv_bfloat16* dqkv;  // [B, T, 3, H, D]
     float scale, scale_log2e;
+    int trace;
 };
 
 __device__ __forceinline__ uint32_t fab_idesc(int n, bool a_mn, bool b_mn) {
@@ -632,7 +634,8 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
     uint8_t* s_do = s_q + 2 * FA_TILE_BYTES;      // dO_i, 2 stages
     uint8_t* s_p = s_do + 2 * FA_TILE_BYTES;      // P   [128 q x 128 keys] as two swizzled blocks
     uint8_t* s_ds = s_p + 2 * FA_TILE_BYTES;      // dS  same layout
-    uint64_t* bars = reinterpret_cast<uint64_t*>(s_ds + 2 * FA_TILE_BYTES);
+    uint8_t* s_dq = s_ds + 2 * FA_TILE_BYTES;     // dQ_i partial, fp32 [128][64], 16-byte chunks XOR-swizzled per row
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_dq + FAB_DQ_BYTES);
     uint64_t* kv_full = bars;         // 1
     uint64_t* qdo_full = bars + 1;    // 2
     uint64_t* qdo_empty = bars + 3;   // 2
@@ -721,6 +724,12 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
             mbar_wait(pds_full, (uint32_t)(it & 1));   // P and dS are in smem, S/dP consumed
             tc_fence_after();
             if (elect_one()) {
+                // dQ first: the softmax warps only wait for it (dV / dK accumulate in TMEM until the end)
+#pragma unroll
+                for (int kk = 0; kk < FA_BLOCK / 16; ++kk)     // reduce over the 128 keys
+                    umma_bf16(t_dq, ds_k + (uint64_t)((kk >> 2) * TILE16 + (kk & 3) * 2), k_mn + (uint64_t)(kk * 128),
+                              id_dq, kk != 0 ? 1u : 0u);
+                umma_commit(dq_full);
 #pragma unroll
                 for (int kk = 0; kk < FA_BLOCK / 16; ++kk) {   // reduce over the 128 query rows
                     // A^T views of P / dS: [q rows, keys] read MN-major (64-key chunks 16 KB apart)
@@ -729,11 +738,6 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
                     umma_bf16(t_dk, ds_mn + (uint64_t)(kk * 128), q_mn0 + so + (uint64_t)(kk * 128), id_kv,
                               (it | kk) != 0 ? 1u : 0u);
                 }
-#pragma unroll
-                for (int kk = 0; kk < FA_BLOCK / 16; ++kk)     // reduce over the 128 keys
-                    umma_bf16(t_dq, ds_k + (uint64_t)((kk >> 2) * TILE16 + (kk & 3) * 2), k_mn + (uint64_t)(kk * 128),
-                              id_dq, kk != 0 ? 1u : 0u);
-                umma_commit(dq_full);
                 umma_commit(&qdo_empty[st]);
                 if (it == niter - 1) umma_commit(dkv_full);
             }
@@ -755,8 +759,10 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
             const int64_t qrow = bh * p.T + (int64_t)i * FA_BLOCK + r;
             const float lse2 = p.lse[qrow] * 1.4426950408889634f;
             const float dlt = p.delta[qrow];
+            FA_TRACE(it, 0);
             mbar_wait(sdp_full, (uint32_t)(it & 1));
             tc_fence_after();
+            FA_TRACE(it, 1);
             auto chunk = [&](int c, auto is_diag) {
                 constexpr bool DIAG = decltype(is_diag)::value;
                 uint32_t vs[32], vd[32];
@@ -785,25 +791,43 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
             };
             if (diag) { chunk(2 * half, std::true_type{}); chunk(2 * half + 1, std::true_type{}); }
             else { chunk(2 * half, std::false_type{}); chunk(2 * half + 1, std::false_type{}); }
+            FA_TRACE(it, 2);
             fence_proxy_async();
             tc_fence_before();
             mbar_arrive(pds_full);
             // dQ_i partial -> fp32 accumulator (other key blocks add to the same rows)
             mbar_wait(dq_full, (uint32_t)(it & 1));
             tc_fence_after();
-            float* dq = p.dq_acc + qrow * FA_D + half * 32;
+            FA_TRACE(it, 3);
+            // dQ_i partial -> staged in shared memory -> ONE bulk reduce-add (cp.reduce.async.bulk) into
+            // the fp32 accumulator: the 128 x 64 block is 32 KB contiguous in dq_acc [B, H, T, D].  Round 1
+            // issued 8 vector atomics per thread here: 1900 of a step's 6250 cycles.  The staging rows
+            // are XOR-swizzled in 16-byte chunks (conflict-free stores); dq_acc keeps that permutation
+            // and fa_dq_convert_kernel undoes it.
             {
                 uint32_t v[32];
                 tmem_ld_32x32(t_dq + lane_addr + half * 32, v);
+                if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // previous tile has left s_dq
                 tmem_ld_wait();
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                uint8_t* row = s_dq + r * 256 + half * 128;
 #pragma unroll
-                for (int e = 0; e < 32; e += 4)
-                    atomicAdd(reinterpret_cast<float4*>(dq + e),
-                              make_float4(__uint_as_float(v[e]), __uint_as_float(v[e + 1]), __uint_as_float(v[e + 2]),
-                                          __uint_as_float(v[e + 3])));
+                for (int c = 0; c < 8; ++c)
+                    *reinterpret_cast<uint4*>(row + ((c ^ (r & 7)) << 4)) = make_uint4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+                fence_proxy_async();
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                if (threadIdx.x == 0) {
+                    float* dst = p.dq_acc + (bh * p.T + (int64_t)i * FA_BLOCK) * FA_D;
+                    asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst),
+                                 "r"(smem_u32(s_dq)), "r"(FAB_DQ_BYTES)
+                                 : "memory");
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
             }
             tc_fence_before();
+            FA_TRACE(it, 4);
         }
+        if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // last dQ tile has landed
         // dV_j, dK_j: thread r owns key row k0 + r
         mbar_wait(dkv_full, 0);
         tc_fence_after();
@@ -873,7 +897,10 @@ __global__ void __launch_bounds__(256) fa_dq_convert_kernel(const float* __restr
         const int t = (int)(r % T); r /= T;
         const int hh = (int)(r % H);
         const int bb = (int)(r / H);
-        const float4 a = reinterpret_cast<const float4*>(dq_acc)[idx * 2], c = reinterpret_cast<const float4*>(dq_acc)[idx * 2 + 1];
+        // the backward kernel stores each 128-byte half row with its 16-byte chunks XOR-swizzled by (t & 7)
+        const int q0 = 2 * v, q1 = 2 * v + 1, sw = t & 7;
+        const float4* rowp = reinterpret_cast<const float4*>(dq_acc) + (idx / (FA_D / 8)) * (FA_D / 4);
+        const float4 a = rowp[(q0 & 8) | ((q0 & 7) ^ sw)], c = rowp[(q1 & 8) | ((q1 & 7) ^ sw)];
         __nv_bfloat16* dst = dqkv + (((int64_t)bb * T + t) * 3 + 0) * ((int64_t)H * FA_D) + (int64_t)hh * FA_D + v * 8;
         *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(c.x, c.y), pack_bf16(c.z, c.w));
     }
@@ -983,7 +1010,8 @@ extern "C" int b200_flash_attn_bwd(const void* qkv, const void* out, const void*
     if (blocks > 148 * 8) blocks = 148 * 8;
     fa_delta_kernel<<<blocks, 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, B, T, H);
     const float scale = 1.f / sqrtf((float)D);
-    FaBwdParams p{B, T, H, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, scale, scale * 1.4426950408889634f};
+    static const int trace = getenv("B200DDP_FA_TRACE_BWD") != nullptr;
+    FaBwdParams p{B, T, H, lse, delta, dq_acc, (__nv_bfloat16*)dqkv, scale, scale * 1.4426950408889634f, trace};
     dim3 grid((unsigned)H, (unsigned)B, (unsigned)(T / FA_BLOCK));
     flash_attn_bwd_kernel<<<grid, FAB_THREADS, FAB_SMEM, s>>>(map_qkv, map_do, p);
     fa_dq_convert_kernel<<<148 * 8, 256, 0, s>>>(dq_acc, (__nv_bfloat16*)dqkv, B, T, H);
