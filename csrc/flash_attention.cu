@@ -705,11 +705,10 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
         const uint64_t ds_mn = umma_smem_desc(smem_u32(s_ds), 16384, 1024);   // dS^T view (dK)
         const uint64_t ds_k = umma_smem_desc(smem_u32(s_ds), 16, 1024);       // dS K-major (dQ)
         mbar_wait(kv_full, 0);
-        for (int it = 0; it < niter; ++it) {
+        auto issue_s_dp = [&](int it) {      // S = Q_i K_j^T and dP = dO_i V_j^T of iteration `it`
             const int st = it & 1;
-            const uint32_t par2 = (uint32_t)((it >> 1) & 1);
             const uint64_t so = (uint64_t)(st * TILE16);
-            mbar_wait(&qdo_full[st], par2);
+            mbar_wait(&qdo_full[st], (uint32_t)((it >> 1) & 1));
             tc_fence_after();
             if (elect_one()) {
 #pragma unroll
@@ -721,15 +720,27 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
                 umma_commit(sdp_full);
             }
             __syncwarp();
+        };
+        issue_s_dp(0);
+        for (int it = 0; it < niter; ++it) {
+            const int st = it & 1;
+            const uint32_t par2 = (uint32_t)((it >> 1) & 1);
+            const uint64_t so = (uint64_t)(st * TILE16);
             mbar_wait(pds_full, (uint32_t)(it & 1));   // P and dS are in smem, S/dP consumed
             tc_fence_after();
+            // Tensor-pipe order: dQ (the softmax warps wait for it), then the NEXT block's S and dP (they wait
+            // for those next), and only then dV / dK, which nobody waits for until the last iteration and
+            // which therefore run under the next block's softmax arithmetic.
             if (elect_one()) {
-                // dQ first: the softmax warps only wait for it (dV / dK accumulate in TMEM until the end)
 #pragma unroll
                 for (int kk = 0; kk < FA_BLOCK / 16; ++kk)     // reduce over the 128 keys
                     umma_bf16(t_dq, ds_k + (uint64_t)((kk >> 2) * TILE16 + (kk & 3) * 2), k_mn + (uint64_t)(kk * 128),
                               id_dq, kk != 0 ? 1u : 0u);
                 umma_commit(dq_full);
+            }
+            __syncwarp();
+            if (it + 1 < niter) issue_s_dp(it + 1);
+            if (elect_one()) {
 #pragma unroll
                 for (int kk = 0; kk < FA_BLOCK / 16; ++kk) {   // reduce over the 128 query rows
                     // A^T views of P / dS: [q rows, keys] read MN-major (64-key chunks 16 KB apart)
