@@ -46,43 +46,16 @@ __device__ __forceinline__ float fa_exp2(float x) {   // MUFU ex2; inputs are <=
     return y;
 }
 
-// exp2 on the FMA pipe.  ncu of the forward: the XU pipe (MUFU) is the busiest unit by far (51 % of
-// its peak over the whole launch, FMA 8 %) — on B200 the softmax of a 128 x 128 score tile is bound by
-// MUFU.EX2, not by the tensor core.  So a share of the exponentials is computed arithmetically:
-// round-to-nearest split x = n + f with the 1.5 * 2^23 trick, 2^f on [-0.5, 0.5] by a cubic
-// (max relative error 1.0e-4, far below bf16's 3.9e-3), 2^n by adding n to the exponent field.
-__device__ __forceinline__ float fa_exp2_poly(float x) {
-    x = fmaxf(x, -125.f);
-    const float t = x + 12582912.f;
-    const float f = x - (t - 12582912.f);
-    float pl = fmaf(f, 0.05592203512787819f, 0.24264007806777954f);
-    pl = fmaf(pl, f, 0.6931210160255432f);
-    pl = fmaf(pl, f, 0.9999244809150696f);
-    return __int_as_float(__float_as_int(pl) + (__float_as_int(t) << 23));
-}
+// Tried and dropped (B200, ncu + in-kernel step traces, profiles/flash_attention_r2.md): computing a
+// share of the exponentials with a cubic on the FMA pipe (the FA4 recipe) and packing bf16 on the ALU
+// pipe instead of F2FP.  Both made the kernels slower: a polynomial exp2 costs 6-7 FMA-pipe
+// instructions at 2 cycles each against 8 cycles of MUFU.EX2 per warp, so the softmax is fastest with
+// every exponential on MUFU and sits near that pipe's rate (16 per clock per SM).
 __device__ __forceinline__ float fa_max3(float a, float b, float c) {
     float r;
     asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
     return r;
 }
-// Two bf16 from two fp32 on the ALU pipe (2 IADD + 1 PRMT): round half away from zero instead of
-// F2FP's round-to-nearest-even (they differ only on exact ties).  On B200 F2FP.BF16.PACK_AB issues
-// to the same quarter-rate XU pipe as MUFU (ncu: XU 71 % busy over the whole backward launch with
-// MUFU.EX2 + F2FP as its only users), so the conversions were costing as much as the exponentials.
-__device__ __forceinline__ uint32_t pack_bf16_alu(float lo, float hi) {
-    return __byte_perm(__float_as_uint(lo) + 0x8000u, __float_as_uint(hi) + 0x8000u, 0x7632);
-}
-// Of every 8 consecutive exponentials, this many take the polynomial, the rest MUFU, chosen so that
-// the XU pipe (16 cycles per warp instruction) and the FMA pipe (2 cycles per instruction, ~6 for a
-// polynomial, plus the rest of the row arithmetic) finish together: forward 4 of 8, backward (more
-// FMA work per element for dS) 2 of 8.
-#ifndef FA_POLY_OF_8
-#define FA_POLY_OF_8 4
-#endif
-#ifndef FAB_POLY_OF_8
-#define FAB_POLY_OF_8 2
-#endif
-
 __device__ __forceinline__ uint32_t fa_idesc(int n, bool b_mn) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(b_mn ? 1 : 0) << 16) | ((uint32_t)(n >> 3) << 17) |
            ((uint32_t)(128 >> 4) << 24);
@@ -548,14 +521,14 @@ flash_attn_fwd2_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FaPara
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
                         const float arg = fmaf(__uint_as_float(v[8 * q + e]), p.scale_log2e, -m);
-                        const float x = (e < FA_POLY_OF_8) ? fa_exp2_poly(arg) : fa_exp2(arg);
+                        const float x = fa_exp2(arg);
                         pv[e] = (!DIAG || c32 * 32 + 8 * q + e <= r) ? x : 0.f;
                     }
                     // pairwise: no 128-long chain of dependent additions
                     psum += ((pv[0] + pv[1]) + (pv[2] + pv[3])) + ((pv[4] + pv[5]) + (pv[6] + pv[7]));
                     const int vec = (c32 & 1) * 4 + q;
                     *reinterpret_cast<uint4*>(blk + ((vec ^ (r & 7)) << 4)) =
-                        make_uint4(pack_bf16_alu(pv[0], pv[1]), pack_bf16_alu(pv[2], pv[3]), pack_bf16_alu(pv[4], pv[5]), pack_bf16_alu(pv[6], pv[7]));
+                        make_uint4(pack_bf16(pv[0], pv[1]), pack_bf16(pv[2], pv[3]), pack_bf16(pv[4], pv[5]), pack_bf16(pv[6], pv[7]));
                 }
             };
             if (diag) {
@@ -800,16 +773,16 @@ flash_attn_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
                         const float arg = fmaf(__uint_as_float(vs[8 * t + e]), p.scale_log2e, -lse2);
-                        const float pe = (e < FAB_POLY_OF_8) ? fa_exp2_poly(arg) : fa_exp2(arg);
+                        const float pe = fa_exp2(arg);
                         const bool ok = !DIAG || c * 32 + 8 * t + e <= r;   // key column <= query row
                         pv[e] = ok ? pe : 0.f;
                         dv[e] = ok ? pe * (__uint_as_float(vd[8 * t + e]) - dlt) * p.scale : 0.f;
                     }
                     const int off = (((c & 1) * 4 + t) ^ (r & 7)) << 4;
                     *reinterpret_cast<uint4*>(bp + off) =
-                        make_uint4(pack_bf16_alu(pv[0], pv[1]), pack_bf16_alu(pv[2], pv[3]), pack_bf16_alu(pv[4], pv[5]), pack_bf16_alu(pv[6], pv[7]));
+                        make_uint4(pack_bf16(pv[0], pv[1]), pack_bf16(pv[2], pv[3]), pack_bf16(pv[4], pv[5]), pack_bf16(pv[6], pv[7]));
                     *reinterpret_cast<uint4*>(bd + off) =
-                        make_uint4(pack_bf16_alu(dv[0], dv[1]), pack_bf16_alu(dv[2], dv[3]), pack_bf16_alu(dv[4], dv[5]), pack_bf16_alu(dv[6], dv[7]));
+                        make_uint4(pack_bf16(dv[0], dv[1]), pack_bf16(dv[2], dv[3]), pack_bf16(dv[4], dv[5]), pack_bf16(dv[6], dv[7]));
                 }
             };
             if (diag) { chunk(2 * half, std::true_type{}); chunk(2 * half + 1, std::true_type{}); }
