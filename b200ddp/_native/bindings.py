@@ -47,6 +47,9 @@ class GemmDesc(C.Structure):
         ("tile_m", C.c_int),
         ("split_k", C.c_int),
         ("cta_pair", C.c_int),
+        ("a_conv", C.c_int), ("b_conv", C.c_int),
+        ("conv_n", C.c_int), ("conv_h", C.c_int), ("conv_w", C.c_int), ("conv_c", C.c_int),
+        ("conv_r", C.c_int), ("conv_s", C.c_int), ("conv_stride", C.c_int), ("conv_pad", C.c_int),
     ]
 
 
@@ -271,12 +274,16 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, M: int, N: int,
          loss_out: Optional[torch.Tensor] = None, loss_scale: float = 1.0,
          ce_write_grad: bool = True, tile_n: int = 0, max_ctas: int = 0, split_k: int = 0,
          batch=None, causal: int = 0, lda=None, ldb=None, ldd=None, tile_m: int = 0,
-         cta_pair: int = 0) -> None:
+         cta_pair: int = 0, a_conv=None, b_conv=None) -> None:
     """out[M,N] = epilogue(A @ B^T).  A is [M,K] (K-major) or stored [K,M] (a_mn_major);
     B is [N,K] or stored [K,N] (b_mn_major).  Strides are taken from the tensors."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
     assert a.stride(-1) == 1 and b.stride(-1) == 1 and out.stride(-1) == 1
-    if batch is None:
+    conv = a_conv if a_conv is not None else b_conv     # (R, S, stride, pad): the operand is an NHWC activation
+    if conv is not None:
+        act = a if a_conv is not None else b
+        assert act.dim() == 4 and act.is_contiguous(), "implicit convolution wants a contiguous NHWC tensor"
+    elif batch is None:
         assert a.dim() == 2 and b.dim() == 2 and out.dim() == 2
     assert out.dtype in (torch.bfloat16, torch.float32)
     if bias is not None:
@@ -285,6 +292,14 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, M: int, N: int,
     d.M, d.N, d.K = M, N, K
     d.A, d.lda, d.a_mn_major = a.data_ptr(), (lda if lda is not None else a.stride(0)), int(a_mn_major)
     d.B, d.ldb, d.b_mn_major = b.data_ptr(), (ldb if ldb is not None else b.stride(0)), int(b_mn_major)
+    if conv is not None:
+        d.a_conv, d.b_conv = int(a_conv is not None), int(b_conv is not None)
+        d.conv_n, d.conv_h, d.conv_w, d.conv_c = act.shape
+        d.conv_r, d.conv_s, d.conv_stride, d.conv_pad = conv
+        if a_conv is not None:
+            d.lda = 0
+        else:
+            d.ldb = 0
     d.D, d.ldd, d.d_fp32 = out.data_ptr(), (ldd if ldd is not None else out.stride(0)), int(out.dtype == torch.float32)
     if batch is not None:
         # batch = (n_inner, n_outer, (a_si, a_so), (b_si, b_so), (d_si, d_so)), strides in elements

@@ -79,7 +79,39 @@ struct GemmParams {
     int causal;                            // 0 none, 1 skip tiles above the diagonal, 2 k < m0+BM, 3 k >= m0
     int k_splits, kb_per_split;  // split-K: tile index also selects a K slice; partials are
                                  // combined with vector atomics into a zeroed fp32 D
+    // Implicit-GEMM convolution: the operand is an NHWC activation read through a TMA im2col-mode
+    // tensor map (rows = output pixels, columns = (filter tap, channel)); nothing is gathered in HBM.
+    int a_conv, b_conv;
+    int conv_cblocks, conv_S, conv_taps, conv_Q, conv_PQ, conv_stride, conv_pad, conv_C;
 };
+
+// (image, top-left input row, top-left input column) of output pixel `m` — the im2col coordinate of the
+// first row of a tile; the TMA unit walks the following output pixels itself.
+__device__ __forceinline__ void conv_origin(const GemmParams& p, int m, int& n, int& h, int& w) {
+    n = m / p.conv_PQ;
+    const int rem = m - n * p.conv_PQ;
+    const int pp = rem / p.conv_Q;
+    h = pp * p.conv_stride - p.conv_pad;
+    w = (rem - pp * p.conv_Q) * p.conv_stride - p.conv_pad;
+}
+// column block `nb` (64 columns of the im2col matrix) -> channel offset and filter tap (s, r); blocks
+// past the last tap read channel C.. (out of range: zero-filled, full byte count)
+__device__ __forceinline__ void conv_tap(const GemmParams& p, int nb, int& c, uint16_t& fs, uint16_t& fr) {
+    const int tap = nb / p.conv_cblocks;
+    c = (nb - tap * p.conv_cblocks) * 64;
+    if (tap >= p.conv_taps) { c = p.conv_C; fs = 0; fr = 0; return; }
+    const int r = tap / p.conv_S;
+    fr = (uint16_t)r;
+    fs = (uint16_t)(tap - r * p.conv_S);
+}
+__device__ __forceinline__ void tma_load_im2col(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c, int w,
+                                                int h, int n, uint16_t off_w, uint16_t off_h) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+        : "memory");
+}
 
 template <int BN> struct StagesFor { static constexpr int value = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8); };
 
@@ -634,14 +666,30 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
                     uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
                     uint8_t* sb = smem_b + stage * B_STAGE_BYTES;
                     const int k0 = kb * BK;
-                    if (!p.a_mn) {
+                    if (p.a_conv) {          // rows = 128 output pixels from m0, k-block = 64 channels of one tap
+                        int cn, ch, cw, cc;
+                        uint16_t fs, fr;
+                        conv_origin(p, m0, cn, ch, cw);
+                        conv_tap(p, kb, cc, fs, fr);
+                        tma_load_im2col(sa, &tma_a, &full_bar[stage], cc, cw, ch, cn, fs, fr);
+                    } else if (!p.a_mn) {
                         tma_load_4d(sa, &tma_a, &full_bar[stage], k0, m0, t.hb, t.bb);
                     } else {
 #pragma unroll
                         for (int j = 0; j < BM / 64; ++j)
                             tma_load_4d(sa + j * 8192, &tma_a, &full_bar[stage], m0 + j * 64, k0, t.hb, t.bb);
                     }
-                    if (!p.b_mn) {
+                    if (p.b_conv) {          // MN-major B: 64-column chunks of the im2col matrix x 64 pixels from k0
+                        int cn, ch, cw;
+                        conv_origin(p, k0, cn, ch, cw);
+#pragma unroll
+                        for (int j = 0; j < (BN >= 64 ? BN / 64 : 1); ++j) {
+                            int cc;
+                            uint16_t fs, fr;
+                            conv_tap(p, n0 / 64 + j, cc, fs, fr);
+                            tma_load_im2col(sb + j * 8192, &tma_b, &full_bar[stage], cc, cw, ch, cn, fs, fr);
+                        }
+                    } else if (!p.b_mn) {
                         tma_load_4d(sb, &tma_b, &full_bar[stage], k0, n0, t.hb, t.bb);
                     } else {
 #pragma unroll
@@ -958,6 +1006,14 @@ __device__ __forceinline__ void tma_load_4d_pair(void* smem_dst, const CUtensorM
         "l"(reinterpret_cast<uint64_t>(map)), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
         : "memory");
 }
+__device__ __forceinline__ void tma_load_im2col_pair(void* smem_dst, const CUtensorMap* map, uint32_t leader_bar, int c,
+                                                     int w, int h, int n, uint16_t off_w, uint16_t off_h) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(smem_u32(smem_dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(leader_bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+        : "memory");
+}
 __device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
                                                uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -1044,7 +1100,13 @@ gemm_kernel_2sm(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
                     uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
                     uint8_t* sb = smem_b + stage * B_HALF_BYTES;
                     const int k0 = kb * BK;
-                    if (!p.a_mn) {
+                    if (p.a_conv) {
+                        int cn, ch, cw, cc;
+                        uint16_t fs, fr;
+                        conv_origin(p, m0, cn, ch, cw);
+                        conv_tap(p, kb, cc, fs, fr);
+                        tma_load_im2col_pair(sa, &tma_a, lbar, cc, cw, ch, cn, fs, fr);
+                    } else if (!p.a_mn) {
                         tma_load_4d_pair(sa, &tma_a, lbar, k0, m0, 0, 0);
                     } else {
 #pragma unroll
@@ -1169,6 +1231,44 @@ static int make_map(CUtensorMap* map, const void* base, int64_t inner, int64_t o
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     B200_REQUIRE(r == CUDA_SUCCESS, "gemm: cuTensorMapEncodeTiled failed (%d) inner=%lld outer=%lld ld=%lld box=%dx%d",
                  (int)r, (long long)inner, (long long)outer, (long long)ld, box_inner, box_outer);
+    return 0;
+}
+
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeIm2colFn get_im2col_fn() {
+    static EncodeIm2colFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeIm2colFn>(ptr);
+    });
+    return fn;
+}
+
+// im2col-mode tensor map over an NHWC bf16 activation: one load fetches `pixels` consecutive output
+// pixels (walking q, then p, then the image) x 64 channels at filter-tap offset (s, r), zero-filling
+// the padding halo.  Bounding box per the driver's convention: lower corner = -pad, upper corner =
+// pad - (filter extent - 1); traversal stride = convolution stride.
+static int make_im2col_map(CUtensorMap* map, const void* base, const b200_gemm_desc* d, int pixels) {
+    EncodeIm2colFn enc = get_im2col_fn();
+    B200_REQUIRE(enc != nullptr, "gemm: cuTensorMapEncodeIm2col is unavailable from this driver");
+    cuuint64_t dims[4] = {(cuuint64_t)d->conv_c, (cuuint64_t)d->conv_w, (cuuint64_t)d->conv_h, (cuuint64_t)d->conv_n};
+    cuuint64_t strides[3] = {(cuuint64_t)d->conv_c * 2, (cuuint64_t)d->conv_w * d->conv_c * 2,
+                             (cuuint64_t)d->conv_h * d->conv_w * d->conv_c * 2};
+    int lower[2] = {-d->conv_pad, -d->conv_pad};
+    int upper[2] = {d->conv_pad - (d->conv_s - 1), d->conv_pad - (d->conv_r - 1)};
+    cuuint32_t estr[4] = {1, (cuuint32_t)d->conv_stride, (cuuint32_t)d->conv_stride, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower, upper,
+                     64, (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    B200_REQUIRE(r == CUDA_SUCCESS, "gemm: cuTensorMapEncodeIm2col failed (%d) n=%d h=%d w=%d c=%d r=%d s=%d stride=%d pad=%d",
+                 (int)r, d->conv_n, d->conv_h, d->conv_w, d->conv_c, d->conv_r, d->conv_s, d->conv_stride, d->conv_pad);
     return 0;
 }
 
@@ -1321,11 +1421,25 @@ static int select_kernel(const b200_gemm_desc* d, int sms, GemmPlan* out) {
     //                                      single-buffered accumulators expose the epilogue
     //   256xBN per SM pair (cta_group::2)  everything else: double-buffered accumulators, and each SM
     //                                      stages only half of B
-    const bool big_cfg = fast_cfg && nbi * nbo == 1 && !d->causal;
+    const bool conv = d->a_conv || d->b_conv;
+    if (conv) {
+        B200_REQUIRE(nbi * nbo == 1 && !d->causal, "gemm: implicit convolution operands are not batched");
+        B200_REQUIRE(!(d->a_conv && d->b_conv), "gemm: only one operand can be the im2col view");
+        B200_REQUIRE(d->conv_c > 0 && d->conv_c % 64 == 0, "gemm: implicit convolution needs channels %% 64 == 0 (got %d)", d->conv_c);
+        B200_REQUIRE(d->conv_r >= 1 && d->conv_s >= 1 && d->conv_stride >= 1 && d->conv_pad >= 0 && d->conv_n > 0 &&
+                     d->conv_h > 0 && d->conv_w > 0, "gemm: bad convolution geometry");
+        const int P = (d->conv_h + 2 * d->conv_pad - d->conv_r) / d->conv_stride + 1;
+        const int Q = (d->conv_w + 2 * d->conv_pad - d->conv_s) / d->conv_stride + 1;
+        const int64_t pix = (int64_t)d->conv_n * P * Q, kk = (int64_t)d->conv_r * d->conv_s * d->conv_c;
+        if (d->a_conv) B200_REQUIRE(d->M == pix && d->K == kk && !d->a_mn_major, "gemm: a_conv wants M = N*P*Q (%lld) and K = R*S*C (%lld)", (long long)pix, (long long)kk);
+        if (d->b_conv) B200_REQUIRE(d->N == kk && d->K == pix, "gemm: b_conv wants N = R*S*C (%lld) and K = N*P*Q (%lld)", (long long)kk, (long long)pix);
+    }
+    // (the im2col view as B operand is read by the one-SM kernels only)
+    const bool big_cfg = fast_cfg && nbi * nbo == 1 && !d->causal && !d->b_conv;
     const int64_t t2 = (int64_t)((d->M + BM2 - 1) / BM2) * ((d->N + 255) / 256);
     bool m256 = big_cfg && (d->tile_n == 0 || d->tile_n == 256) &&
-                (d->tile_m == 256 || (d->tile_m == 0 && d->tile_n == 0 && d->cta_pair != 1 && !m256_off &&
-                                      d->M >= 512 && d->K >= 4096 && t2 >= sms));
+                !conv && (d->tile_m == 256 || (d->tile_m == 0 && d->tile_n == 0 && d->cta_pair != 1 && !m256_off &&
+                                                d->M >= 512 && d->K >= 4096 && t2 >= sms));
     int pair_bn = 0;   // 0: not the pair kernel
     if (big_cfg && !m256 && d->tile_m == 0 && d->M > 128 && d->N > 64 &&
         (d->cta_pair == 1 || (d->cta_pair == 0 && d->tile_n == 0 && !pair_off))) {
@@ -1340,7 +1454,7 @@ static int select_kernel(const b200_gemm_desc* d, int sms, GemmPlan* out) {
                  "gemm: tile_m 256 needs tile_n 256, a non-batched problem and a light epilogue with bf16 output");
     int bn = pair ? pair_bn : (m256 ? 256 : (d->tile_n ? d->tile_n : pick_tile_n(d, sms)));
     B200_REQUIRE(bn == 16 || bn == 32 || bn == 64 || bn == 128 || bn == 256, "gemm: tile_n %d unsupported", bn);
-    B200_REQUIRE(!(d->b_mn_major && bn < 64), "gemm: MN-major B needs tile_n >= 64");
+    B200_REQUIRE(!((d->b_mn_major || d->b_conv) && bn < 64), "gemm: MN-major B needs tile_n >= 64");
     if (d->epilogue == B200_EPI_SOFTMAX_CE) {
         B200_REQUIRE(d->N <= bn && bn <= 32, "gemm: fused cross-entropy needs N <= 32 (got %d)", d->N);
         B200_REQUIRE(d->targets != nullptr, "gemm: fused cross-entropy needs targets");
@@ -1366,8 +1480,8 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
     }
     B200_REQUIRE(d && d->A && d->B && d->D, "gemm: null pointer");
     B200_REQUIRE(d->M > 0 && d->N > 0 && d->K > 0, "gemm: bad shape %dx%dx%d", d->M, d->N, d->K);
-    B200_REQUIRE((d->lda % 8) == 0 && (d->ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements (got %lld, %lld)",
-                 (long long)d->lda, (long long)d->ldb);
+    B200_REQUIRE((d->a_conv || (d->lda % 8) == 0) && (d->b_conv || (d->ldb % 8) == 0),
+                 "gemm: lda/ldb must be multiples of 8 elements (got %lld, %lld)", (long long)d->lda, (long long)d->ldb);
     B200_REQUIRE(((uintptr_t)d->A % 16) == 0 && ((uintptr_t)d->B % 16) == 0, "gemm: A/B must be 16-byte aligned");
     const int sms = sm_count();
     const int nbi = d->batch_inner > 1 ? d->batch_inner : 1, nbo = d->batch_outer > 1 ? d->batch_outer : 1;
@@ -1379,16 +1493,25 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
 
     CUtensorMap ma, mb;
     int rc;
-    if (!d->a_mn_major) rc = make_map(&ma, d->A, d->K, d->M, d->lda, BK, m256 ? BM2 : BM, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
+    if (d->a_conv) rc = make_im2col_map(&ma, d->A, d, BM);   // 128 output pixels x 64 channels per load
+    else if (!d->a_mn_major) rc = make_map(&ma, d->A, d->K, d->M, d->lda, BK, m256 ? BM2 : BM, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
     else rc = make_map(&ma, d->A, d->M, d->K, d->lda, 64, BK, nbi, d->a_stride_inner, nbo, d->a_stride_outer);
     if (rc) return rc;
-    if (!d->b_mn_major) rc = make_map(&mb, d->B, d->K, d->N, d->ldb, BK, pair ? bn / 2 : bn, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
+    if (d->b_conv) rc = make_im2col_map(&mb, d->B, d, BK);   // 64 pixels (one k-block) x 64 channels per load
+    else if (!d->b_mn_major) rc = make_map(&mb, d->B, d->K, d->N, d->ldb, BK, pair ? bn / 2 : bn, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
     else rc = make_map(&mb, d->B, d->N, d->K, d->ldb, 64, BK, nbi, d->b_stride_inner, nbo, d->b_stride_outer);
     if (rc) return rc;
 
     GemmParams p{};
     p.M = d->M; p.N = d->N; p.K = d->K;
-    p.a_mn = d->a_mn_major; p.b_mn = d->b_mn_major;
+    p.a_mn = d->a_mn_major; p.b_mn = d->b_mn_major || d->b_conv;
+    p.a_conv = d->a_conv; p.b_conv = d->b_conv;
+    if (d->a_conv || d->b_conv) {
+        const int P = (d->conv_h + 2 * d->conv_pad - d->conv_r) / d->conv_stride + 1;
+        const int Q = (d->conv_w + 2 * d->conv_pad - d->conv_s) / d->conv_stride + 1;
+        p.conv_cblocks = d->conv_c / 64; p.conv_S = d->conv_s; p.conv_taps = d->conv_r * d->conv_s;
+        p.conv_Q = Q; p.conv_PQ = P * Q; p.conv_stride = d->conv_stride; p.conv_pad = d->conv_pad; p.conv_C = d->conv_c;
+    }
     p.D = d->D; p.ldd = d->ldd; p.d_fp32 = d->d_fp32;
     p.bias = d->bias; p.epilogue = d->epilogue;
     p.aux = (const __nv_bfloat16*)d->aux; p.ldaux = d->ldaux;
@@ -1402,7 +1525,7 @@ extern "C" int b200_gemm(const b200_gemm_desc* d, void* stream) {
     p.num_k_blocks = (d->K + BK - 1) / BK;
     // instruction descriptor: fp32 accumulate, bf16 A/B, majors, N>>3, M>>4
     p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(d->a_mn_major ? 1 : 0) << 15) |
-              ((uint32_t)(d->b_mn_major ? 1 : 0) << 16) | ((uint32_t)(bn >> 3) << 17) |
+              ((uint32_t)((d->b_mn_major || d->b_conv) ? 1 : 0) << 16) | ((uint32_t)(bn >> 3) << 17) |
               ((uint32_t)((pair ? 256 : BM) >> 4) << 24);
     p.batch_inner = nbi; p.batch_outer = nbo;
     p.d_stride_inner = d->d_stride_inner; p.d_stride_outer = d->d_stride_outer;

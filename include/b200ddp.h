@@ -173,6 +173,16 @@ typedef struct {
                                                  * cta_group::2, one 256x256 tile per SM pair; needs a
                                                  * non-batched problem, a light epilogue and bf16 D);
                                                  * -1 = never */
+    /* Implicit-GEMM convolution: one operand is the im2col VIEW of an NHWC bf16 activation
+     * [conv_n, conv_h, conv_w, conv_c] (conv_c a multiple of 64), read through a TMA im2col-mode tensor map
+     * — nothing is gathered in memory.  Row m of the view is output pixel (n, p, q), column
+     * k = (r * conv_s + s) * conv_c + c.
+     *   a_conv: A (pointer to the activation) is the view: M = N*P*Q, K = R*S*C  (forward; B = weights
+     *           laid out [Cout, R*S*C])
+     *   b_conv: B is the view read MN-major: N = R*S*C, K = N*P*Q  (weight gradient with A = dY^T)
+     * ref: BASELINE.json config 3 (ResNet-50); the reference's baseline runs cuDNN convolutions. */
+    int a_conv, b_conv;
+    int conv_n, conv_h, conv_w, conv_c, conv_r, conv_s, conv_stride, conv_pad;
 } b200_gemm_desc;
 
 int b200_gemm(const b200_gemm_desc* d, void* stream);

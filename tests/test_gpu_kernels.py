@@ -859,6 +859,40 @@ def test_resnet50_engine_step():
     assert torch.isfinite(loss)
 
 
+@pytest.mark.parametrize("N,H,W,Cin,Cout,k,stride,pad", [
+    (4, 56, 56, 64, 64, 3, 1, 1),       # ResNet-50 3x3
+    (3, 28, 30, 128, 128, 3, 2, 1),     # strided 3x3, non-square, ragged tile of pixels
+    (2, 56, 56, 256, 512, 1, 2, 0),     # strided 1x1 (downsample branch)
+    (2, 14, 14, 256, 256, 3, 1, 1),     # small feature map: a tile of 128 pixels spans rows and images
+])
+def test_implicit_gemm_convolution(B, N, H, W, Cin, Cout, k, stride, pad):
+    """TMA im2col-mode operands against fp32 torch convolutions: forward (A = im2col view of the NHWC
+    activation) and weight gradient (B = the same view, MN-major), no gathered matrix in memory."""
+    torch.manual_seed(31)
+    dev = torch.device("cuda")
+    x = bf(torch.randn(N, Cin, H, W, device=dev))
+    w = bf(torch.randn(Cout, Cin, k, k, device=dev) * 0.1)
+    xh = x.permute(0, 2, 3, 1).contiguous()                               # NHWC
+    w2 = w.permute(0, 2, 3, 1).reshape(Cout, k * k * Cin).contiguous()    # [Cout, (r, s, c)]
+    P = (H + 2 * pad - k) // stride + 1
+    Q = (W + 2 * pad - k) // stride + 1
+    M, K = N * P * Q, k * k * Cin
+    y = torch.empty(M, Cout, dtype=torch.bfloat16, device=dev)
+    B.gemm(xh, w2, y, M=M, N=Cout, K=K, a_conv=(k, k, stride, pad))
+    ref_x = x.float().requires_grad_(True)
+    ref_w = w.float().requires_grad_(True)
+    ref = F.conv2d(ref_x, ref_w, stride=stride, padding=pad)
+    want = ref.permute(0, 2, 3, 1).reshape(M, Cout)
+    assert rel_err(y, want) < 5e-3, rel_err(y, want)
+    # weight gradient: dW[Cout, (r, s, c)] = dY^T [Cout, M] @ im2col(x) [M, K]
+    dy = bf(torch.randn(M, Cout, device=dev))
+    dw = torch.zeros(Cout, K, dtype=torch.float32, device=dev)
+    B.gemm(dy, xh, dw, M=Cout, N=K, K=M, a_mn_major=True, b_conv=(k, k, stride, pad), split_k=1 if M < 4096 else 0)
+    ref.backward(dy.float().view(N, P, Q, Cout).permute(0, 3, 1, 2))
+    want_dw = ref_w.grad.permute(0, 2, 3, 1).reshape(Cout, K)
+    assert rel_err(dw, want_dw) < 5e-3, rel_err(dw, want_dw)
+
+
 @pytest.mark.parametrize("Cin,Cout,k,stride,pad,H", [
     (64, 64, 1, 1, 0, 14), (256, 512, 1, 2, 0, 14), (64, 64, 3, 1, 1, 14), (128, 128, 3, 2, 1, 15),
     (3, 64, 7, 2, 3, 32)])
