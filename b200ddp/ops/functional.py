@@ -606,15 +606,24 @@ class _Conv2d(torch.autograd.Function):
         w2 = w2.reshape(Cout, -1).contiguous()
         N, H, W_, Cp = xh.shape
         direct = R == 1 and S == 1 and stride == 1 and pad == 0
-        a = xh.view(N * H * W_, Cp) if direct else _im2col(xh, R, S, stride, pad)
+        # Implicit GEMM: every other convolution whose channel count fills 64-wide k-blocks reads the
+        # activation through a TMA im2col-mode tensor map — forward and weight gradient — so no
+        # gathered [N*P*Q, R*S*C] matrix is ever written (round 1: 1.0 ms of im2col per step and
+        # 2.2 GB of saved operands at batch 64).  The 3-channel stem keeps the explicit gather.
+        implicit = (not direct) and Cp % 64 == 0 and os.environ.get("B200DDP_NO_IMPLICIT_CONV") is None
         P = (H + 2 * pad - R) // stride + 1
         Q = (W_ + 2 * pad - S) // stride + 1
         y = torch.empty(N * P * Q, Cout, dtype=torch.bfloat16, device=x.device)
-        B.gemm(a, w2, y, M=N * P * Q, N=Cout, K=w2.shape[1])
-        # the gathered operand is kept for the weight gradient (2.2 GB across ResNet-50 at batch 64:
-        # cheap next to 180 GB of HBM, and it halves the im2col traffic of a step)
+        if implicit:
+            a = xh
+            B.gemm(xh, w2, y, M=N * P * Q, N=Cout, K=w2.shape[1], a_conv=(R, S, stride, pad))
+        else:
+            a = xh.view(N * H * W_, Cp) if direct else _im2col(xh, R, S, stride, pad)
+            B.gemm(a, w2, y, M=N * P * Q, N=Cout, K=w2.shape[1])
+        # explicit path: the gathered operand is kept for the weight gradient
         ctx.save_for_backward(xh, w2, a)
         ctx.w, ctx.geom = w, (R, S, stride, pad, direct, cpad, Cin, P, Q)
+        ctx.implicit = implicit
         return y.view(N, P, Q, Cout).permute(0, 3, 1, 2)
 
     @staticmethod
@@ -647,7 +656,14 @@ class _Conv2d(torch.autograd.Function):
         # or the two-SM kernel straight to bf16 when the output has enough tiles (_wgrad_into)
         garena = getattr(w, "_b200_grad", None)
         dw2 = torch.empty(Cout, Kt, dtype=garena.dtype if garena is not None else torch.bfloat16, device=dy.device)
-        _wgrad_into(dy2, a, dw2)
+        if ctx.implicit:
+            # dW = dY^T @ im2col(x) with the im2col view as MN-major B operand; the output is small
+            # ([Cout, R*S*C]) and the reduction long (all pixels): split-K into an fp32 buffer
+            tmp = torch.zeros(Cout, Kt, dtype=torch.float32, device=dy.device)
+            B.gemm(dy2, xh, tmp, M=Cout, N=Kt, K=M, a_mn_major=True, b_conv=(R, S, stride, pad), split_k=1)
+            dw2.copy_(tmp)
+        else:
+            _wgrad_into(dy2, a, dw2)
         dw = dw2.view(Cout, R, S, Cp)[..., :Cin].permute(0, 3, 1, 2)  # back to [Cout, Cin, R, S]
 
         def emit(dst):
