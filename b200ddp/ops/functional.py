@@ -640,7 +640,15 @@ class _Conv2d(torch.autograd.Function):
             dyh = dyh.contiguous()
         dy2 = dyh.view(M, Cout)
         dx = None
-        if ctx.needs_input_grad[0]:
+        if ctx.needs_input_grad[0] and ctx.implicit and stride == 1 and Cout % 64 == 0 and not cpad:
+            # Data gradient of a stride-1 convolution = convolution of dY with the filter mirrored in
+            # (r, s) and transposed in (Cout, Cin), padding R-1-pad: the same implicit-GEMM forward
+            # kernel, no [M, R*S*C] column matrix and no col2im pass.
+            wf = w.flip(2, 3).permute(1, 2, 3, 0).reshape(Cin, R * S * Cout).contiguous()
+            dxh = torch.empty(N * H * W_, Cin, dtype=torch.bfloat16, device=dy.device)
+            B.gemm(dyh, wf, dxh, M=N * H * W_, N=Cin, K=R * S * Cout, a_conv=(R, S, 1, R - 1 - pad))
+            dx = dxh.view(N, H, W_, Cin).permute(0, 3, 1, 2)
+        elif ctx.needs_input_grad[0]:
             dcol = torch.empty(M, Kt, dtype=torch.bfloat16, device=dy.device)
             B.gemm(dy2, w2, dcol, M=M, N=Kt, K=Cout, b_mn_major=True)  # W2 stored [Cout, Kt] = [K, N]
             if direct:

@@ -891,6 +891,12 @@ def test_implicit_gemm_convolution(B, N, H, W, Cin, Cout, k, stride, pad):
     ref.backward(dy.float().view(N, P, Q, Cout).permute(0, 3, 1, 2))
     want_dw = ref_w.grad.permute(0, 2, 3, 1).reshape(Cout, K)
     assert rel_err(dw, want_dw) < 5e-3, rel_err(dw, want_dw)
+    if stride == 1:   # data gradient = implicit convolution of dY with the mirrored, transposed filter
+        wf = w.flip(2, 3).permute(1, 2, 3, 0).reshape(Cin, k * k * Cout).contiguous()
+        dx = torch.empty(N * H * W, Cin, dtype=torch.bfloat16, device=dev)
+        B.gemm(dy.view(N, P, Q, Cout), wf, dx, M=N * H * W, N=Cin, K=k * k * Cout, a_conv=(k, k, 1, k - 1 - pad))
+        want_dx = ref_x.grad.permute(0, 2, 3, 1).reshape(N * H * W, Cin)
+        assert rel_err(dx, want_dx) < 5e-3, rel_err(dx, want_dx)
 
 
 @pytest.mark.parametrize("Cin,Cout,k,stride,pad,H", [
