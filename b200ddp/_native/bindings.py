@@ -151,9 +151,9 @@ def declare(L: C.CDLL) -> None:
     L.b200_causal_softmax_fwd.restype = L.b200_causal_softmax_bwd.restype = C.c_int
     L.b200_batchnorm_scratch_bytes.argtypes = [C.c_int]
     L.b200_batchnorm_scratch_bytes.restype = C.c_int64
-    L.b200_batchnorm_fwd.argtypes = [C.c_void_p] * 9 + [C.c_int64, C.c_int, C.c_float, C.c_float, C.c_int,
+    L.b200_batchnorm_fwd.argtypes = [C.c_void_p] * 10 + [C.c_int64, C.c_int, C.c_float, C.c_float, C.c_int,
                                                          C.c_int, C.c_void_p, C.c_void_p]
-    L.b200_batchnorm_bwd.argtypes = [C.c_void_p] * 10 + [C.c_int, C.c_int64, C.c_int, C.c_int, C.c_void_p,
+    L.b200_batchnorm_bwd.argtypes = [C.c_void_p] * 11 + [C.c_int, C.c_int64, C.c_int, C.c_int, C.c_void_p,
                                                           C.c_void_p]
     L.b200_batchnorm_eval_rstd.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_void_p]
     for name in ("b200_batchnorm_fwd", "b200_batchnorm_bwd", "b200_batchnorm_eval_rstd"):

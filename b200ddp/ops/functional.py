@@ -722,13 +722,18 @@ class _BatchNormAct(torch.autograd.Function):
             rstd = torch.empty(Cc, dtype=torch.float32, device=x.device)
             nat.check(L.b200_batchnorm_eval_rstd(running_var.data_ptr(), rstd.data_ptr(), Cc, eps,
                                                  nat.stream_ptr(x.device)), "b200_batchnorm_eval_rstd")
+        mask = None
+        if relu and training and any(ctx.needs_input_grad[:3]):
+            mask = torch.empty(rows * (Cc // 8), dtype=torch.uint8, device=x.device)
         nat.check(L.b200_batchnorm_fwd(
-            xh.data_ptr(), rh.data_ptr() if rh is not None else None, y.data_ptr(), gamma.data_ptr(),
+            xh.data_ptr(), rh.data_ptr() if rh is not None else None, y.data_ptr(),
+            mask.data_ptr() if mask is not None else None, gamma.data_ptr(),
             beta.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
             running_mean.data_ptr() if training else None, running_var.data_ptr() if training else None,
             rows, Cc, eps, momentum, int(training), int(relu), sc.data_ptr(), nat.stream_ptr(x.device)),
             "b200_batchnorm_fwd")
-        ctx.save_for_backward(xh, y if relu else xh, mean, rstd)
+        ctx.save_for_backward(xh, mask if mask is not None else (y if relu else xh), mean, rstd)
+        ctx.has_mask = mask is not None
         ctx.weight, ctx.bias = weight, bias
         ctx.relu, ctx.has_res = relu, residual is not None
         return y.permute(0, 3, 1, 2)
@@ -751,7 +756,8 @@ class _BatchNormAct(torch.autograd.Function):
             gdst, bdst = torch.empty_like(weight), torch.empty_like(bias)
         sc = _scratch_buf(dy.device, int(L.b200_batchnorm_scratch_bytes(Cc)))
         nat.check(L.b200_batchnorm_bwd(
-            dyh.data_ptr(), xh.data_ptr(), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+            dyh.data_ptr(), xh.data_ptr(), None if ctx.has_mask else y.data_ptr(),
+            y.data_ptr() if ctx.has_mask else None, mean.data_ptr(), rstd.data_ptr(),
             _f32_param(weight).data_ptr(), dx.data_ptr(), dres.data_ptr() if dres is not None else None,
             gdst.data_ptr(), bdst.data_ptr(), int(gdst.dtype == torch.bfloat16), rows, Cc, int(ctx.relu),
             sc.data_ptr(), nat.stream_ptr(dy.device)), "b200_batchnorm_bwd")

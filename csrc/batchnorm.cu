@@ -32,6 +32,26 @@ __device__ __forceinline__ uint4 bn_pack8(const float (&f)[8]) {
     return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
 }
 
+__device__ __forceinline__ void bn_load8(const float* __restrict__ p, float (&f)[8]) {
+    const float4 a = reinterpret_cast<const float4*>(p)[0], b = reinterpret_cast<const float4*>(p)[1];
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
+    f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+// g *= [y > 0]: from the one-byte-per-8-channels mask the forward pass wrote, else from y itself.
+__device__ __forceinline__ void bn_relu_gate(float (&g)[8], const __nv_bfloat16* __restrict__ y,
+                                             const uint8_t* __restrict__ mask, int64_t idx) {
+    if (mask) {
+        const uint32_t m = mask[idx];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] = (m >> k) & 1u ? g[k] : 0.f;
+    } else {
+        float yv[8];
+        bn_unpack8(reinterpret_cast<const uint4*>(y)[idx], yv);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] = yv[k] > 0.f ? g[k] : 0.f;
+    }
+}
+
 // Per-block partial sums of two per-channel quantities.
 //   MODE 0 (forward):  (x, x^2)
 //   MODE 1 (backward): (g, g * xhat) with g = dy * [y > 0] when relu, xhat = (x - mean) * rstd
@@ -39,8 +59,8 @@ __device__ __forceinline__ uint4 bn_pack8(const float (&f)[8]) {
 template <int MODE>
 __global__ void __launch_bounds__(BN_THREADS) bn_reduce_kernel(
     const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ x,
-    const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean, const float* __restrict__ rstd,
-    float* __restrict__ partials, int64_t rows, int C, int relu) {
+    const __nv_bfloat16* __restrict__ y, const uint8_t* __restrict__ mask, const float* __restrict__ mean,
+    const float* __restrict__ rstd, float* __restrict__ partials, int64_t rows, int C, int relu) {
     __shared__ float sm[BN_THREADS][17];
     const int cv = C >> 3;
     const int lanes_r = BN_THREADS / cv;
@@ -48,8 +68,8 @@ __global__ void __launch_bounds__(BN_THREADS) bn_reduce_kernel(
     float s0[8] = {0, 0, 0, 0, 0, 0, 0, 0}, s1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     float mu[8], rs[8];
     if (MODE == 1) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { mu[k] = mean[v * 8 + k]; rs[k] = rstd[v * 8 + k]; }
+        bn_load8(mean + v * 8, mu);
+        bn_load8(rstd + v * 8, rs);
     }
     if (rl < lanes_r) {
 #pragma unroll 4
@@ -63,12 +83,7 @@ __global__ void __launch_bounds__(BN_THREADS) bn_reduce_kernel(
             } else {
                 float xv[8];
                 bn_unpack8(reinterpret_cast<const uint4*>(x)[idx], xv);
-                if (relu) {
-                    float yv[8];
-                    bn_unpack8(reinterpret_cast<const uint4*>(y)[idx], yv);
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) f[k] = yv[k] > 0.f ? f[k] : 0.f;
-                }
+                if (relu) bn_relu_gate(f, y, mask, idx);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) { s0[k] += f[k]; s1[k] += f[k] * (xv[k] - mu[k]) * rs[k]; }
             }
@@ -115,34 +130,58 @@ __device__ __forceinline__ bool bn_sum_partials(const float* __restrict__ partia
     return true;
 }
 
-// Forward finalize: mean / rstd from the partial sums, running statistics update.
+// Forward finalize: mean / rstd from the partial sums, running statistics update, and the two
+// per-channel constants of the apply pass: coef = [scale = rstd*gamma | shift = beta - mean*scale].
 __global__ void __launch_bounds__(BN_FIN_THREADS) bn_finalize_fwd_kernel(const float* __restrict__ partials, int nparts, int C,
                                                               int64_t rows, float eps, float momentum,
+                                                              const float* __restrict__ gamma, const float* __restrict__ beta,
                                                               float* __restrict__ mean, float* __restrict__ rstd,
-                                                              float* running_mean, float* running_var) {
+                                                              float* running_mean, float* running_var,
+                                                              float* __restrict__ coef) {
     const int c = blockIdx.x * 32 + (threadIdx.x & 31);
     float s, q;
     if (!bn_sum_partials(partials, nparts, C, c, s, q)) return;
     const float m = s / (float)rows;
     const float var = fmaxf(q / (float)rows - m * m, 0.f);
+    const float r = rsqrtf(var + eps);
     mean[c] = m;
-    rstd[c] = rsqrtf(var + eps);
+    rstd[c] = r;
+    const float sc = r * gamma[c];
+    coef[c] = sc;
+    coef[C + c] = beta[c] - m * sc;
     if (running_mean) {
         const float unbiased = rows > 1 ? var * (float)rows / (float)(rows - 1) : var;
         running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * m;
         running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
     }
 }
+// Inference: the same two constants from statistics that already exist.
+__global__ void bn_coef_kernel(const float* __restrict__ mean, const float* __restrict__ rstd,
+                               const float* __restrict__ gamma, const float* __restrict__ beta,
+                               float* __restrict__ coef, int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float sc = rstd[c] * gamma[c];
+    coef[c] = sc;
+    coef[C + c] = beta[c] - mean[c] * sc;
+}
 
-// Backward finalize: dbeta = sum g, dgamma = sum g*xhat (bf16 or fp32 out) + fp32 copies for dx.
+// Backward finalize: dbeta = sum g, dgamma = sum g*xhat (bf16 or fp32 out), and the three
+// per-channel constants of the dx pass (see bn_bwd_apply_kernel): coef = [a | b2 | c].
 __global__ void __launch_bounds__(BN_FIN_THREADS) bn_finalize_bwd_kernel(const float* __restrict__ partials, int nparts, int C,
-                                                              float* __restrict__ sums, void* dgamma, void* dbeta,
+                                                              const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                              const float* __restrict__ gamma, float inv_rows,
+                                                              float* __restrict__ coef, void* dgamma, void* dbeta,
                                                               int grads_bf16) {
     const int c = blockIdx.x * 32 + (threadIdx.x & 31);
     float s, q;
     if (!bn_sum_partials(partials, nparts, C, c, s, q)) return;
-    sums[c] = s;
-    sums[C + c] = q;
+    const float rs = rstd[c], mu = mean[c];
+    const float sg = s * inv_rows, sq = q * inv_rows;
+    const float ka = gamma[c] * rs;
+    coef[c] = ka;
+    coef[C + c] = -ka * rs * sq;
+    coef[2 * C + c] = ka * (rs * mu * sq - sg);
     if (grads_bf16) {
         reinterpret_cast<__nv_bfloat16*>(dbeta)[c] = __float2bfloat16_rn(s);
         reinterpret_cast<__nv_bfloat16*>(dgamma)[c] = __float2bfloat16_rn(q);
@@ -152,81 +191,93 @@ __global__ void __launch_bounds__(BN_FIN_THREADS) bn_finalize_bwd_kernel(const f
     }
 }
 
-// y = relu?( (x - mean) * rstd * gamma + beta (+ residual) ).  In inference `rstd` already holds
-// rsqrt(running_var + eps) and `mean` the running mean.
+// y = relu?( x * scale + shift (+ residual) ), and with `mask` one byte per 8 channels holding
+// [y > 0] for the backward pass (1/16 of the bytes of y).
 // The grid stride is a multiple of C/8 (C is a power of two <= 2048, the stride a multiple of
 // 256), so every thread stays on the same 8 channels: their scale/shift live in registers.
+// Two vectors per thread are in flight per trip.
 __global__ void __launch_bounds__(256) bn_apply_kernel(const __nv_bfloat16* __restrict__ x,
                                                        const __nv_bfloat16* __restrict__ residual,
-                                                       __nv_bfloat16* __restrict__ y, const float* __restrict__ mean,
-                                                       const float* __restrict__ rstd, const float* __restrict__ gamma,
-                                                       const float* __restrict__ beta, int64_t total_vecs, int C, int relu) {
+                                                       __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ mask,
+                                                       const float* __restrict__ coef, int64_t total_vecs, int C,
+                                                       int relu) {
     const int cv = C >> 3;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     const int64_t first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int c0 = (int)(first % cv) * 8;
     float sc[8], sh[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        sc[k] = rstd[c0 + k] * gamma[c0 + k];
-        sh[k] = beta[c0 + k] - mean[c0 + k] * sc[k];
-    }
-    for (int64_t i = first; i < total_vecs; i += stride) {
-        float f[8];
-        bn_unpack8(reinterpret_cast<const uint4*>(x)[i], f);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], sc[k], sh[k]);
+    bn_load8(coef + c0, sc);
+    bn_load8(coef + C + c0, sh);
+    for (int64_t i = first; i < total_vecs; i += 2 * stride) {
+        const int64_t j = i + stride;
+        const bool two = j < total_vecs;
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        const uint4 xa = __ldcs(reinterpret_cast<const uint4*>(x) + i);
+        const uint4 xb = two ? __ldcs(reinterpret_cast<const uint4*>(x) + j) : z;
+        uint4 ra = z, rb = z;
         if (residual) {
-            float r[8];
-            bn_unpack8(reinterpret_cast<const uint4*>(residual)[i], r);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) f[k] += r[k];
+            ra = __ldcs(reinterpret_cast<const uint4*>(residual) + i);
+            if (two) rb = __ldcs(reinterpret_cast<const uint4*>(residual) + j);
         }
-        if (relu) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) f[k] = fmaxf(f[k], 0.f);
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !two) break;
+            float f[8], r[8];
+            bn_unpack8(h ? xb : xa, f);
+            bn_unpack8(h ? rb : ra, r);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[k] = fmaf(f[k], sc[k], sh[k]) + r[k];
+            if (relu) {
+                uint32_t m = 0;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    m |= f[k] > 0.f ? 1u << k : 0u;
+                    f[k] = fmaxf(f[k], 0.f);
+                }
+                if (mask) mask[h ? j : i] = (uint8_t)m;
+            }
+            reinterpret_cast<uint4*>(y)[h ? j : i] = bn_pack8(f);
         }
-        reinterpret_cast<uint4*>(y)[i] = bn_pack8(f);
     }
 }
 
 // dx = gamma * rstd * (g - sum_g/rows - xhat * sum_gxhat/rows), g = dy * [y > 0] when relu;
 // dres (optional) = g: the gradient of the fused residual branch.  Per-channel terms are
-// folded into three register constants per channel (same channel-invariance as above):
+// folded into three constants per channel by the finalize kernel:
 //   dx = a * g + b2 * x + c,  a = gamma*rstd,  b2 = -a*rstd*q,  c = a*(rstd*mean*q - s)
 // with s = sum_g/rows, q = sum_gxhat/rows.
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(
     const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ y,
-    const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
-    const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres,
-    int64_t total_vecs, int C, float inv_rows, int relu) {
+    const uint8_t* __restrict__ mask, const float* __restrict__ coef, __nv_bfloat16* __restrict__ dx,
+    __nv_bfloat16* __restrict__ dres, int64_t total_vecs, int C, int relu) {
     const int cv = C >> 3;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     const int64_t first = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int c0 = (int)(first % cv) * 8;
     float ka[8], kb[8], kc[8];
+    bn_load8(coef + c0, ka);
+    bn_load8(coef + C + c0, kb);
+    bn_load8(coef + 2 * C + c0, kc);
+    for (int64_t i = first; i < total_vecs; i += 2 * stride) {
+        const int64_t j = i + stride;
+        const bool two = j < total_vecs;
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        const uint4 ga = __ldcs(reinterpret_cast<const uint4*>(dy) + i);
+        const uint4 xa = __ldcs(reinterpret_cast<const uint4*>(x) + i);
+        const uint4 gb = two ? __ldcs(reinterpret_cast<const uint4*>(dy) + j) : z;
+        const uint4 xb = two ? __ldcs(reinterpret_cast<const uint4*>(x) + j) : z;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const float rs = rstd[c0 + k], mu = mean[c0 + k];
-        const float sg = sums[c0 + k] * inv_rows, sq = sums[C + c0 + k] * inv_rows;
-        ka[k] = gamma[c0 + k] * rs;
-        kb[k] = -ka[k] * rs * sq;
-        kc[k] = ka[k] * (rs * mu * sq - sg);
-    }
-    for (int64_t i = first; i < total_vecs; i += stride) {
-        float g[8], xv[8], o[8];
-        bn_unpack8(reinterpret_cast<const uint4*>(dy)[i], g);
-        bn_unpack8(reinterpret_cast<const uint4*>(x)[i], xv);
-        if (relu) {
-            float yv[8];
-            bn_unpack8(reinterpret_cast<const uint4*>(y)[i], yv);
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !two) break;
+            float g[8], xv[8], o[8];
+            bn_unpack8(h ? gb : ga, g);
+            bn_unpack8(h ? xb : xa, xv);
+            if (relu) bn_relu_gate(g, y, mask, h ? j : i);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) g[k] = yv[k] > 0.f ? g[k] : 0.f;
+            for (int k = 0; k < 8; ++k) o[k] = fmaf(ka[k], g[k], fmaf(kb[k], xv[k], kc[k]));
+            reinterpret_cast<uint4*>(dx)[h ? j : i] = bn_pack8(o);
+            if (dres) reinterpret_cast<uint4*>(dres)[h ? j : i] = bn_pack8(g);
         }
-#pragma unroll
-        for (int k = 0; k < 8; ++k) o[k] = fmaf(ka[k], g[k], fmaf(kb[k], xv[k], kc[k]));
-        reinterpret_cast<uint4*>(dx)[i] = bn_pack8(o);
-        if (dres) reinterpret_cast<uint4*>(dres)[i] = bn_pack8(g);
     }
 }
 
@@ -250,10 +301,10 @@ static int bn_ew_grid(int64_t vecs) {
 }  // namespace b200
 
 extern "C" int64_t b200_batchnorm_scratch_bytes(int C) {
-    return (int64_t)b200::BN_MAX_BLOCKS * 2 * C * (int64_t)sizeof(float) + 2 * (int64_t)C * sizeof(float);
+    return (int64_t)b200::BN_MAX_BLOCKS * 2 * C * (int64_t)sizeof(float) + 3 * (int64_t)C * sizeof(float);
 }
 
-extern "C" int b200_batchnorm_fwd(const void* x, const void* residual, void* y, const float* gamma,
+extern "C" int b200_batchnorm_fwd(const void* x, const void* residual, void* y, void* relu_mask, const float* gamma,
                                   const float* beta, float* mean, float* rstd, float* running_mean,
                                   float* running_var, int64_t rows, int C, float eps, float momentum,
                                   int training, int relu, void* scratch, void* stream) {
@@ -261,41 +312,48 @@ extern "C" int b200_batchnorm_fwd(const void* x, const void* residual, void* y, 
     B200_REQUIRE(x && y && gamma && beta && mean && rstd, "batchnorm_fwd: null pointer");
     if (int rc = bn_check(rows, C)) return rc;
     cudaStream_t s = (cudaStream_t)stream;
+    B200_REQUIRE(scratch, "batchnorm_fwd: needs scratch");
+    float* coef = (float*)scratch + (int64_t)BN_MAX_BLOCKS * 2 * C;
     if (training) {
-        B200_REQUIRE(scratch, "batchnorm_fwd: training needs scratch");
         const int grid = bn_reduce_grid(rows, C);
         bn_reduce_kernel<0><<<grid, BN_THREADS, 0, s>>>((const __nv_bfloat16*)x, nullptr, nullptr, nullptr, nullptr,
-                                                        (float*)scratch, rows, C, 0);
+                                                        nullptr, (float*)scratch, rows, C, 0);
         bn_finalize_fwd_kernel<<<(C + 31) / 32, BN_FIN_THREADS, 0, s>>>((const float*)scratch, grid, C, rows, eps, momentum,
-                                                               mean, rstd, running_mean, running_var);
+                                                               gamma, beta, mean, rstd, running_mean, running_var, coef);
         b200_count_launch(2);
+    } else {
+        bn_coef_kernel<<<(C + 255) / 256, 256, 0, s>>>(mean, rstd, gamma, beta, coef, C);
+        b200_count_launch(1);
     }
     const int64_t vecs = rows * (C >> 3);
     bn_apply_kernel<<<bn_ew_grid(vecs), 256, 0, s>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)residual,
-                                                     (__nv_bfloat16*)y, mean, rstd, gamma, beta, vecs, C, relu);
+                                                     (__nv_bfloat16*)y, (uint8_t*)relu_mask, coef, vecs, C, relu);
     b200_count_launch(1);
     B200_CUDA_OK(cudaGetLastError());
     return 0;
 }
 
-extern "C" int b200_batchnorm_bwd(const void* dy, const void* x, const void* y, const float* mean, const float* rstd,
+extern "C" int b200_batchnorm_bwd(const void* dy, const void* x, const void* y, const void* relu_mask,
+                                  const float* mean, const float* rstd,
                                   const float* gamma, void* dx, void* dres, void* dgamma, void* dbeta,
                                   int grads_bf16, int64_t rows, int C, int relu, void* scratch, void* stream) {
     using namespace b200;
     B200_REQUIRE(dy && x && mean && rstd && gamma && dx && dgamma && dbeta && scratch, "batchnorm_bwd: null pointer");
-    B200_REQUIRE(!relu || y, "batchnorm_bwd: the ReLU mask needs the forward output");
+    B200_REQUIRE(!relu || y || relu_mask, "batchnorm_bwd: the ReLU gate needs the forward output or its mask");
     if (int rc = bn_check(rows, C)) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     const int grid = bn_reduce_grid(rows, C);
     float* partials = (float*)scratch;
-    float* sums = partials + (int64_t)BN_MAX_BLOCKS * 2 * C;
+    float* coef = partials + (int64_t)BN_MAX_BLOCKS * 2 * C;
     bn_reduce_kernel<1><<<grid, BN_THREADS, 0, s>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,
-                                                    (const __nv_bfloat16*)y, mean, rstd, partials, rows, C, relu);
-    bn_finalize_bwd_kernel<<<(C + 31) / 32, BN_FIN_THREADS, 0, s>>>(partials, grid, C, sums, dgamma, dbeta, grads_bf16);
+                                                    (const __nv_bfloat16*)y, (const uint8_t*)relu_mask, mean, rstd,
+                                                    partials, rows, C, relu);
+    bn_finalize_bwd_kernel<<<(C + 31) / 32, BN_FIN_THREADS, 0, s>>>(partials, grid, C, mean, rstd, gamma,
+                                                                    1.f / (float)rows, coef, dgamma, dbeta, grads_bf16);
     const int64_t vecs = rows * (C >> 3);
     bn_bwd_apply_kernel<<<bn_ew_grid(vecs), 256, 0, s>>>(
-        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, mean, rstd, gamma, sums,
-        (__nv_bfloat16*)dx, (__nv_bfloat16*)dres, vecs, C, 1.f / (float)rows, relu);
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (const uint8_t*)relu_mask, coef,
+        (__nv_bfloat16*)dx, (__nv_bfloat16*)dres, vecs, C, relu);
     b200_count_launch(3);
     B200_CUDA_OK(cudaGetLastError());
     return 0;

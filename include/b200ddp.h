@@ -267,14 +267,18 @@ int b200_col2im(const void* dcol, void* dx, int N, int H, int W, int C, int R, i
  * fwd: training != 0 computes batch statistics (and updates running_* when non-null, unbiased
  * variance, `momentum`), otherwise mean/rstd must already hold the inference statistics
  * (b200_batchnorm_eval_rstd).  y = relu?((x - mean) * rstd * gamma + beta (+ residual)).
+ * relu_mask (optional, uint8 [rows * C/8]): with relu the forward writes bit k of byte v = [y[8v+k] > 0];
+ * the backward reads it instead of y (1/16 of the bytes) when it is passed, else y itself.
  * bwd: g = dy * [y > 0] when relu; dgamma/dbeta [C] bf16 or fp32; dx; dres = g when non-null
  * (gradient of the fused residual branch).  scratch: b200_batchnorm_scratch_bytes(C). */
 int64_t b200_batchnorm_scratch_bytes(int C);
-int b200_batchnorm_fwd(const void* x, const void* residual, void* y, const float* gamma, const float* beta,
+int b200_batchnorm_fwd(const void* x, const void* residual, void* y, void* relu_mask, const float* gamma,
+                       const float* beta,
                        float* mean, float* rstd, float* running_mean, float* running_var, int64_t rows,
                        int C, float eps, float momentum, int training, int relu, void* scratch,
                        void* stream);
-int b200_batchnorm_bwd(const void* dy, const void* x, const void* y, const float* mean, const float* rstd,
+int b200_batchnorm_bwd(const void* dy, const void* x, const void* y, const void* relu_mask,
+                       const float* mean, const float* rstd,
                        const float* gamma, void* dx, void* dres, void* dgamma, void* dbeta, int grads_bf16,
                        int64_t rows, int C, int relu, void* scratch, void* stream);
 int b200_batchnorm_eval_rstd(const float* running_var, float* rstd, int C, float eps, void* stream);
