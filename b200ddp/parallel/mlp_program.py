@@ -103,6 +103,8 @@ class FusedSession:
         nat.check(self.L.b200_mlp_create(C.byref(h), C.byref(d)), "b200_mlp_create")
         self.handle = h.value
         self._keep = (d, comm)
+        # > 0: the update runs on extra clusters of the step launch itself (one launch per step)
+        self.update_clusters = int(self.L.b200_mlp_update_clusters(self.handle))
 
     def rebuild(self) -> None:
         """Hyper-parameters are baked into the session: drop it and build a new one."""
@@ -193,7 +195,7 @@ class MLPProgram:
         self.fused: Optional[FusedSession] = FusedSession(self) if FusedSession.supports(self) else None
         self._last_fused = False
         if self.fused is not None:
-            self.launches_per_step = 1 + len(engine.layout.buckets)
+            self.launches_per_step = 1 if self.fused.update_clusters else 1 + len(engine.layout.buckets)
 
     def on_params_changed(self) -> None:
         pass  # weights are read in place from the arenas; nothing is cached

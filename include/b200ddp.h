@@ -394,6 +394,10 @@ typedef struct {
 int64_t b200_mlp_scratch_bytes(void);
 int b200_mlp_create(void** session, const b200_mlp_desc* d);
 int b200_mlp_destroy(void* session);
+/* Number of extra 8-CTA clusters that run the update (all-reduce + optimizer) inside the step launch;
+ * 0 = the update is launched separately after the step kernel (more than one bucket, or the launch
+ * would not be fully resident).  Env B200DDP_MLP_UPDATE_CLUSTERS overrides the default (0 disables). */
+int b200_mlp_update_clusters(void* session);
 /* forward (+ backward when train) on device inputs x fp32 [bsz,in], y int64 [bsz]; no update.
  * logits_out: optional fp32 [bsz, classes]. */
 int b200_mlp_forward_backward(void* session, const float* x, const int64_t* y, int bsz, int train,

@@ -36,6 +36,21 @@ print("us/step in chunks of 5 after 1 s idle:", [round(marks[k].elapsed_time(mar
 if os.environ.get("B200DDP_MLP_TRACE"):
     import ctypes as C
     from b200ddp import _native as nat
+    if fs.update_clusters:
+        eng.train_steps(xs, ys, 0, 40)
+        ub = (C.c_ulonglong * 34)()
+        nat.lib().b200_mlp_debug_utrace.argtypes = [C.c_void_p]
+        nat.check(nat.lib().b200_mlp_debug_utrace(ub), "utrace")
+        un = ["compute entry", "compute past wait", "compute signal", "upd0 grads loaded", "upd0 entry", "upd0 past wait",
+              "upd0 scalars", "upd0 flag seen", "upd0 loop done", "upd0 stores issued", "updL entry", "updL past wait",
+              "updL scalars", "updL flag seen", "updL loop done", "upd0 CTA synced"]
+        a, b = (ub[0:16], ub[16:32]) if ub[0] < ub[16] else (ub[16:32], ub[0:16])
+        t0 = a[0]
+        print("merged-update wall clock (globaltimer ns since the earlier launch's entry): earlier launch | later launch")
+        for i, nm in enumerate(un):
+            if nm != "-":
+                print(f"  {nm:18s} {a[i] - t0:8d} {b[i] - t0:8d}")
+        print(f"  last update CTA counted in (any step) {ub[32] - t0:8d}; compute saw the update (last time) {ub[33] - t0:8d}")
     names = ["entry", "x staged", "cta sync", "P1 mma done", "P1 drained", "cluster sync 1", "F1 done", "P2 mma done",
              "P2 drained", "cluster sync 2", "F2 done", "P3 done", "cluster sync 3", "CE done", "P4 mma done",
              "P4 epilogue", "P5 mma done", "P5 drained", "cluster sync 4", "F5 done", "P6 mma done", "P6 stored", "exit",
