@@ -543,6 +543,40 @@ def test_fused_mlp_train_steps_over_a_device_pool(monkeypatch):
     assert abs(a.last_loss().item() - last.item()) == 0.0
 
 
+@pytest.mark.parametrize("opt,kw", [("adam", {}), ("adamw", {"weight_decay": 0.05}), ("adam", {"weight_decay": 0.01}),
+                                    ("sgd", {"momentum": 0.9})])
+def test_fused_mlp_update_ctas_match_the_separate_update_kernel(monkeypatch, opt, kw):
+    """The update done by extra clusters of the step launch (several steps per launch, optimizer
+    state in registers, straight-line division / square root) is bit-identical to the optimizer
+    kernel launched after the step kernel (IEEE intrinsics), state and all."""
+    from b200ddp.models.simplenet import SimpleNet
+    from b200ddp.parallel.engine import DataParallel
+    torch.manual_seed(11)
+    dev = torch.device("cuda")
+    net = SimpleNet().to(dev)
+    lr = 0.05 if opt == "sgd" else 1e-3
+    monkeypatch.setenv("B200DDP_MLP_UPDATE_CLUSTERS", "0")
+    a = DataParallel(copy.deepcopy(net), backend="b200", compute_dtype=torch.bfloat16, optimizer=opt, lr=lr, **kw)
+    assert a.program.fused.update_clusters == 0
+    monkeypatch.delenv("B200DDP_MLP_UPDATE_CLUSTERS")
+    b = DataParallel(copy.deepcopy(net), backend="b200", compute_dtype=torch.bfloat16, optimizer=opt, lr=lr, **kw)
+    assert b.program.fused.update_clusters > 0
+    xs = torch.randn(7, 64, 784, device=dev)
+    xs[:, :, :40] = 0.0          # inputs that are always zero: zero gradients, zero moments (slow-path operands)
+    ys = torch.randint(0, 10, (7, 64), device=dev)
+    a.train_steps(xs, ys, 0, 150)      # b: three launches (64 + 64 + 22 steps)
+    b.train_steps(xs, ys, 0, 150)
+    torch.cuda.synchronize()
+    assert torch.equal(a.shadow, b.shadow) and torch.equal(a.master, b.master)
+    assert torch.equal(a.optimizer.exp_avg, b.optimizer.exp_avg)
+    if opt != "sgd":
+        assert torch.equal(a.optimizer.exp_avg_sq, b.optimizer.exp_avg_sq)
+    assert b.optimizer.step_dev[0].item() == 150 and a.last_loss().item() == b.last_loss().item()
+    one = b.train_step(xs[1], ys[1])   # a single-step launch after the multi-step ones
+    ref = a.train_step(xs[1], ys[1])
+    assert one.item() == ref.item() and torch.equal(a.shadow, b.shadow)
+
+
 def test_engine_checkpoint_roundtrip_on_gpu(tmp_path, reference_module):
     from b200ddp import load_checkpoint, save_checkpoint
     from b200ddp.models.simplenet import SimpleNet

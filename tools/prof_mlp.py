@@ -37,13 +37,14 @@ if os.environ.get("B200DDP_MLP_TRACE"):
     import ctypes as C
     from b200ddp import _native as nat
     if fs.update_clusters:
+        print("update clusters in the step launch:", fs.update_clusters)
         eng.train_steps(xs, ys, 0, 40)
         ub = (C.c_ulonglong * 34)()
         nat.lib().b200_mlp_debug_utrace.argtypes = [C.c_void_p]
         nat.check(nat.lib().b200_mlp_debug_utrace(ub), "utrace")
         un = ["compute entry", "compute past wait", "compute signal", "upd0 grads loaded", "upd0 entry", "upd0 past wait",
               "upd0 scalars", "upd0 flag seen", "upd0 loop done", "upd0 stores issued", "updL entry", "updL past wait",
-              "updL scalars", "updL flag seen", "updL loop done", "upd0 CTA synced"]
+              "updL scalars", "updL flag seen", "updL loop done", "-"]
         a, b = (ub[0:16], ub[16:32]) if ub[0] < ub[16] else (ub[16:32], ub[0:16])
         t0 = a[0]
         print("merged-update wall clock (globaltimer ns since the earlier launch's entry): earlier launch | later launch")
