@@ -82,6 +82,18 @@ def max_over_ranks(v: float, device) -> float:
     return float(t.item())
 
 
+def _step_path(engine) -> str:
+    prog = engine.program
+    if prog is None or prog.fused is None:
+        return "GEMM-per-layer CUDA graph"
+    k = prog.fused.update_clusters
+    if k:
+        return (f"one kernel: 8-CTA compute cluster (fwd+CE+bwd) + {k} update clusters (all-reduce + Adam) in the "
+                "same launch, up to 64 steps per launch with counter hand-overs (engine.train_steps); the "
+                "end-to-end arm launches it once per step")
+    return "fused cluster kernel (fwd+CE+bwd) + fused all-reduce/Adam kernel, launched from C (engine.train_steps)"
+
+
 def timed(fn_run, steps: int, warmup: int, device, sample_clocks: bool, fn_end=None):
     """fn_run(first, count) runs steps [first, first + count); fn_end() (optional) drains whatever
     the steps left pending, still inside the timed region.  Returns (ms total max-over-ranks,
@@ -186,10 +198,7 @@ def run_ours(args):
                        "global_batch": world * bsz, "per_rank_batch": bsz, "seq_len": None,
                        "parallelism": f"dp{world}", "optimizer": "adam", "backend": backend,
                        "grad_wire_dtype": "fp32", "master_weights": "fp32",
-                       "step_path": ("fused cluster kernel (fwd+CE+bwd) + fused all-reduce/Adam kernel, "
-                                     "launched from C (engine.train_steps)")
-                       if engine.program is not None and engine.program.fused is not None
-                       else "GEMM-per-layer CUDA graph",
+                       "step_path": _step_path(engine),
                        "l2": f"inputs rotate through a {n}-batch pool "
                              f"({n * (bsz * IN_FEATURES * 4 + bsz * 8) / 2**20:.0f} MiB) larger than L2"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches,
