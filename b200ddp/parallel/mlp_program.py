@@ -222,7 +222,8 @@ class MLPProgram:
 
     def train_many(self, x_pool: torch.Tensor, y_pool: torch.Tensor, first: int, count: int):
         """`count` optimisation steps over an on-device pool of batches ([P, bsz, in], [P, bsz]):
-        step i uses batch (first + i) % P.  One native call, two launches per step."""
+        step i uses batch (first + i) % P.  One native call; one launch per up to 64 steps when the
+        update rides in the step launch (FusedSession.update_clusters), else two launches per step."""
         if not self._fused_ok(x_pool[0], y_pool[0]) or not x_pool.is_contiguous() or not y_pool.is_contiguous():
             loss = None
             for i in range(count):
