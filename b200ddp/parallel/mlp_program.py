@@ -34,9 +34,10 @@ from .._native import bindings as B
 
 
 class FusedSession:
-    """Native session of the fused step (``csrc/mlp_fused.cu``): ONE 8-CTA-cluster kernel for
-    forward + cross-entropy + backward, then the fused all-reduce + optimizer kernel — two
-    launches per step, issued from C without a CUDA graph.  Built for the reference's model
+    """Native session of the fused step (``csrc/mlp_fused.cu``): ONE launch per step (or per up to
+    64 steps) — an 8-CTA cluster for forward + cross-entropy + backward and ``update_clusters``
+    more clusters of the same grid for the all-reduce + optimizer; two launches per step when the
+    update cannot ride along.  Issued from C without a CUDA graph.  Built for the reference's model
     class (ref ``train.py:32-50``): two hidden layers of 256, at most 16 classes, at most 1024
     inputs, batches of at most 64; everything else runs the GEMM-per-layer schedule below."""
 
