@@ -5,16 +5,29 @@ set -u
 mkdir -p gpurun_out
 cap() { # target, kernel regex, name, skip
   local tgt=$1 re=$2 name=$3 skip=${4:-1}
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:$re -s $skip -c 1 -f -o gpurun_out/ncu_$name \
+  timeout 900 ncu --set full --clock-control none --import-source on -k "regex:$re" -s $skip -c 1 -f -o gpurun_out/ncu_$name \
       python tools/prof_targets.py $tgt > gpurun_out/ncu_$name.log 2>&1
   echo "$name rc=$? $(grep -c '==PROF== Profiling' gpurun_out/ncu_$name.log)"
 }
 for tgt in mlpstep gpt2step rn50step; do
   timeout 300 python tools/prof_targets.py $tgt > gpurun_out/plain_$tgt.log 2>&1 || { echo "plain $tgt failed"; tail -5 gpurun_out/plain_$tgt.log; exit 1; }
 done
-cap mlpstep mlp_step_kernel mlp_step 8
-cap mlpstep optimizer_kernel optimizer 8
-cap gpt2step flash_attn_fwd_kernel flash_fwd 12
+if [ "${1:-all}" = "changed" ]; then   # the kernels touched since the last full pass
+cap mlpstep mlp_step_kernel mlp_step 1
+cap gpt2step flash_attn_fwd2_kernel flash_fwd 12
+cap gpt2step flash_attn_bwd_kernel flash_bwd 12
+cap gpt2step optimizer_kernel optimizer 0
+cap rn50step bn_reduce_kernel bn_reduce 60
+cap rn50step bn_apply_kernel bn_apply 60
+cap rn50step bn_bwd_apply_kernel bn_bwd_apply 60
+cap rn50step bn_finalize_fwd_kernel bn_finalize 30
+cap rn50step im2col_flat_kernel im2col_flat 0
+cap rn50step gemm_kernel_2sm conv_gemm_2sm 30
+cap rn50step "gemm_kernel<256" conv_wgrad_splitk 20
+else
+cap mlpstep mlp_step_kernel mlp_step 1
+cap gpt2step optimizer_kernel optimizer 0
+cap gpt2step flash_attn_fwd2_kernel flash_fwd 12
 cap gpt2step flash_attn_bwd_kernel flash_bwd 12
 cap gpt2step gemm_kernel_2sm gemm_2sm 60
 cap gpt2step gemm_kernel_m256 gemm_m256 1
@@ -26,7 +39,8 @@ cap gpt2step colsum_stage1_kernel colsum 20
 cap rn50step bn_reduce_kernel bn_reduce 60
 cap rn50step bn_apply_kernel bn_apply 60
 cap rn50step bn_bwd_apply_kernel bn_bwd_apply 60
-cap rn50step im2col_kernel im2col 10
+cap rn50step im2col_flat_kernel im2col_flat 0
 cap rn50step col2im_kernel col2im 10
 cap rn50step maxpool_fwd_kernel maxpool_fwd 1
+fi
 ls -la gpurun_out/*.ncu-rep | awk '{s+=$5} END {print s/1e6 " MB of reports"}'

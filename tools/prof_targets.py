@@ -49,7 +49,8 @@ elif what == "mlpstep":
     from b200ddp import DataParallel, SimpleNet
     eng = DataParallel(SimpleNet().to(dev), backend="b200", compute_dtype=torch.bfloat16)
     xs = torch.randn(8, 64, 784, device=dev); ys = torch.randint(0, 10, (8, 64), device=dev)
-    eng.train_steps(xs, ys, 0, 24)
+    for _ in range(3):      # three launches of 24 steps each (the update rides in the step launch)
+        eng.train_steps(xs, ys, 0, 24)
 elif what in ("gpt2step", "rn50step"):
     from b200ddp import DataParallel
     torch.manual_seed(0)
