@@ -81,38 +81,63 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
 
 // partials layout: [gridDim.x * LN_WARPS][2][C] fp32 (dgamma then dbeta)
 template <int ITER>
-__global__ void __launch_bounds__(LN_WARPS * 32)
+__global__ void __launch_bounds__(LN_WARPS * 32, ITER <= 3 ? 2 : 1)
 layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean_in,
                      const float* __restrict__ rstd_in, __nv_bfloat16* __restrict__ dx,
                      const __nv_bfloat16* __restrict__ dx_add, float* __restrict__ partials, int64_t rows) {
     constexpr int C = ITER * 256;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float g[ITER][8], dg[ITER][8], db[ITER][8];
+    // Registers: gamma stays packed (bf16), xhat / dy*gamma are recomputed in the second pass instead
+    // of kept, and the NEXT row's x and dy are requested before this row is reduced — a warp has two
+    // rows (2 x 6 x 16 B per lane at C = 768) in flight, so 16 warps per SM cover the HBM latency.
+    // (First version: one row in flight per warp, arrays of 48 floats kept across the warp
+    // reductions, 0.38 of the HBM roofline.)
+    uint4 gp[ITER];
+    float dg[ITER][8], db[ITER][8];
 #pragma unroll
     for (int it = 0; it < ITER; ++it) {
-        unpack8(reinterpret_cast<const uint4*>(gamma)[it * 32 + lane], g[it]);
+        gp[it] = reinterpret_cast<const uint4*>(gamma)[it * 32 + lane];
 #pragma unroll
         for (int k = 0; k < 8; ++k) { dg[it][k] = 0.f; db[it][k] = 0.f; }
     }
-    for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < rows; row += (int64_t)gridDim.x * LN_WARPS) {
-        const uint4* xr = reinterpret_cast<const uint4*>(x + row * C);
-        const uint4* dyr = reinterpret_cast<const uint4*>(dy + row * C);
-        const float mean = mean_in[row], rstd = rstd_in[row];
-        float xh[ITER][8], dxh[ITER][8];
+    const int64_t step = (int64_t)gridDim.x * LN_WARPS;
+    int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp;
+    uint4 rx[ITER], rd[ITER];
+    float mean = 0.f, rstd = 0.f;
+    if (row < rows) {
+#pragma unroll
+        for (int it = 0; it < ITER; ++it) {
+            rx[it] = __ldcs(reinterpret_cast<const uint4*>(x + row * C) + it * 32 + lane);
+            rd[it] = __ldcs(reinterpret_cast<const uint4*>(dy + row * C) + it * 32 + lane);
+        }
+        mean = mean_in[row]; rstd = rstd_in[row];
+    }
+    for (; row < rows; row += step) {
+        const int64_t next = row + step;
+        uint4 nx[ITER], nd[ITER];
+        float nmean = 0.f, nrstd = 0.f;
+        if (next < rows) {
+#pragma unroll
+            for (int it = 0; it < ITER; ++it) {
+                nx[it] = __ldcs(reinterpret_cast<const uint4*>(x + next * C) + it * 32 + lane);
+                nd[it] = __ldcs(reinterpret_cast<const uint4*>(dy + next * C) + it * 32 + lane);
+            }
+            nmean = mean_in[next]; nrstd = rstd_in[next];
+        }
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int it = 0; it < ITER; ++it) {
-            float xv[8], dv[8];
-            unpack8(xr[it * 32 + lane], xv);
-            unpack8(dyr[it * 32 + lane], dv);
+            float xv[8], dv[8], g[8];
+            unpack8(rx[it], xv);
+            unpack8(rd[it], dv);
+            unpack8(gp[it], g);
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-                xh[it][k] = (xv[k] - mean) * rstd;
-                dxh[it][k] = dv[k] * g[it][k];
-                s1 += dxh[it][k];
-                s2 += dxh[it][k] * xh[it][k];
-                dg[it][k] += dv[k] * xh[it][k];
+                const float xh = (xv[k] - mean) * rstd, dxh = dv[k] * g[k];
+                s1 += dxh;
+                s2 += dxh * xh;
+                dg[it][k] += dv[k] * xh;
                 db[it][k] += dv[k];
             }
         }
@@ -121,17 +146,23 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         uint4* dxr = reinterpret_cast<uint4*>(dx + row * C);
 #pragma unroll
         for (int it = 0; it < ITER; ++it) {
-            float o[8];
+            float xv[8], dv[8], g[8], o[8];
+            unpack8(rx[it], xv);
+            unpack8(rd[it], dv);
+            unpack8(gp[it], g);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) o[k] = rstd * (dxh[it][k] - s1 - xh[it][k] * s2);
+            for (int k = 0; k < 8; ++k) o[k] = rstd * (dv[k] * g[k] - s1 - (xv[k] - mean) * rstd * s2);
             if (dx_add) {  // residual-stream gradient joins here
                 float r[8];
-                unpack8(reinterpret_cast<const uint4*>(dx_add + row * C)[it * 32 + lane], r);
+                unpack8(__ldcs(reinterpret_cast<const uint4*>(dx_add + row * C) + it * 32 + lane), r);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) o[k] += r[k];
             }
             dxr[it * 32 + lane] = pack8(o);
         }
+#pragma unroll
+        for (int it = 0; it < ITER; ++it) { rx[it] = nx[it]; rd[it] = nd[it]; }
+        mean = nmean; rstd = nrstd;
     }
     // block-level reduction over the 8 warps (fixed order), one partial row per block;
     // the [8][C] staging buffer is used twice (dgamma, then dbeta): 8*2048*4 = 64 KB at most
@@ -155,24 +186,42 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     }
 }
 
-// out[c] = sum_p partials[p * pstride + c].  Block = 32 columns x 8 row groups: thread (x, y)
-// sums rows y, y+8, ... (coalesced 128-byte reads), then the 8 groups are added in a fixed
-// order through shared memory -> deterministic.  Output bf16 or fp32.
-__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ partials,
-                                                              int64_t nparts, int64_t pstride, int cols,
-                                                              void* __restrict__ out, int out_bf16) {
-    __shared__ float sm[8][33];
-    const int x = threadIdx.x & 31, y = threadIdx.x >> 5;
-    const int c = blockIdx.x * 32 + x;
+// out[c] = sum_p partials[p * pstride + c].  Block = 8 columns x 128 row groups: thread (x, y)
+// sums rows y, y+128, ... (32-byte segments), then the 128 groups are added in a fixed order in
+// two levels through shared memory -> deterministic.  Output bf16 or fp32.  blockIdx.y selects a
+// second (partials, out) pair so dgamma and dbeta share a launch.
+// (First version: 32 columns x 8 row groups — with 296 partial rows every thread walked 37
+// dependent L2 round trips, ~25 us per call, and LayerNorm backward made two calls.)
+constexpr int RP_THREADS = 1024;
+__global__ void __launch_bounds__(RP_THREADS) reduce_partials_kernel(const float* __restrict__ partials0,
+                                                                      const float* __restrict__ partials1,
+                                                                      int64_t nparts, int64_t pstride, int cols,
+                                                                      void* __restrict__ out0, void* __restrict__ out1,
+                                                                      int out_bf16) {
+    __shared__ float sm[128][9];
+    __shared__ float sm2[16][9];
+    const float* __restrict__ partials = blockIdx.y ? partials1 : partials0;
+    void* out = blockIdx.y ? out1 : out0;
+    const int x = threadIdx.x & 7, y = threadIdx.x >> 3;
+    const int c = blockIdx.x * 8 + x;
     float s = 0.f;
-    if (c < cols)
-        for (int64_t p = y; p < nparts; p += 8) s += partials[p * pstride + c];
+    if (c < cols) {
+#pragma unroll 4
+        for (int64_t p = y; p < nparts; p += 128) s += partials[p * pstride + c];
+    }
     sm[y][x] = s;
+    __syncthreads();
+    if (y < 16) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += sm[y * 8 + k][x];
+        sm2[y][x] = t;
+    }
     __syncthreads();
     if (y == 0 && c < cols) {
         float t = 0.f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) t += sm[k][x];
+        for (int k = 0; k < 16; ++k) t += sm2[k][x];
         if (out_bf16) reinterpret_cast<__nv_bfloat16*>(out)[c] = __float2bfloat16_rn(t);
         else reinterpret_cast<float*>(out)[c] = t;
     }
@@ -264,10 +313,9 @@ extern "C" int b200_layernorm_bwd(const void* dy, const void* x, const void* gam
     switch (cols / 256) { LN_BWD(1) LN_BWD(2) LN_BWD(3) LN_BWD(4) LN_BWD(5) LN_BWD(6) LN_BWD(7) LN_BWD(8) }
 #undef LN_BWD
     const int64_t nparts = (int64_t)grid;
-    const int rb = (cols + 31) / 32;
-    reduce_partials_kernel<<<rb, 256, 0, s>>>(partials, nparts, 2 * (int64_t)cols, cols, dgamma, grads_bf16);
-    reduce_partials_kernel<<<rb, 256, 0, s>>>(partials + cols, nparts, 2 * (int64_t)cols, cols, dbeta, grads_bf16);
-    b200_count_launch(3);
+    reduce_partials_kernel<<<dim3((cols + 7) / 8, 2), RP_THREADS, 0, s>>>(partials, partials + cols, nparts, 2 * (int64_t)cols,
+                                                                        cols, dgamma, dbeta, grads_bf16);
+    b200_count_launch(2);
     B200_CUDA_OK(cudaGetLastError());
     return 0;
 }
@@ -294,8 +342,8 @@ extern "C" int b200_colsum(const void* x, int64_t ld, int64_t rows, int cols, vo
     cudaStream_t s = (cudaStream_t)stream;
     colsum_stage1_kernel<<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, ld, rows, cols, rows_per,
                                              (float*)scratch, pstride);
-    reduce_partials_kernel<<<(cols + 31) / 32, 256, 0, s>>>((const float*)scratch, chunks, pstride, cols,
-                                                              out, out_bf16);
+    reduce_partials_kernel<<<dim3((cols + 7) / 8, 1), RP_THREADS, 0, s>>>((const float*)scratch, nullptr, chunks, pstride, cols,
+                                                                        out, nullptr, out_bf16);
     b200_count_launch(2);
     B200_CUDA_OK(cudaGetLastError());
     return 0;
