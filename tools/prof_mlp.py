@@ -6,10 +6,14 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, torch.distributed as dist
 os.environ.setdefault("RANK", "0"); os.environ.setdefault("WORLD_SIZE", "1")
 os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29577")
-dist.init_process_group("nccl", device_id=torch.device("cuda", 0))
+LOCAL = int(os.environ.get("LOCAL_RANK", "0"))
+torch.cuda.set_device(LOCAL)
+dist.init_process_group("nccl", device_id=torch.device("cuda", LOCAL))
+if dist.get_rank() != 0:
+    sys.stdout = open(os.devnull, "w")
 from b200ddp import DataParallel, SimpleNet
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 200
-dev = torch.device("cuda", 0)
+dev = torch.device("cuda", LOCAL)
 torch.manual_seed(0)
 eng = DataParallel(SimpleNet().to(dev), backend="b200", compute_dtype=torch.bfloat16)
 xs = torch.randn(64, 64, 784, device=dev); ys = torch.randint(0, 10, (64, 64), device=dev)
