@@ -35,7 +35,7 @@ from .._native import bindings as B
 
 class FusedSession:
     """Native session of the fused step (``csrc/mlp_fused.cu``): ONE launch per step (or per up to
-    64 steps) — an 8-CTA cluster for forward + cross-entropy + backward and ``update_clusters``
+    256 steps) — an 8-CTA cluster for forward + cross-entropy + backward and ``update_clusters``
     more clusters of the same grid for the all-reduce + optimizer; two launches per step when the
     update cannot ride along.  Issued from C without a CUDA graph.  Built for the reference's model
     class (ref ``train.py:32-50``): two hidden layers of 256, at most 16 classes, at most 1024
@@ -223,7 +223,7 @@ class MLPProgram:
 
     def train_many(self, x_pool: torch.Tensor, y_pool: torch.Tensor, first: int, count: int):
         """`count` optimisation steps over an on-device pool of batches ([P, bsz, in], [P, bsz]):
-        step i uses batch (first + i) % P.  One native call; one launch per up to 64 steps when the
+        step i uses batch (first + i) % P.  One native call; one launch per up to 256 steps when the
         update rides in the step launch (FusedSession.update_clusters), else two launches per step."""
         if not self._fused_ok(x_pool[0], y_pool[0]) or not x_pool.is_contiguous() or not y_pool.is_contiguous():
             loss = None

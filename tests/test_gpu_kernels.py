@@ -564,14 +564,15 @@ def test_fused_mlp_update_ctas_match_the_separate_update_kernel(monkeypatch, opt
     xs = torch.randn(7, 64, 784, device=dev)
     xs[:, :, :40] = 0.0          # inputs that are always zero: zero gradients, zero moments (slow-path operands)
     ys = torch.randint(0, 10, (7, 64), device=dev)
-    a.train_steps(xs, ys, 0, 150)      # b: three launches (64 + 64 + 22 steps)
-    b.train_steps(xs, ys, 0, 150)
+    n = 600 if (opt, kw) == ("adam", {}) else 150     # 600: the batches are memorised, gradients and moments tiny
+    a.train_steps(xs, ys, 0, n)        # b: several launches (64 steps each)
+    b.train_steps(xs, ys, 0, n)
     torch.cuda.synchronize()
     assert torch.equal(a.shadow, b.shadow) and torch.equal(a.master, b.master)
     assert torch.equal(a.optimizer.exp_avg, b.optimizer.exp_avg)
     if opt != "sgd":
         assert torch.equal(a.optimizer.exp_avg_sq, b.optimizer.exp_avg_sq)
-    assert b.optimizer.step_dev[0].item() == 150 and a.last_loss().item() == b.last_loss().item()
+    assert b.optimizer.step_dev[0].item() == n and a.last_loss().item() == b.last_loss().item()
     one = b.train_step(xs[1], ys[1])   # a single-step launch after the multi-step ones
     ref = a.train_step(xs[1], ys[1])
     assert one.item() == ref.item() and torch.equal(a.shadow, b.shadow)
