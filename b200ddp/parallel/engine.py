@@ -303,7 +303,7 @@ class DataParallel(nn.Module):
     def train_steps(self, x_pool: torch.Tensor, y_pool: torch.Tensor, first: int, count: int) -> None:
         """`count` optimisation steps over an on-device pool of batches (x_pool [P, B, ...],
         y_pool [P, B]); step i uses batch (first + i) % P.  With the fused MLP session this is ONE
-        native call that issues two launches per step (no Python, no graph replay in the loop);
+        native call that issues one launch per up to 256 steps (no Python, no graph replay in the loop);
         other models loop over ``train_step``.  The loss of the last step is ``last_loss()``."""
         self.check_graphs_current()
         if self.program is not None and count > 0:

@@ -128,7 +128,7 @@ class HostStepper:
     FUSED = -1   # `_live` value while the fused MLP session has a step in flight
 
     def _fused_step(self, hx: torch.Tensor, hy: torch.Tensor) -> Optional[float]:
-        """Fused two-launch MLP step (csrc/mlp_fused.cu): the session copies the pinned batch into
+        """Fused single-launch MLP step (csrc/mlp_fused.cu): the session copies the pinned batch into
         its device ring on a copy stream, launches the step kernel (which stores the loss into
         mapped pinned memory itself) and the update, and hands back the previous step's loss."""
         eng = self.engine

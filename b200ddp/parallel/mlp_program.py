@@ -192,7 +192,7 @@ class MLPProgram:
         self._bufs: Dict[int, _Buffers] = {}
         self._side = torch.cuda.Stream(self.device)
         self.launches_per_step = 0
-        # the fused two-launch step when the model is the reference's shape class
+        # the fused single-launch step when the model is the reference's shape class
         self.fused: Optional[FusedSession] = FusedSession(self) if FusedSession.supports(self) else None
         self._last_fused = False
         if self.fused is not None:

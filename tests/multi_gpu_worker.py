@@ -167,7 +167,7 @@ def check_program(rank, world, dev, sharded, fused=True):
 
 
 def check_program_pool(rank, world, dev):
-    """engine.train_steps (one native call, two launches per step) == the same steps one by one."""
+    """engine.train_steps (one native call, many steps per launch) == the same steps one by one."""
     symm_mod.ONE_SHOT_MAX_BYTES = 2 << 20
     torch.manual_seed(300)
     net = SimpleNet().to(dev)

@@ -435,7 +435,7 @@ def test_mlp_program_trains_and_evaluates():
 
 # ------------------------------------------------------------------ fused cluster-kernel step
 def _engine_pair(monkeypatch, dropout=0.0, seed=21):
-    """Two engines on the same weights: the fused two-launch session and the GEMM-per-layer graph."""
+    """Two engines on the same weights: the fused single-launch session and the GEMM-per-layer graph."""
     from b200ddp.models.simplenet import SimpleNet
     from b200ddp.parallel.engine import DataParallel
     torch.manual_seed(seed)
@@ -523,7 +523,7 @@ def test_fused_mlp_dropout_is_a_mask_with_the_right_rate(monkeypatch):
 
 
 def test_fused_mlp_train_steps_over_a_device_pool(monkeypatch):
-    """engine.train_steps (one native call, two launches per step) == the same steps one by one,
+    """engine.train_steps (one native call, many steps per launch) == the same steps one by one,
     dropout included (the mask depends on the step number only)."""
     from b200ddp.models.simplenet import SimpleNet
     from b200ddp.parallel.engine import DataParallel
@@ -786,7 +786,7 @@ def test_host_stepper_matches_train_step(model):
     assert stepper.finish() is None               # nothing pending any more
     want = [b.train_step(hx[i].to(dev), hy[i].to(dev)).item() for i in range(steps)]
     assert len(got) == steps and a.optimizer.step_count == b.optimizer.step_count == steps
-    if model == "simplenet":                      # the native path was taken: fused two-launch session ...
+    if model == "simplenet":                      # the native path was taken: fused session ...
         assert a.program.fused is not None and a.program.fused.host_ready and not stepper._runners
     else:                                         # ... or the graph runner
         assert len(stepper._runners) == 1
