@@ -203,6 +203,9 @@ def run_ours(args):
                              f"({n * (bsz * IN_FEATURES * 4 + bsz * 8) / 2**20:.0f} MiB) larger than L2"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": gpu_launches,
             "launches_per_step": per_step,
+            # one launch of the fused step kernel runs many whole steps (forward, loss, backward,
+            # all-reduce, Adam each); kernels_per_step counts the kernels a step's work runs in
+            "steps_per_launch": (args.steps / gpu_launches) if gpu_launches else None,
         }
         print(json.dumps(out), flush=True)
     dist.destroy_process_group()
