@@ -53,7 +53,7 @@ if os.environ.get("B200DDP_MLP_TRACE"):
         t0 = a[0]
         print("merged-update wall clock (globaltimer ns since the earlier launch's entry): earlier launch | later launch")
         for i, nm in enumerate(un):
-            if nm != "-":
+            if nm != "-" and a[i] and abs(a[i] - t0) < 10**9:     # marks this path does not write stay zero
                 print(f"  {nm:18s} {a[i] - t0:8d} {b[i] - t0:8d}")
         print(f"  last update CTA counted in (any step) {ub[32] - t0:8d}; compute saw the update (last time) {ub[33] - t0:8d}")
     names = ["entry", "x staged", "cta sync", "P1 mma done", "P1 drained", "cluster sync 1", "F1 done", "P2 mma done",
