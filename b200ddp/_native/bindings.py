@@ -102,6 +102,8 @@ def declare(L: C.CDLL) -> None:
     L.b200_mlp_host_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_float),
                                      C.POINTER(C.c_int), C.c_void_p]
     L.b200_mlp_host_finish.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_void_p]
+    L.b200_mlp_host_run.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
+    L.b200_mlp_host_run.restype = C.c_int
     L.b200_mlp_update_clusters.argtypes = [C.c_void_p]
     L.b200_mlp_update_clusters.restype = C.c_int
     for name in ("b200_mlp_create", "b200_mlp_destroy", "b200_mlp_forward_backward", "b200_mlp_train",

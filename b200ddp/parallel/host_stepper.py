@@ -18,6 +18,7 @@ other models after ``DataParallel.GRAPH_WARMUP_STEPS`` eager steps) ``step`` tak
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, Optional
 
 import torch
@@ -149,6 +150,68 @@ class HostStepper:
         if same and self._valid.value:
             return float(self._prev.value)
         return prev
+
+    # ------------------------------------------------------------------ many steps per call
+    def run(self, batches) -> list:
+        """Trains on every (pinned_x, pinned_y) of `batches` and returns their losses.  For the fused MLP
+        session this is ONE native call: each step still copies its own inputs host -> device and
+        hands its own loss back to the host (ref train.py:133, :141), but the kernel launches run
+        up to 256 steps each and wait for every step's input copy themselves.  Other models: a
+        loop over ``step``."""
+        batches = list(batches)
+        if not batches:
+            return []
+        ptrs = self._fused_run_ok(batches[0][0], batches[0][1])
+        if not ptrs or any(b[0].shape != batches[0][0].shape or not b[0].is_pinned() for b in batches):
+            out = []
+            for hx, hy in batches:
+                prev = self.step(hx, hy)
+                if prev is not None:
+                    out.append(prev)
+            out.append(self.finish())
+            return out[-len(batches):]
+        import numpy as np
+        xp = np.fromiter((b[0].data_ptr() for b in batches), dtype=np.uint64, count=len(batches))
+        yp = np.fromiter((b[1].data_ptr() for b in batches), dtype=np.uint64, count=len(batches))
+        return self._fused_run(xp, yp, batches[0][0].shape[0])
+
+    def run_pool(self, x_pool: torch.Tensor, y_pool: torch.Tensor, first: int, count: int) -> list:
+        """``run`` over a pinned host pool x_pool [P, B, ...] / y_pool [P, B]: step i trains on batch
+        (first + i) % P.  The host-memory counterpart of ``engine.train_steps``."""
+        P = x_pool.shape[0]
+        if (count > 0 and x_pool.is_pinned() and y_pool.is_pinned() and x_pool.is_contiguous() and y_pool.is_contiguous()
+                and self._fused_run_ok(x_pool[0], y_pool[0])):
+            import numpy as np
+            idx = (first + np.arange(count, dtype=np.uint64)) % np.uint64(P)
+            xp = np.uint64(x_pool.data_ptr()) + idx * np.uint64(x_pool.stride(0) * x_pool.element_size())
+            yp = np.uint64(y_pool.data_ptr()) + idx * np.uint64(y_pool.stride(0) * y_pool.element_size())
+            return self._fused_run(xp, yp, x_pool.shape[1])
+        return self.run([(x_pool[(first + i) % P], y_pool[(first + i) % P]) for i in range(count)])
+
+    def _fused_run_ok(self, hx: torch.Tensor, hy: torch.Tensor) -> bool:
+        eng = self.engine
+        return bool(eng.program is not None and eng.program._fused_ok(hx, hy) and eng.program.fused.update_clusters > 0
+                    and hx.is_contiguous() and hy.is_contiguous() and os.environ.get("B200DDP_MLP_EVENT_WAIT") is None)
+
+    def _fused_run(self, xp, yp, bsz: int) -> list:
+        import numpy as np
+        eng = self.engine
+        fs = eng.program.fused
+        L = nat.lib()
+        if not fs.host_ready:
+            nat.check(L.b200_mlp_host_init(fs.handle, fs.MAX_BATCH, self.slots), "b200_mlp_host_init")
+            fs.host_ready = True
+        carried = self._take_previous()       # a step submitted through step() is finished first
+        if carried is not None:
+            self._carry = carried
+        eng.program._leave_gemm_path()
+        n = int(xp.shape[0])
+        losses = np.empty(n, dtype=np.float32)
+        nat.check(L.b200_mlp_host_run(fs.handle, xp.ctypes.data, yp.ctypes.data, n, int(bsz), losses.ctypes.data,
+                                      nat.stream_ptr(self.device)), "b200_mlp_host_run")
+        eng.optimizer.step_count += n
+        eng._step_index += n
+        return losses.tolist()
 
     def _take_previous(self) -> Optional[float]:
         """Loss of the last submitted step, whichever path it took; clears the pending state."""

@@ -164,17 +164,22 @@ def run_ours(args):
         # copies its inputs host->device and its loss device->host (read one step late, so a
         # step is always queued behind the running one); the per-step host work is one native
         # call (csrc/runner.cu).
-        stepper = engine.host_stepper()
+        stepper = engine.host_stepper(slots=4)
         losses = []
+        use_run = hasattr(stepper, "run_pool") and os.environ.get("B200DDP_BENCH_E2E_STEP") is None
 
         def e2e_step(first, count):
+            if use_run:     # one native call for `count` steps; every step still has its own H2D and its own loss
+                losses.extend(stepper.run_pool(hx, hy, first, count))
+                return
             for i in range(first, first + count):
                 prev = stepper.step(hx[i % n], hy[i % n])
                 if prev is not None:
                     losses.append(prev)
 
         def e2e_end():
-            losses.append(stepper.finish())     # the last step's loss, inside the timed region
+            if not use_run:
+                losses.append(stepper.finish())     # the last step's loss, inside the timed region
 
         torch.cuda.synchronize()
         t_ms, _ = timed(e2e_step, args.steps, args.warmup, device, sample_clocks=False, fn_end=e2e_end)
@@ -185,7 +190,10 @@ def run_ours(args):
                "h2d_bytes_per_step": bsz * IN_FEATURES * 4 + bsz * 8,
                "d2h_bytes_per_step": 8,   # the loss and its sequence number, stored to pinned host memory
                "host_loss_is_finite": all(l == l for l in host_loss),
-               "final_loss": float(host_loss[-1]), "api": "DataParallel.host_stepper().step(pinned_x, pinned_y)"}
+               "final_loss": float(host_loss[-1]),
+               "api": ("DataParallel.host_stepper().run_pool(pinned_x_pool, pinned_y_pool, first, count): per step one "
+                       "H2D of that step's batch and one loss to the host, up to 256 steps per kernel launch")
+               if use_run else "DataParallel.host_stepper().step(pinned_x, pinned_y)"}
 
     if rank == 0:
         out = {

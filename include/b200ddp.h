@@ -411,6 +411,12 @@ int b200_mlp_host_init(void* session, int bsz, int slots);
 int b200_mlp_host_step(void* session, const void* host_x, const void* host_y, int bsz, float* prev_loss,
                        int* prev_valid, void* stream);
 int b200_mlp_host_finish(void* session, float* last_loss, int* valid, void* stream);
+/* `n` steps on `n` pinned host batches (host_x[i] fp32 [bsz,in], host_y[i] int64 [bsz]) in one call:
+ * every step's inputs are copied host -> device and its loss comes back into losses[i], but a launch
+ * runs up to 256 steps — the kernel itself waits for each step's input copy.  Needs the update CTAs
+ * (b200_mlp_update_clusters > 0) and b200_mlp_host_init; may be mixed with b200_mlp_host_step calls. */
+int b200_mlp_host_run(void* session, const void* const* host_x, const void* const* host_y, int64_t n, int bsz,
+                      float* losses, void* stream);
 
 /* Broadcast of [offset_bytes, offset_bytes + nbytes) of rank `root`'s c->push arena into every
  * rank's (multiples of 16 bytes).  One kernel on every rank with an entry and an exit flag barrier;

@@ -578,6 +578,41 @@ def test_fused_mlp_update_ctas_match_the_separate_update_kernel(monkeypatch, opt
     assert one.item() == ref.item() and torch.equal(a.shadow, b.shadow)
 
 
+def test_host_stepper_run_matches_step_by_step():
+    """stepper.run / run_pool (one native call, the kernel waits for every step's own input copy) ==
+    the same pinned batches through stepper.step one by one: losses and parameters bit for bit,
+    also when the two are mixed and when a run spans several launches."""
+    from b200ddp.models.simplenet import SimpleNet
+    from b200ddp.parallel.engine import DataParallel
+    torch.manual_seed(21)
+    dev = torch.device("cuda")
+    net = SimpleNet().to(dev)
+    a = DataParallel(copy.deepcopy(net), backend="b200", compute_dtype=torch.bfloat16, lr=1e-3)
+    b = DataParallel(copy.deepcopy(net), backend="b200", compute_dtype=torch.bfloat16, lr=1e-3)
+    P = 9
+    hx = torch.randn(P, 64, 784).pin_memory()
+    hy = torch.randint(0, 10, (P, 64)).pin_memory()
+    sa, sb = a.host_stepper(slots=4), b.host_stepper(slots=4)
+    n = 300                                        # > 256: two launches inside one run
+    want = []
+    for i in range(n + 12):
+        prev = sa.step(hx[i % P], hy[i % P])
+        if prev is not None:
+            want.append(prev)
+    want.append(sa.finish())
+    got = sb.run_pool(hx, hy, 0, n)
+    assert len(got) == n
+    first = sb.step(hx[n % P], hy[n % P])           # mixing: a single step, then a list-based run, then one more step
+    assert first is None
+    tail = sb.run([(hx[i % P], hy[i % P]) for i in range(n + 1, n + 11)])
+    last = sb.step(hx[(n + 11) % P], hy[(n + 11) % P])
+    got += [last] + tail + [sb.finish()]
+    torch.cuda.synchronize()
+    assert got == want
+    assert torch.equal(a.shadow, b.shadow) and torch.equal(a.master, b.master)
+    assert b.optimizer.step_count == n + 12 and b.optimizer.step_dev[0].item() == n + 12
+
+
 def test_engine_checkpoint_roundtrip_on_gpu(tmp_path, reference_module):
     from b200ddp import load_checkpoint, save_checkpoint
     from b200ddp.models.simplenet import SimpleNet
