@@ -89,8 +89,8 @@ def _step_path(engine) -> str:
     k = prog.fused.update_clusters
     if k:
         return (f"one kernel: 8-CTA compute cluster (fwd+CE+bwd) + {k} update clusters (all-reduce + Adam) in the "
-                "same launch, up to 256 steps per launch with counter hand-overs (engine.train_steps); the "
-                "end-to-end arm launches it once per step")
+                "same launch, up to 256 steps per launch with counter hand-overs (engine.train_steps; the end-to-end "
+                "arm feeds the same launches from pinned host batches, host_stepper.run_pool)")
     return "fused cluster kernel (fwd+CE+bwd) + fused all-reduce/Adam kernel, launched from C (engine.train_steps)"
 
 

@@ -184,6 +184,28 @@ def check_program_pool(rank, world, dev):
     log("train_steps over a device pool == 50 single steps (bit-identical), back-to-back no-exit-wait kernels")
 
 
+def check_host_run(rank, world, dev):
+    """host_stepper.run_pool (pinned host batches, the kernel waits for every step's own copy, many
+    steps per launch) == engine.train_steps on the same batches resident on the device."""
+    symm_mod.ONE_SHOT_MAX_BYTES = 2 << 20
+    torch.manual_seed(500)
+    net = SimpleNet().to(dev)
+    a = DataParallel(copy.deepcopy(net), backend="b200", compute_dtype=torch.bfloat16, lr=1e-3)
+    b = DataParallel(copy.deepcopy(net), backend="b200", compute_dtype=torch.bfloat16, lr=1e-3)
+    torch.manual_seed(600 + rank)
+    hx = torch.randn(5, 64, 784).pin_memory(); hy = torch.randint(0, 10, (5, 64)).pin_memory()
+    a.train_steps(hx.to(dev), hy.to(dev), 0, 70)
+    losses = b.host_stepper(slots=4).run_pool(hx, hy, 0, 70)
+    torch.cuda.synchronize()
+    assert len(losses) == 70 and all(l == l for l in losses)
+    assert torch.equal(a.shadow, b.shadow), rel(a.shadow, b.shadow)
+    assert abs(losses[-1] - a.last_loss().item()) == 0.0
+    gs = [torch.empty_like(b.shadow) for _ in range(world)]
+    dist.all_gather(gs, b.shadow)
+    assert all(torch.equal(gs[0], t) for t in gs), "replicas diverged under host_stepper.run_pool"
+    log("host_stepper.run_pool over pinned batches == train_steps on the device (bit-identical), replicas identical")
+
+
 def check_buffer_broadcast(rank, world, dev):
     """K4: module buffers follow rank 0 before every training forward — our broadcast kernel on the
     peer-mapped buffer arenas (captured in the step graph), no NCCL call on the step."""
@@ -269,6 +291,7 @@ def main():
         check_program(rank, world, dev, sharded, fused=True)
     check_program(rank, world, dev, True, fused=False)
     check_program_pool(rank, world, dev)
+    check_host_run(rank, world, dev)
     check_buffer_broadcast(rank, world, dev)
     check_autograd_overlap(rank, world, dev)
     dist.barrier()
