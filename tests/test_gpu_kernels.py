@@ -830,6 +830,11 @@ def test_host_stepper_matches_train_step(model):
     # (split-K / bias-gradient atomics make two GPT-2 runs differ in the last bits; 12 Adam steps amplify it)
     assert rel_err(a.master, b.master) < 4e-3
     stepper.close()
+    # run(): one native call on the fused session, a loop over step() for every other model
+    more = stepper.run([(hx[i], hy[i]) for i in range(4)])
+    assert len(more) == 4 and all(l == l for l in more) and a.optimizer.step_count == steps + 4
+    assert stepper.finish() is None
+    stepper.close()
 
 
 @pytest.mark.parametrize("model", ["simplenet", "gpt2"])
