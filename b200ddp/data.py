@@ -237,6 +237,36 @@ class BatchLoader:
             yield hx[:n], hy[:n]
 
 
+    def host_epoch(self, max_bytes: int = 1 << 30):
+        """This epoch's shard as ONE pinned pool for ``HostStepper.run_pool``: ``(x [nb, B, ...],
+        y [nb, B], tail)`` with the nb full batches in sampler order and ``tail`` the short last
+        batch ``(hx, hy)`` or None.  The pinned buffers belong to the loader and are
+        refilled every epoch; returns None when the shard is larger than `max_bytes`."""
+        if not self._cuda or self._resident:
+            raise RuntimeError("host_epoch needs a CUDA target device and a host-resident data set")
+        d = self.dataset
+        idx = self.sampler.indices()
+        B = self.batch_size
+        nb, rem = idx.numel() // B, idx.numel() % B
+        per = d.data[0].numel() * d.data.element_size() + d.labels[0].numel() * d.labels.element_size()
+        if nb == 0 or idx.numel() * per > max_bytes:
+            return None
+        pool = getattr(self, "_host_pool", None)
+        if pool is None or pool[0].shape[0] < nb + 1:
+            pool = self._host_pool = (
+                torch.empty(nb + 1, B, *d.data.shape[1:], dtype=d.data.dtype).pin_memory(),
+                torch.empty(nb + 1, B, *d.labels.shape[1:], dtype=d.labels.dtype).pin_memory())
+        xp, yp = pool
+        torch.index_select(d.data, 0, idx[:nb * B], out=xp[:nb].view(nb * B, *d.data.shape[1:]))
+        torch.index_select(d.labels, 0, idx[:nb * B], out=yp[:nb].view(nb * B, *d.labels.shape[1:]))
+        tail = None
+        if rem:
+            torch.index_select(d.data, 0, idx[nb * B:], out=xp[nb, :rem])
+            torch.index_select(d.labels, 0, idx[nb * B:], out=yp[nb, :rem])
+            tail = (xp[nb, :rem], yp[nb, :rem])
+        return xp[:nb], yp[:nb], tail
+
+
 def create_data_loader(
     dataset: SyntheticDataset,
     batch_size: int,

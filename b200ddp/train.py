@@ -90,6 +90,30 @@ def train_epoch(engine, loader, device, epoch: int, rank: int, log_interval: int
             if idx % log_interval == 0 and rank == 0:
                 logger.info(f"Epoch {epoch}, Batch {idx}/{n}, Loss: {value:.4f}")
 
+        # Fused MLP session: the whole shard of the epoch as one pinned pool, `log_interval`-sized
+        # native calls (each step still copies its own batch and reports its own loss; up to 256
+        # steps per kernel launch — HostStepper.run_pool)
+        epoch_pool = None
+        if (fault is None and hasattr(loader, "host_epoch") and os.environ.get("B200DDP_NO_HOST_RUN") is None
+                and engine.program is not None and getattr(engine.program, "fused", None) is not None
+                and engine.program.fused.update_clusters > 0):
+            epoch_pool = loader.host_epoch()
+        if epoch_pool is not None and stepper._fused_run_ok(epoch_pool[0][0], epoch_pool[1][0]):
+            xp, yp, tail = epoch_pool
+            nb = xp.shape[0]
+            chunk = max(int(log_interval), 1) * 8
+            for c0 in range(0, nb, chunk):
+                with nvtx_range("train_steps"):
+                    got = stepper.run_pool(xp, yp, c0, min(chunk, nb - c0))
+                for j, value in enumerate(got):
+                    account(c0 + j, value)
+            num_batches = nb
+            if tail is not None:
+                prev = stepper.step(*tail)
+                last = stepper.finish()
+                account(nb, last if last is not None else prev)
+                num_batches += 1
+            return total / max(1, num_batches)
         for batch_idx, (hx, hy) in enumerate(loader.host_batches()):
             if fault is not None and fault == (rank, global_step + batch_idx):
                 logger.error(f"injected fault at step {global_step + batch_idx}")

@@ -613,6 +613,35 @@ def test_host_stepper_run_matches_step_by_step():
     assert b.optimizer.step_count == n + 12 and b.optimizer.step_dev[0].item() == n + 12
 
 
+def test_train_epoch_through_run_pool_matches_the_per_batch_path(monkeypatch):
+    """train.train_epoch on a host-resident data set: the epoch's shard as one pinned pool through
+    HostStepper.run_pool (plus the short last batch through step) == one stepper.step per batch."""
+    from b200ddp.data import SyntheticDataset, create_data_loader
+    from b200ddp.models.simplenet import SimpleNet
+    from b200ddp.parallel.engine import DataParallel
+    from b200ddp.train import train_epoch
+    torch.manual_seed(31)
+    dev = torch.device("cuda")
+    net = SimpleNet().to(dev)
+    ds = SyntheticDataset(64 * 37 + 19)                    # 37 full batches and a tail of 19
+    out = []
+    for per_batch in (False, True):
+        if per_batch:
+            monkeypatch.setenv("B200DDP_NO_HOST_RUN", "1")
+        eng = DataParallel(copy.deepcopy(net), backend="b200", compute_dtype=torch.bfloat16, lr=1e-3)
+        loader, sampler = create_data_loader(ds, 64, 0, 1, device=dev, seed=7)
+        avg = []
+        for epoch in range(2):
+            sampler.set_epoch(epoch)
+            avg.append(train_epoch(eng, loader, dev, epoch, rank=0))
+        torch.cuda.synchronize()
+        out.append((avg, eng.shadow.clone(), eng.optimizer.step_count))
+    (avg_a, sh_a, n_a), (avg_b, sh_b, n_b) = out
+    assert n_a == n_b == 2 * 38
+    assert torch.equal(sh_a, sh_b)
+    assert all(abs(x - y) < 1e-6 for x, y in zip(avg_a, avg_b)), (avg_a, avg_b)
+
+
 def test_engine_checkpoint_roundtrip_on_gpu(tmp_path, reference_module):
     from b200ddp import load_checkpoint, save_checkpoint
     from b200ddp.models.simplenet import SimpleNet
