@@ -81,63 +81,38 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
 
 // partials layout: [gridDim.x * LN_WARPS][2][C] fp32 (dgamma then dbeta)
 template <int ITER>
-__global__ void __launch_bounds__(LN_WARPS * 32, ITER <= 3 ? 2 : 1)
+__global__ void __launch_bounds__(LN_WARPS * 32)
 layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean_in,
                      const float* __restrict__ rstd_in, __nv_bfloat16* __restrict__ dx,
                      const __nv_bfloat16* __restrict__ dx_add, float* __restrict__ partials, int64_t rows) {
     constexpr int C = ITER * 256;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // Registers: gamma stays packed (bf16), xhat / dy*gamma are recomputed in the second pass instead
-    // of kept, and the NEXT row's x and dy are requested before this row is reduced — a warp has two
-    // rows (2 x 6 x 16 B per lane at C = 768) in flight, so 16 warps per SM cover the HBM latency.
-    // (First version: one row in flight per warp, arrays of 48 floats kept across the warp
-    // reductions, 0.38 of the HBM roofline.)
-    uint4 gp[ITER];
-    float dg[ITER][8], db[ITER][8];
+    float g[ITER][8], dg[ITER][8], db[ITER][8];
 #pragma unroll
     for (int it = 0; it < ITER; ++it) {
-        gp[it] = reinterpret_cast<const uint4*>(gamma)[it * 32 + lane];
+        unpack8(reinterpret_cast<const uint4*>(gamma)[it * 32 + lane], g[it]);
 #pragma unroll
         for (int k = 0; k < 8; ++k) { dg[it][k] = 0.f; db[it][k] = 0.f; }
     }
-    const int64_t step = (int64_t)gridDim.x * LN_WARPS;
-    int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp;
-    uint4 rx[ITER], rd[ITER];
-    float mean = 0.f, rstd = 0.f;
-    if (row < rows) {
-#pragma unroll
-        for (int it = 0; it < ITER; ++it) {
-            rx[it] = __ldcs(reinterpret_cast<const uint4*>(x + row * C) + it * 32 + lane);
-            rd[it] = __ldcs(reinterpret_cast<const uint4*>(dy + row * C) + it * 32 + lane);
-        }
-        mean = mean_in[row]; rstd = rstd_in[row];
-    }
-    for (; row < rows; row += step) {
-        const int64_t next = row + step;
-        uint4 nx[ITER], nd[ITER];
-        float nmean = 0.f, nrstd = 0.f;
-        if (next < rows) {
-#pragma unroll
-            for (int it = 0; it < ITER; ++it) {
-                nx[it] = __ldcs(reinterpret_cast<const uint4*>(x + next * C) + it * 32 + lane);
-                nd[it] = __ldcs(reinterpret_cast<const uint4*>(dy + next * C) + it * 32 + lane);
-            }
-            nmean = mean_in[next]; nrstd = rstd_in[next];
-        }
+    for (int64_t row = (int64_t)blockIdx.x * LN_WARPS + warp; row < rows; row += (int64_t)gridDim.x * LN_WARPS) {
+        const uint4* xr = reinterpret_cast<const uint4*>(x + row * C);
+        const uint4* dyr = reinterpret_cast<const uint4*>(dy + row * C);
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float xh[ITER][8], dxh[ITER][8];
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int it = 0; it < ITER; ++it) {
-            float xv[8], dv[8], g[8];
-            unpack8(rx[it], xv);
-            unpack8(rd[it], dv);
-            unpack8(gp[it], g);
+            float xv[8], dv[8];
+            unpack8(xr[it * 32 + lane], xv);
+            unpack8(dyr[it * 32 + lane], dv);
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-                const float xh = (xv[k] - mean) * rstd, dxh = dv[k] * g[k];
-                s1 += dxh;
-                s2 += dxh * xh;
-                dg[it][k] += dv[k] * xh;
+                xh[it][k] = (xv[k] - mean) * rstd;
+                dxh[it][k] = dv[k] * g[it][k];
+                s1 += dxh[it][k];
+                s2 += dxh[it][k] * xh[it][k];
+                dg[it][k] += dv[k] * xh[it][k];
                 db[it][k] += dv[k];
             }
         }
@@ -146,23 +121,17 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
         uint4* dxr = reinterpret_cast<uint4*>(dx + row * C);
 #pragma unroll
         for (int it = 0; it < ITER; ++it) {
-            float xv[8], dv[8], g[8], o[8];
-            unpack8(rx[it], xv);
-            unpack8(rd[it], dv);
-            unpack8(gp[it], g);
+            float o[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) o[k] = rstd * (dv[k] * g[k] - s1 - (xv[k] - mean) * rstd * s2);
+            for (int k = 0; k < 8; ++k) o[k] = rstd * (dxh[it][k] - s1 - xh[it][k] * s2);
             if (dx_add) {  // residual-stream gradient joins here
                 float r[8];
-                unpack8(__ldcs(reinterpret_cast<const uint4*>(dx_add + row * C) + it * 32 + lane), r);
+                unpack8(reinterpret_cast<const uint4*>(dx_add + row * C)[it * 32 + lane], r);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) o[k] += r[k];
             }
             dxr[it * 32 + lane] = pack8(o);
         }
-#pragma unroll
-        for (int it = 0; it < ITER; ++it) { rx[it] = nx[it]; rd[it] = nd[it]; }
-        mean = nmean; rstd = nrstd;
     }
     // block-level reduction over the 8 warps (fixed order), one partial row per block;
     // the [8][C] staging buffer is used twice (dgamma, then dbeta): 8*2048*4 = 64 KB at most
