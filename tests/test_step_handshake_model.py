@@ -149,3 +149,73 @@ def test_skipping_the_entry_barrier_is_caught():
 def test_ticket_chain_never_deadlocks_with_one_update_cta():
     for seed in range(30):
         assert run(3, 1, 6, random.Random(seed)) is None
+
+
+# --------------------------------------------------------------------------- end-to-end ring
+def run_ring(steps, slots, lookahead, loss_ring, rng):
+    """b200_mlp_host_run: the host feeds pinned batches into `slots` device slots (copy, then the
+    step's sequence number), at most `lookahead` steps ahead of the last loss it has read; the kernel
+    waits for slot[t % slots] >= t + 1, reads the batch (a read is not atomic), publishes loss t + 1
+    into ring[t % loss_ring]; the host reads losses in order.  Checks: the kernel only ever reads
+    the batch of its own step, start to end; the host reads every loss before it is overwritten."""
+    slot_data = [None] * slots          # step whose batch sits in the slot (None: garbage)
+    slot_flag = [0] * slots             # sequence number written behind the batch
+    ring = [(0, None)] * loss_ring      # (sequence number, loss of which step)
+    fed = got = 0
+    k = {"t": 0, "pc": "wait", "seen": None}
+    host_pc = "feed"
+    budget = 200 * steps
+    while got < steps:
+        budget -= 1
+        if budget < 0:
+            return "deadlock / livelock"
+        if rng.random() < 0.5:                                   # host
+            if host_pc == "feed" and fed < steps and fed - got < lookahead:
+                slot_data[fed % slots] = fed                     # the copy
+                host_pc = "flag"
+            elif host_pc == "flag":
+                slot_flag[fed % slots] = fed + 1                 # stream-ordered behind the copy
+                fed += 1
+                host_pc = "feed"
+            elif ring[got % loss_ring][0] >= got + 1:            # loss of step `got` has arrived
+                if ring[got % loss_ring] != (got + 1, got):
+                    return f"host read loss slot {ring[got % loss_ring]} for step {got}"
+                got += 1
+        else:                                                    # kernel
+            t = k["t"]
+            if t >= steps:
+                continue
+            if k["pc"] == "wait":
+                if slot_flag[t % slots] >= t + 1:
+                    k["pc"] = "read_begin"
+            elif k["pc"] == "read_begin":
+                k["seen"] = slot_data[t % slots]
+                k["pc"] = "read_end"
+            elif k["pc"] == "read_end":
+                if k["seen"] != t or slot_data[t % slots] != t:
+                    return f"step {t} read the batch of step {k['seen']}/{slot_data[t % slots]}"
+                k["pc"] = "publish"
+            elif k["pc"] == "publish":
+                ring[t % loss_ring] = (t + 1, t)
+                k["t"], k["pc"] = t + 1, "wait"
+    return None
+
+
+@pytest.mark.parametrize("slots", [2, 3, 4])
+def test_input_ring_is_safe_with_slots_minus_one_steps_in_flight(slots):
+    for seed in range(40):
+        assert run_ring(60, slots, slots - 1, 8, random.Random(seed)) is None, seed
+
+
+def test_feeding_as_many_steps_ahead_as_there_are_slots_is_safe_too_but_one_more_is_caught():
+    # `slots` in flight is still safe in this model (a slot is rewritten only after the loss of the
+    # step that read it); the native loop keeps one slot of margin.  slots + 1 overwrites a batch
+    # that has not been read.
+    assert all(run_ring(60, 3, 3, 8, random.Random(s)) is None for s in range(40))
+    hits = sum(run_ring(60, 3, 4, 8, random.Random(s)) is not None for s in range(40))
+    assert hits >= 30
+
+
+def test_a_loss_ring_shorter_than_the_lookahead_is_caught():
+    hits = sum(run_ring(60, 4, 3, 2, random.Random(s)) is not None for s in range(40))
+    assert hits >= 20
