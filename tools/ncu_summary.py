@@ -70,6 +70,13 @@ def main():
     with open(os.path.join(OUT, "INDEX.md"), "w") as f:
         f.write("# ncu captures, one launch per kernel family (round 2)\n\nWritten by `tools/ncu_summary.py` from the reports "
                 "`tools/gpu_r2_ncu_families.sh` brings back.  Durations are cold-cache, serialised launches.\n\n"
+                "Not here: the multi-GPU collectives (`allreduce_optimizer_kernel`, `allreduce_kernel`, `broadcast_kernel`, the "
+                "update CTAs of `mlp_step_kernel` at W > 1).  ncu on this pool is for one GPU only (a multi-rank command under it "
+                "replays every kernel ~40 times against peers that have moved on), so NVLink byte counters cannot be captured; "
+                "their evidence is the CUDA-event sweeps with per-algorithm rooflines (`../r2_allreduce_sweep_bf16_4gpu.txt`, "
+                "`../r1_call9_allreduce_sweep_bf16_8gpu_nvls.txt`), the SASS listings (`../sass/allreduce_optimizer_kernel.sass`: "
+                "`multimem.ld_reduce` / `multimem.st`, fence counts) and the in-kernel wall-clock trace of the 8-GPU step "
+                "(`../mlp_fused_timeline.md`).  `mlp_step` below is the single-GPU launch of the same kernel (24 steps).\n\n"
                 "| capture | kernel | us | DRAM GB/s | of copy bandwidth | tensor pipe % |\n|---|---|---|---|---|---|\n")
         for name, kernel, us, gbs, tensor in index:
             t = f"{float(tensor):.1f}" if tensor not in ("", "n/a") and float(tensor) > 0 else ""
