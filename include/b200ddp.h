@@ -418,6 +418,16 @@ int b200_mlp_host_finish(void* session, float* last_loss, int* valid, void* stre
 int b200_mlp_host_run(void* session, const void* const* host_x, const void* const* host_y, int64_t n, int bsz,
                       float* losses, void* stream);
 
+/* Tuning aids (tools/prof_mlp.py, tools/fa_check.py); they synchronise the device.
+ * b200_mlp_debug_trace: clock64 of thread 0 of the 8 compute CTAs at 24 phase boundaries of the last
+ * fused-step launch made with B200DDP_MLP_TRACE set (out: long long[8 * 24]).
+ * b200_mlp_debug_utrace: globaltimer (ns) marks of the compute cluster and of the first / last update
+ * CTA for the last two single-launch steps (out: unsigned long long[34]).
+ * b200_flash_debug_trace: clock64 of one softmax thread per step with B200DDP_FA_TRACE set (long long[128]). */
+int b200_mlp_debug_trace(long long* out);
+int b200_mlp_debug_utrace(unsigned long long* out);
+int b200_flash_debug_trace(long long* out);
+
 /* Broadcast of [offset_bytes, offset_bytes + nbytes) of rank `root`'s c->push arena into every
  * rank's (multiples of 16 bytes).  One kernel on every rank with an entry and an exit flag barrier;
  * capturable like the other collectives.  ref: train.py:136 (DDP forward -> _sync_buffers, the
