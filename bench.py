@@ -45,6 +45,10 @@ def parse():
     p.add_argument("--ref-backend", default="nccl", choices=["nccl", "gloo"],
                    help="reference arm: nccl = one-word backend delta (SURVEY §6); gloo = as shipped")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--dtype", choices=["bf16", "fp32"], default="bf16",
+                   help="this framework's arm only: fp32 = the reference arm's precision (torch autograd with fp32 "
+                        "cuBLAS GEMMs, TF32 off, under the engine's whole-step graph and fused all-reduce + Adam kernel); "
+                        "bf16 (BASELINE.json's config) = the fused tcgen05 step kernel")
     return p.parse_args()
 
 
@@ -84,7 +88,10 @@ def max_over_ranks(v: float, device) -> float:
 
 def _step_path(engine) -> str:
     prog = engine.program
-    if prog is None or prog.fused is None:
+    if prog is None:
+        return ("torch autograd forward / backward (ATen + cuBLAS in the compute dtype, TF32 off) inside the engine's "
+                "whole-step CUDA graph, fused all-reduce + Adam kernel of this framework")
+    if prog.fused is None:
         return "GEMM-per-layer CUDA graph"
     k = prog.fused.update_clusters
     if k:
@@ -133,8 +140,9 @@ def run_ours(args):
     assert nat.available()
     torch.manual_seed(1234)
     backend = args.backend if world > 1 else "b200"
+    fp32 = args.dtype == "fp32"
     engine = DataParallel(SimpleNet().to(device), optimizer="adam", lr=1e-3, backend=backend,
-                          compute_dtype=torch.bfloat16)
+                          compute_dtype=torch.float32 if fp32 else torch.bfloat16)
     bsz = args.batch_size
     xs, ys, n = make_pool(bsz, device, pinned=False, seed=100 + rank)
 
@@ -153,6 +161,12 @@ def run_ours(args):
 
     ms, clocks = timed(run_counted, args.steps, args.warmup, device, sample_clocks=(rank == 0))
     gpu_launches = bindings.launch_count() - launches_before[0]   # counted in C at every launch site
+    launch_unit = "kernel launches of this framework (counted in C at every launch site)"
+    if fp32 and gpu_launches == 0:
+        # the fp32 arm replays the engine's captured step: one graph launch per step, holding ATen /
+        # cuBLAS kernels and this framework's fused Adam kernel (captured launches are not re-counted)
+        gpu_launches = args.steps
+        launch_unit = "CUDA graph launches (one captured step each: ATen / cuBLAS kernels + this framework's fused Adam kernel)"
     per_step = gpu_launches / max(args.steps, 1)
     value = world * bsz * args.steps / (ms / 1e3)
 
@@ -193,14 +207,14 @@ def run_ours(args):
                "final_loss": float(host_loss[-1]),
                "api": ("DataParallel.host_stepper().run_pool(pinned_x_pool, pinned_y_pool, first, count): per step one "
                        "H2D of that step's batch and one loss to the host, up to 256 steps per kernel launch")
-               if use_run else "DataParallel.host_stepper().step(pinned_x, pinned_y)"}
+               if use_run and not fp32 else "DataParallel.host_stepper().step(pinned_x, pinned_y) (one native call per step)"}
 
     if rank == 0:
         out = {
             "metric": "train samples/sec (device-timed, max over ranks)", "value": value,
             "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic (random-init weights)",
+            "vs_baseline": None, "dtype": args.dtype, "data": "synthetic (random-init weights)",
             "impl": "b200ddp",
             "config": {"model": "SimpleNet 784-256-256-10 (reference train.py model)",
                        "global_batch": world * bsz, "per_rank_batch": bsz, "seq_len": None,
@@ -214,6 +228,7 @@ def run_ours(args):
             # one launch of the fused step kernel runs many whole steps (forward, loss, backward,
             # all-reduce, Adam each); kernels_per_step counts the kernels a step's work runs in
             "steps_per_launch": (args.steps / gpu_launches) if gpu_launches else None,
+            "launch_unit": launch_unit,
         }
         print(json.dumps(out), flush=True)
     dist.destroy_process_group()
